@@ -1,0 +1,636 @@
+// C ABI of ldc_b200 (include/ldc_b200.h): handle management, host<->device plumbing and the launch
+// sequences of the tiled and resident kernel paths.  No exception crosses the boundary.
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+#include "peak.cuh"
+#include "resident_main.cuh"
+#include "tiled.cuh"
+
+namespace ldc {
+thread_local std::string g_last_error;
+
+static bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Copy in either direction; host pointers are complete when this returns.
+static int copy_in(ldc_handle* h, double* dst_dev, const double* src, size_t n) {
+    if (!src) return LDC_OK;
+    const bool dev = is_device_ptr(src);
+    LDC_CUDA(cudaMemcpyAsync(dst_dev, src, n * sizeof(double), dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                             h->stream));
+    if (!dev) LDC_CUDA(cudaStreamSynchronize(h->stream));
+    return LDC_OK;
+}
+
+static int copy_out(ldc_handle* h, void* dst, const void* src_dev, size_t bytes) {
+    if (!dst) return LDC_OK;
+    const bool dev = is_device_ptr(dst);
+    LDC_CUDA(cudaMemcpyAsync(dst, src_dev, bytes, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    if (!dev) LDC_CUDA(cudaStreamSynchronize(h->stream));
+    return LDC_OK;
+}
+
+template <typename T>
+static int dalloc(T** p, size_t n) {
+    LDC_CUDA(cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T)));
+    LDC_CUDA(cudaMemset(*p, 0, std::max<size_t>(n, 1) * sizeof(T)));
+    return LDC_OK;
+}
+
+static dim3 grid2d(int rows, int cols, int B) { return dim3((cols + 31) / 32, (rows + 7) / 8, B); }
+static const dim3 kBlock2d(32, 8, 1);
+
+// p_full = Ix p Iy^T of `psrc` into h->pfull (spectral/sg.py:255-276).
+static void launch_pfull(ldc_handle* h, const double* psrc, const CavityStatus* mask) {
+    k_left_mul<<<grid2d(h->n1x, h->my, h->B), kBlock2d, 0, h->stream>>>(h->Ix, psrc, h->ptmp, h->n1x, h->mx, h->my, mask);
+    // Iy is (n1y x my) row-major, i.e. already "A^T" (my x n1y) of the map p -> p Iy^T when read as AT[k][j] = Iy[j][k];
+    // k_right_mul wants AT (ca x ra) = Iy^T stored row-major, which set_operators prepared in h->IyT.
+    k_right_mul<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(h->ptmp, h->IyT, h->pfull, h->n1x, h->my, h->n1y,
+                                                                          mask);
+    h->launches += 2;
+}
+
+static void launch_residual(ldc_handle* h, const double* u, const double* v, const double* psrc, const CavityStatus* mask) {
+    launch_pfull(h, psrc, mask);
+    k_residual<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(u, v, h->pfull, h->Dx, h->Dxx, h->DyT, h->DyyT, h->Re,
+                                                                        h->beta2, h->Ru, h->Rv, h->Rp, h->n1x, h->n1y, mask);
+    h->launches += 1;
+}
+
+// One RK4 step of every active cavity on the tiled path.
+static void launch_tiled_step(ldc_handle* h, int freeze_pressure, int warmup, long long max_iter, int nan_exit,
+                              const double* tol) {
+    const int nfull = h->n1x * h->n1y, ninner = h->mx * h->my;
+    k_step_begin<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->p, h->u0, h->v0, h->p0, h->dt, h->Re, h->beta2, h->CFL,
+                                                     h->lidvel, h->dx_min, h->dy_min, nfull, ninner, h->status);
+    h->launches += 1;
+    for (int s = 0; s < 4; ++s) {
+        // freeze_pressure: SGSolver takes grad(p^n) in all four stages; p itself is still staged
+        launch_residual(h, h->u, h->v, freeze_pressure ? h->p0 : h->p, h->status);
+        k_stage_update<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(
+            h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->dt, h->ulid, h->vlid, rk_alpha(s), h->n1x, h->n1y, 1,
+            h->status);
+        h->launches += 1;
+    }
+    k_step_end<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->u0, h->v0, nfull, tol, warmup, max_iter, nan_exit, h->status);
+    h->launches += 1;
+}
+
+static int count_active(ldc_handle* h, int* out) {
+    k_count_active<<<1, 256, 0, h->stream>>>(h->status, h->B, h->n_active);
+    h->launches += 1;
+    LDC_CUDA(cudaMemcpyAsync(h->h_pinned, h->n_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    LDC_CUDA(cudaStreamSynchronize(h->stream));
+    *out = *h->h_pinned;
+    return LDC_OK;
+}
+
+static int check_ready(const ldc_handle* h, const char* who) {
+    if (!h) return fail(LDC_ERR_INVALID, std::string(who) + ": null handle");
+    if (!h->ops_set) return fail(LDC_ERR_STATE, std::string(who) + ": ldc_set_operators has not been called");
+    if (!h->cases_set) return fail(LDC_ERR_STATE, std::string(who) + ": ldc_set_cases has not been called");
+    return LDC_OK;
+}
+
+}  // namespace ldc
+
+using namespace ldc;
+
+namespace ldc {
+
+static bool resident_shape_ok(const ldc_handle* h) {
+    return h->nx == h->ny && res_pick_mp(h->mx) != 0;
+}
+
+// Dynamic shared memory the resident kernel needs for this handle (bytes), 0 if unsupported.
+static size_t resident_smem_bytes(const ldc_handle* h) {
+    if (!resident_shape_ok(h)) return 0;
+    const int MP = res_pick_mp(h->mx);
+    const int warps = MP == 64 ? 8 : (MP == 48 ? 6 : 4);
+    const size_t MAT = (size_t)MP * res_ld(MP);
+    const size_t d = (h->square_ops ? 3 : 6) * MAT + 8 * MP + 3 * MAT + 8 * MP + 8 + 2 * MP + 4 + 8 * warps;
+    return d * sizeof(double);
+}
+
+static bool resident_ok(const ldc_handle* h) {
+    const size_t bytes = resident_smem_bytes(h);
+    if (bytes == 0) return false;
+    int max_optin = 0;
+    if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return false;
+    return bytes <= (size_t)max_optin;
+}
+
+static bool use_resident(const ldc_handle* h) {
+    if (h->path == LDC_PATH_TILED) return false;
+    return resident_ok(h);
+}
+
+// canonical <-> packed state synchronisation
+static int ensure_canonical(ldc_handle* h) {
+    if (h->canon_valid) return LDC_OK;
+    const int n1 = h->n1x;
+    k_unpack_state<<<dim3((n1 * n1 + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride, n1,
+                                                                             h->MP);
+    h->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    h->canon_valid = true;
+    return LDC_OK;
+}
+
+static int ensure_packed(ldc_handle* h) {
+    if (h->packed_valid) return LDC_OK;
+    const int MP = h->MP, LD = res_ld(MP);
+    k_pack_state<<<dim3((MP * LD + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride,
+                                                                           h->n1x, MP);
+    h->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    h->packed_valid = true;
+    return LDC_OK;
+}
+
+}  // namespace ldc
+
+extern "C" {
+
+const char* ldc_version(void) { return "ldc_b200 0.1.0 sm_100a"; }
+const char* ldc_last_error(void) { return g_last_error.c_str(); }
+
+int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_stream) {
+    if (!out) return fail(LDC_ERR_INVALID, "ldc_create: out is null");
+    *out = nullptr;
+    if (nx < 2 || ny < 2 || batch < 1) return fail(LDC_ERR_INVALID, "ldc_create: need nx, ny >= 2 and batch >= 1");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(LDC_ERR_CUDA, "ldc_create: no CUDA device is visible (this library has no CPU fallback)");
+    }
+    if (device < 0 || device >= ndev) return fail(LDC_ERR_INVALID, "ldc_create: device index out of range");
+    LDC_CUDA(cudaSetDevice(device));
+    ldc_handle* h = new (std::nothrow) ldc_handle();
+    if (!h) return fail(LDC_ERR_INVALID, "ldc_create: out of host memory");
+    h->nx = nx; h->ny = ny; h->n1x = nx + 1; h->n1y = ny + 1; h->mx = nx - 1; h->my = ny - 1;
+    h->B = batch; h->device = device; h->stream = (cudaStream_t)cuda_stream;
+    const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my, B = batch;
+    int rc = LDC_OK;
+#define A_(p, n) if (rc == LDC_OK) rc = dalloc(&h->p, (n))
+    A_(Dx, (size_t)h->n1x * h->n1x); A_(Dxx, (size_t)h->n1x * h->n1x);
+    A_(Dy, (size_t)h->n1y * h->n1y); A_(Dyy, (size_t)h->n1y * h->n1y);
+    A_(DyT, (size_t)h->n1y * h->n1y); A_(DyyT, (size_t)h->n1y * h->n1y);
+    A_(Ix, (size_t)h->n1x * h->mx); A_(Iy, (size_t)h->n1y * h->my); A_(IyT, (size_t)h->n1y * h->my);
+    A_(Re, B); A_(beta2, B); A_(CFL, B); A_(lidvel, B); A_(ulid, B * h->n1x); A_(vlid, B * h->n1x);
+    A_(u, B * nf); A_(v, B * nf); A_(p, B * ni); A_(u0, B * nf); A_(v0, B * nf); A_(p0, B * ni);
+    A_(Ru, B * nf); A_(Rv, B * nf); A_(Rp, B * ni); A_(ptmp, B * h->n1x * h->my); A_(pfull, B * nf);
+    A_(dt, B); A_(tol, B); A_(status, B); A_(n_active, 1);
+    if (rc == LDC_OK && resident_shape_ok(h)) {
+        h->MP = res_pick_mp(h->mx);
+        h->LD = res_ld(h->MP);
+        h->r_state_stride = res_state_stride(h->MP);
+        A_(r_ops, res_ops_size(h->MP, false));
+        A_(r_state, B * h->r_state_stride);
+    }
+#undef A_
+    if (rc == LDC_OK && cudaMallocHost((void**)&h->h_pinned, sizeof(int)) != cudaSuccess)
+        rc = fail(LDC_ERR_CUDA, "ldc_create: cudaMallocHost failed");
+    if (rc == LDC_OK && (cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess))
+        rc = fail(LDC_ERR_CUDA, "ldc_create: cudaEventCreate failed");
+    if (rc != LDC_OK) {
+        const std::string keep = g_last_error;
+        ldc_destroy(h);
+        g_last_error = keep;
+        return rc;
+    }
+    *out = h;
+    return LDC_OK;
+}
+
+void ldc_destroy(ldc_t* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
+                      h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
+                      h->tol, h->r_ops, h->r_state};
+    for (double* q : ptrs) if (q) cudaFree(q);
+    if (h->status) cudaFree(h->status);
+    if (h->n_active) cudaFree(h->n_active);
+    if (h->ticket) cudaFree(h->ticket);
+    if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    delete h;
+}
+
+int ldc_set_path(ldc_t* h, int path) {
+    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (path == LDC_PATH_RESIDENT && !resident_shape_ok(h))
+        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the resident path needs nx == ny and nx - 1 <= 64");
+    h->path = path;
+    return LDC_OK;
+}
+
+int ldc_resident_supported(const ldc_t* h) {
+    if (!h) return fail(LDC_ERR_INVALID, "ldc_resident_supported: null handle");
+    return resident_ok(h) ? LDC_OK : LDC_ERR_UNSUPPORTED;
+}
+
+int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const double* Dy, const double* Dyy, const double* Ix,
+                      const double* Iy, double dx_min, double dy_min) {
+    if (!h || !Dx || !Dxx || !Dy || !Dyy || !Ix || !Iy) return fail(LDC_ERR_INVALID, "ldc_set_operators: null argument");
+    if (!(dx_min > 0) || !(dy_min > 0)) return fail(LDC_ERR_INVALID, "ldc_set_operators: dx_min, dy_min must be positive");
+    LDC_CUDA(cudaSetDevice(h->device));
+    const size_t sx = (size_t)h->n1x * h->n1x, sy = (size_t)h->n1y * h->n1y;
+    int rc;
+    if ((rc = copy_in(h, h->Dx, Dx, sx))) return rc;
+    if ((rc = copy_in(h, h->Dxx, Dxx, sx))) return rc;
+    if ((rc = copy_in(h, h->Dy, Dy, sy))) return rc;
+    if ((rc = copy_in(h, h->Dyy, Dyy, sy))) return rc;
+    if ((rc = copy_in(h, h->Ix, Ix, (size_t)h->n1x * h->mx))) return rc;
+    if ((rc = copy_in(h, h->Iy, Iy, (size_t)h->n1y * h->my))) return rc;
+    h->dx_min = dx_min;
+    h->dy_min = dy_min;
+    const int T = 256;
+    k_transpose<<<(int)((sy + T - 1) / T), T, 0, h->stream>>>(h->Dy, h->DyT, h->n1y, h->n1y);
+    k_transpose<<<(int)((sy + T - 1) / T), T, 0, h->stream>>>(h->Dyy, h->DyyT, h->n1y, h->n1y);
+    k_transpose<<<(h->n1y * h->my + T - 1) / T, T, 0, h->stream>>>(h->Iy, h->IyT, h->n1y, h->my);
+    h->launches += 3;
+    // square_ops: x and y operators identical bit for bit (lets the resident kernel keep one copy in shared memory)
+    h->square_ops = false;
+    if (h->nx == h->ny) {
+        std::vector<double> a(sx), b(sx);
+        bool same = (dx_min == dy_min);
+        const double* px[3] = {h->Dx, h->Dxx, h->Ix};
+        const double* py[3] = {h->Dy, h->Dyy, h->Iy};
+        const size_t sz[3] = {sx, sx, (size_t)h->n1x * h->mx};
+        for (int q = 0; q < 3 && same; ++q) {
+            LDC_CUDA(cudaMemcpyAsync(a.data(), px[q], sz[q] * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(b.data(), py[q], sz[q] * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            LDC_CUDA(cudaStreamSynchronize(h->stream));
+            same = std::memcmp(a.data(), b.data(), sz[q] * sizeof(double)) == 0;
+        }
+        h->square_ops = same;
+    }
+    if (h->r_ops) {
+        // G = (D I) rows 1..n-2: the pressure interpolation folded into the derivative (resident.cuh)
+        const int MP = h->MP, LD = res_ld(MP), n1 = h->n1x, m = h->mx;
+        const size_t MAT = (size_t)MP * LD;
+        double* DI = h->pfull;  // scratch: n1 x m doubles fit in one cavity's full grid
+        LDC_CUDA(cudaMemsetAsync(h->r_ops, 0, res_ops_size(MP, false) * sizeof(double), h->stream));
+        double* vecs = h->r_ops + (h->square_ops ? 3 : 6) * MAT;
+        k_left_mul<<<grid2d(n1, m, 1), kBlock2d, 0, h->stream>>>(h->Dx, h->Ix, DI, n1, n1, m, nullptr);
+        k_pack_ops<<<(int)((MAT + T - 1) / T), T, 0, h->stream>>>(h->Dx, h->Dxx, DI, h->r_ops, vecs, n1, MP);
+        k_left_mul<<<grid2d(n1, m, 1), kBlock2d, 0, h->stream>>>(h->Dy, h->Iy, DI, n1, n1, m, nullptr);
+        k_pack_ops<<<(int)((MAT + T - 1) / T), T, 0, h->stream>>>(h->Dy, h->Dyy, DI, h->square_ops ? h->r_ops : h->r_ops + 3 * MAT,
+                                                                 vecs + 4 * MP, n1, MP);
+        h->launches += 4;
+    }
+    LDC_CUDA(cudaGetLastError());
+    LDC_CUDA(cudaStreamSynchronize(h->stream));
+    h->ops_set = true;
+    return LDC_OK;
+}
+
+int ldc_set_cases(ldc_t* h, const double* Re, const double* beta2, const double* CFL, const double* lid_velocity,
+                  const double* u_lid, const double* v_lid) {
+    if (!h || !Re || !beta2 || !CFL || !lid_velocity || !u_lid || !v_lid)
+        return fail(LDC_ERR_INVALID, "ldc_set_cases: null argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = copy_in(h, h->Re, Re, h->B))) return rc;
+    if ((rc = copy_in(h, h->beta2, beta2, h->B))) return rc;
+    if ((rc = copy_in(h, h->CFL, CFL, h->B))) return rc;
+    if ((rc = copy_in(h, h->lidvel, lid_velocity, h->B))) return rc;
+    if ((rc = copy_in(h, h->ulid, u_lid, (size_t)h->B * h->n1x))) return rc;
+    if ((rc = copy_in(h, h->vlid, v_lid, (size_t)h->B * h->n1x))) return rc;
+    h->cases_set = true;
+    return LDC_OK;
+}
+
+int ldc_set_state(ldc_t* h, const double* u, const double* v, const double* p) {
+    if (!h) return fail(LDC_ERR_INVALID, "ldc_set_state: null handle");
+    LDC_CUDA(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = ensure_canonical(h))) return rc;  // partial updates keep the other fields
+    const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my;
+    if ((rc = copy_in(h, h->u, u, h->B * nf))) return rc;
+    if ((rc = copy_in(h, h->v, v, h->B * nf))) return rc;
+    if ((rc = copy_in(h, h->p, p, h->B * ni))) return rc;
+    h->packed_valid = false;
+    return LDC_OK;
+}
+
+int ldc_get_state(ldc_t* h, double* u, double* v, double* p) {
+    if (!h) return fail(LDC_ERR_INVALID, "ldc_get_state: null handle");
+    LDC_CUDA(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = ensure_canonical(h))) return rc;
+    const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my;
+    if ((rc = copy_out(h, u, h->u, h->B * nf * sizeof(double)))) return rc;
+    if ((rc = copy_out(h, v, h->v, h->B * nf * sizeof(double)))) return rc;
+    if ((rc = copy_out(h, p, h->p, h->B * ni * sizeof(double)))) return rc;
+    return LDC_OK;
+}
+
+int ldc_init_state(ldc_t* h) {
+    if (!h) return fail(LDC_ERR_INVALID, "ldc_init_state: null handle");
+    if (!h->cases_set) return fail(LDC_ERR_STATE, "ldc_init_state: ldc_set_cases has not been called");
+    LDC_CUDA(cudaSetDevice(h->device));
+    const int nfull = h->n1x * h->n1y;
+    k_init_state<<<dim3((nfull + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->ulid, h->vlid, h->n1x, h->n1y);
+    h->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    h->canon_valid = true;
+    h->packed_valid = false;
+    return LDC_OK;
+}
+
+int ldc_residual(ldc_t* h, double* Ru, double* Rv, double* Rp, double* norms) {
+    int rc = check_ready(h, "ldc_residual");
+    if (rc) return rc;
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = ensure_canonical(h))) return rc;
+    launch_residual(h, h->u, h->v, h->p, nullptr);
+    LDC_CUDA(cudaGetLastError());
+    const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my;
+    if ((rc = copy_out(h, Ru, h->Ru, h->B * nf * sizeof(double)))) return rc;
+    if ((rc = copy_out(h, Rv, h->Rv, h->B * nf * sizeof(double)))) return rc;
+    if ((rc = copy_out(h, Rp, h->Rp, h->B * ni * sizeof(double)))) return rc;
+    if (norms) {
+        double* d = h->ptmp;  // scratch [B][3] (B * n1x * my >= 3 B)
+        k_residual_norms<<<h->B, RED_THREADS, 0, h->stream>>>(h->Ru, h->Rv, h->Rp, (int)nf, (int)ni, d);
+        h->launches += 1;
+        LDC_CUDA(cudaGetLastError());
+        if ((rc = copy_out(h, norms, d, (size_t)h->B * 3 * sizeof(double)))) return rc;
+    }
+    return LDC_OK;
+}
+
+}  // extern "C"
+
+namespace ldc {
+
+__global__ void k_export_status(const CavityStatus* __restrict__ st, int B, long long* iters, int* conv, int* divg,
+                                double* rel, double* uv) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const CavityStatus s = st[b];
+    iters[b] = s.iters;
+    conv[b] = s.converged;
+    divg[b] = s.diverged;
+    rel[b] = (s.v_res > s.u_res) ? s.v_res : s.u_res;
+    uv[2 * b] = s.u_res;
+    uv[2 * b + 1] = s.v_res;
+}
+
+template <int MP, int WM, int WN>
+static int launch_resident_t(ldc_handle* h, const ResParams& P) {
+    using C = ResCfg<MP, WM, WN>;
+    const size_t bytes = C::smem_doubles(h->square_ops) * sizeof(double);
+    LDC_CUDA(cudaFuncSetAttribute(k_resident_rk4<MP, WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    k_resident_rk4<MP, WM, WN><<<h->B, C::THREADS, bytes, h->stream>>>(P);
+    h->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+static int launch_resident(ldc_handle* h, const ResParams& P) {
+    switch (h->MP) {
+        case 16: return launch_resident_t<16, 2, 2>(h, P);
+        case 32: return launch_resident_t<32, 2, 2>(h, P);
+        case 48: return launch_resident_t<48, 2, 3>(h, P);
+        case 64: return launch_resident_t<64, 2, 4>(h, P);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "resident path: unsupported padded size");
+}
+
+// Shared driver of ldc_step / ldc_solve: iterate until every cavity is inactive.
+static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, int warmup, int freeze, int nan_exit) {
+    k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+    h->launches += 1;
+    int rc;
+    const bool resident = use_resident(h);
+    if (h->path == LDC_PATH_RESIDENT && !resident)
+        return fail(LDC_ERR_UNSUPPORTED, "resident path requested but the shape does not fit shared memory");
+    LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
+    if (resident) {
+        if ((rc = ensure_packed(h))) return rc;
+        ResParams P;
+        P.ops = h->r_ops; P.square = h->square_ops ? 1 : 0;
+        P.state = h->r_state; P.state_stride = h->r_state_stride;
+        P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
+        P.n1 = h->n1x; P.m = h->mx; P.K4 = (h->mx + 3) / 4 * 4;
+        P.dx_min = h->dx_min; P.dy_min = h->dy_min;
+        P.status = h->status; P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.freeze = freeze;
+        P.max_iter = max_iter;
+        const long long chunk = h->MP >= 64 ? 1024 : (h->MP >= 48 ? 2048 : (h->MP >= 32 ? 4096 : 16384));
+        h->canon_valid = false;
+        for (long long done = 0; done < max_iter; done += chunk) {
+            P.n_steps = std::min(chunk, max_iter - done);
+            if ((rc = launch_resident(h, P))) return rc;
+            if (done + chunk < max_iter) {
+                int na = 0;
+                if ((rc = count_active(h, &na))) return rc;
+                if (na == 0) break;
+            }
+        }
+    } else {
+        if ((rc = ensure_canonical(h))) return rc;
+        h->packed_valid = false;
+        const long long chunk = 64;
+        for (long long done = 0; done < max_iter; done += chunk) {
+            const long long n = std::min(chunk, max_iter - done);
+            for (long long s = 0; s < n; ++s) launch_tiled_step(h, freeze, warmup, max_iter, nan_exit, tol_dev);
+            LDC_CUDA(cudaGetLastError());
+            if (done + chunk < max_iter) {
+                int na = 0;
+                if ((rc = count_active(h, &na))) return rc;
+                if (na == 0) break;
+            }
+        }
+    }
+    LDC_CUDA(cudaEventRecord(h->ev1, h->stream));
+    LDC_CUDA(cudaEventSynchronize(h->ev1));
+    float ms = 0;
+    LDC_CUDA(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    h->last_ms = ms;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+// Export per-cavity status through scratch device buffers carved out of h->Ru.
+static int export_status(ldc_handle* h, int64_t* iters, int32_t* conv, int32_t* divg, double* rel, double* uv) {
+    char* base = reinterpret_cast<char*>(h->Ru);
+    const size_t B = h->B;
+    long long* d_it = reinterpret_cast<long long*>(base);
+    double* d_rel = reinterpret_cast<double*>(base + 8 * B);
+    double* d_uv = reinterpret_cast<double*>(base + 16 * B);
+    int* d_cv = reinterpret_cast<int*>(base + 32 * B);
+    int* d_dv = reinterpret_cast<int*>(base + 36 * B);
+    k_export_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B, d_it, d_cv, d_dv, d_rel, d_uv);
+    h->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    int rc;
+    if ((rc = copy_out(h, iters, d_it, B * 8))) return rc;
+    if ((rc = copy_out(h, conv, d_cv, B * 4))) return rc;
+    if ((rc = copy_out(h, divg, d_dv, B * 4))) return rc;
+    if ((rc = copy_out(h, rel, d_rel, B * 8))) return rc;
+    if ((rc = copy_out(h, uv, d_uv, B * 16))) return rc;
+    return LDC_OK;
+}
+
+}  // namespace ldc
+
+extern "C" {
+
+int ldc_step(ldc_t* h, int64_t n_steps, int freeze_pressure, double* rel) {
+    int rc = check_ready(h, "ldc_step");
+    if (rc) return rc;
+    if (n_steps < 0) return fail(LDC_ERR_INVALID, "ldc_step: n_steps must be >= 0");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if (n_steps == 0) return LDC_OK;
+    if ((rc = run_steps(h, nullptr, n_steps, 0, freeze_pressure ? 1 : 0, 0))) return rc;
+    if (rel) return export_status(h, nullptr, nullptr, nullptr, nullptr, rel);
+    return LDC_OK;
+}
+
+int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit, int64_t* iters,
+              int32_t* converged, int32_t* diverged, double* rel_res) {
+    int rc = check_ready(h, "ldc_solve");
+    if (rc) return rc;
+    if (!tol || max_iter < 0 || warmup < 0) return fail(LDC_ERR_INVALID, "ldc_solve: bad argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = copy_in(h, h->tol, tol, h->B))) return rc;
+    if (max_iter > 0) {
+        if ((rc = run_steps(h, h->tol, max_iter, warmup, freeze_pressure ? 1 : 0, nan_exit ? 1 : 0))) return rc;
+    } else {
+        k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 1;
+    }
+    return export_status(h, iters, converged, diverged, rel_res, nullptr);
+}
+
+int ldc_diagnostics(ldc_t* h, const double* W, double* out) {
+    int rc = check_ready(h, "ldc_diagnostics");
+    if (rc) return rc;
+    if (!W || !out) return fail(LDC_ERR_INVALID, "ldc_diagnostics: null argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = ensure_canonical(h))) return rc;
+    const size_t nf = (size_t)h->n1x * h->n1y;
+    double* dW = h->Rv;          // scratch: one full grid
+    double* dOut = h->Rv + nf;   // scratch: [B][3]   (B * nf >= nf + 3 B needs B >= 2 or nf > 3: checked below)
+    double* tmpW = nullptr;
+    if ((size_t)h->B * nf < nf + 3 * (size_t)h->B) {
+        LDC_CUDA(cudaMalloc((void**)&tmpW, (nf + 3 * h->B) * sizeof(double)));
+        dW = tmpW;
+        dOut = tmpW + nf;
+    }
+    if ((rc = copy_in(h, dW, W, nf))) return rc;
+    k_vorticity<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(h->u, h->v, h->Dx, h->DyT, h->pfull, h->n1x, h->n1y);
+    k_diagnostics<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->pfull, h->Dx, h->DyT, dW, dOut, h->n1x, h->n1y);
+    h->launches += 2;
+    LDC_CUDA(cudaGetLastError());
+    rc = copy_out(h, out, dOut, (size_t)h->B * 3 * sizeof(double));
+    if (tmpW) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(tmpW);
+    }
+    return rc;
+}
+
+static int transfer_fields(ldc_t* src, ldc_t* dst, const double* Pxu, const double* Pyu, const double* Pxp, const double* Pyp,
+                           const char* who) {
+    if (!src || !dst || !Pxu || !Pyu || !Pxp || !Pyp) return fail(LDC_ERR_INVALID, std::string(who) + ": null argument");
+    if (src->B != dst->B || src->device != dst->device)
+        return fail(LDC_ERR_INVALID, std::string(who) + ": handles must share batch size and device");
+    if (!dst->cases_set) return fail(LDC_ERR_STATE, std::string(who) + ": ldc_set_cases has not been called on the target");
+    int rc;
+    if ((rc = ensure_canonical(src))) return rc;
+    // order the target stream after the source stream
+    if (src->stream != dst->stream) {
+        LDC_CUDA(cudaEventRecord(src->ev1, src->stream));
+        LDC_CUDA(cudaStreamWaitEvent(dst->stream, src->ev1, 0));
+    }
+    ldc_t* h = dst;
+    // transfer matrices live in the target's operator scratch (ptmp is big enough only for p; use a temp allocation)
+    const size_t sz_xu = (size_t)dst->n1x * src->n1x, sz_yu = (size_t)dst->n1y * src->n1y;
+    const size_t sz_xp = (size_t)dst->mx * src->mx, sz_yp = (size_t)dst->my * src->my;
+    double* M = nullptr;
+    LDC_CUDA(cudaMalloc((void**)&M, (sz_xu + 2 * sz_yu + sz_xp + 2 * sz_yp) * sizeof(double)));
+    double *dPxu = M, *dPyu = dPxu + sz_xu, *dPyuT = dPyu + sz_yu, *dPxp = dPyuT + sz_yu, *dPyp = dPxp + sz_xp,
+           *dPypT = dPyp + sz_yp;
+    rc = copy_in(h, dPxu, Pxu, sz_xu);
+    if (!rc) rc = copy_in(h, dPyu, Pyu, sz_yu);
+    if (!rc) rc = copy_in(h, dPxp, Pxp, sz_xp);
+    if (!rc) rc = copy_in(h, dPyp, Pyp, sz_yp);
+    if (rc) { cudaFree(M); return rc; }
+    const int T = 256;
+    k_transpose<<<(int)((sz_yu + T - 1) / T), T, 0, h->stream>>>(dPyu, dPyuT, dst->n1y, src->n1y);
+    k_transpose<<<(int)((sz_yp + T - 1) / T), T, 0, h->stream>>>(dPyp, dPypT, dst->my, src->my);
+    // U_dst = Px U_src Py^T: columns first (left multiply), then rows (operators/transfer_operators.py:93-130)
+    double* tmp = dst->Ru;  // dst.n1x x src.n1y per cavity; Ru is at least as large when dst is the finer grid
+    double* tmp_alloc = nullptr;
+    if ((size_t)dst->n1x * src->n1y > (size_t)dst->n1x * dst->n1y) {
+        LDC_CUDA(cudaMalloc((void**)&tmp_alloc, (size_t)dst->B * dst->n1x * src->n1y * sizeof(double)));
+        tmp = tmp_alloc;
+    }
+    const double* sf[2] = {src->u, src->v};
+    double* df[2] = {dst->u, dst->v};
+    for (int f = 0; f < 2; ++f) {
+        k_left_mul<<<grid2d(dst->n1x, src->n1y, h->B), kBlock2d, 0, h->stream>>>(dPxu, sf[f], tmp, dst->n1x, src->n1x, src->n1y,
+                                                                                 nullptr);
+        k_right_mul<<<grid2d(dst->n1x, dst->n1y, h->B), kBlock2d, 0, h->stream>>>(tmp, dPyuT, df[f], dst->n1x, src->n1y,
+                                                                                  dst->n1y, nullptr);
+    }
+    k_left_mul<<<grid2d(dst->mx, src->my, h->B), kBlock2d, 0, h->stream>>>(dPxp, src->p, tmp, dst->mx, src->mx, src->my, nullptr);
+    k_right_mul<<<grid2d(dst->mx, dst->my, h->B), kBlock2d, 0, h->stream>>>(tmp, dPypT, dst->p, dst->mx, src->my, dst->my, nullptr);
+    h->launches += 8;
+    cudaError_t e = cudaGetLastError();
+    cudaStreamSynchronize(h->stream);
+    cudaFree(M);
+    if (tmp_alloc) cudaFree(tmp_alloc);
+    if (e != cudaSuccess) return fail(LDC_ERR_CUDA, std::string(who) + ": " + cudaGetErrorString(e));
+    dst->canon_valid = true;
+    dst->packed_valid = false;
+    return LDC_OK;
+}
+
+int ldc_prolongate(ldc_t* coarse, ldc_t* fine, const double* Pxu, const double* Pyu, const double* Pxp, const double* Pyp,
+                   int bc_quirk) {
+    if (fine) LDC_CUDA(cudaSetDevice(fine->device));
+    int rc = transfer_fields(coarse, fine, Pxu, Pyu, Pxp, Pyp, "ldc_prolongate");
+    if (rc) return rc;
+    const int nfull = fine->n1x * fine->n1y;
+    k_transfer_bc<<<dim3((nfull + 255) / 256, fine->B), 256, 0, fine->stream>>>(fine->u, fine->v, fine->ulid, fine->vlid,
+                                                                                 fine->lidvel, fine->n1x, fine->n1y,
+                                                                                 bc_quirk ? 1 : 0);
+    fine->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+int ldc_restrict(ldc_t* fine, ldc_t* coarse, const double* Rxu, const double* Ryu, const double* Rxp, const double* Ryp) {
+    if (coarse) LDC_CUDA(cudaSetDevice(coarse->device));
+    int rc = transfer_fields(fine, coarse, Rxu, Ryu, Rxp, Ryp, "ldc_restrict");
+    if (rc) return rc;
+    const int nfull = coarse->n1x * coarse->n1y;
+    k_transfer_bc<<<dim3((nfull + 255) / 256, coarse->B), 256, 0, coarse->stream>>>(coarse->u, coarse->v, coarse->ulid,
+                                                                                     coarse->vlid, coarse->lidvel, coarse->n1x,
+                                                                                     coarse->n1y, 0);
+    coarse->launches += 1;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+int64_t ldc_launch_count(const ldc_t* h) { return h ? h->launches : 0; }
+double ldc_last_kernel_ms(const ldc_t* h) { return h ? h->last_ms : 0.0; }
+
+int ldc_fp64_peak(int device, int which, double* tflops) { return measure_fp64_peak(device, which, tflops); }
+
+}  // extern "C"

@@ -1,0 +1,225 @@
+"""BatchedSpectralLDC: a batch of independent lid-driven cavities of one polynomial order on one GPU.
+
+Thin host wrapper over the C ABI (include/ldc_b200.h).  All numerics run in the CUDA library; this class
+only builds the per-order operators (operators.py), marshals NumPy / torch buffers and keeps the handle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+from . import operators as ops
+
+_PATHS = {"auto": _lib.LDC_PATH_AUTO, "tiled": _lib.LDC_PATH_TILED, "resident": _lib.LDC_PATH_RESIDENT}
+
+
+@dataclass
+class SolveResult:
+    iterations: np.ndarray   # int64 [B]
+    converged: np.ndarray    # bool  [B]
+    diverged: np.ndarray     # bool  [B]
+    rel_residual: np.ndarray  # float64 [B], last max(u_res, v_res)
+    kernel_ms: float
+
+
+def _per_case(value, B, name):
+    a = np.ascontiguousarray(np.broadcast_to(np.asarray(value, dtype=np.float64), (B,)))
+    if a.shape != (B,):
+        raise ValueError(f"{name} must be a scalar or have shape ({B},)")
+    return a.copy()
+
+
+class BatchedSpectralLDC:
+    """State + operators of `batch` cavities at order (nx, ny); see the reference's SGSolver / SpectralLevel."""
+
+    def __init__(self, nx: int, ny: int | None = None, batch: int = 1, Lx: float = 1.0, Ly: float = 1.0,
+                 basis: str = "chebyshev", device: int = 0, stream: int | None = None, path: str = "auto"):
+        self.lib = _lib.load()
+        ny = nx if ny is None else ny
+        self.nx, self.ny, self.B = int(nx), int(ny), int(batch)
+        self.Lx, self.Ly, self.basis = float(Lx), float(Ly), basis
+        self.device = int(device)
+        self.level = ops.build_level(self.nx, self.ny, self.Lx, self.Ly, basis)
+        self._h = C.c_void_p()
+        _lib.check(self.lib.ldc_create(C.byref(self._h), self.nx, self.ny, self.B, self.device,
+                                       C.c_void_p(stream) if stream else None), "ldc_create")
+        lv = self.level
+        keep = [np.ascontiguousarray(a, dtype=np.float64) for a in (lv.Dx, lv.Dxx, lv.Dy, lv.Dyy, lv.Ix, lv.Iy)]
+        _lib.check(self.lib.ldc_set_operators(self._h, *[_lib.ptr(a) for a in keep], lv.dx_min, lv.dy_min),
+                   "ldc_set_operators")
+        self.set_path(path)
+        self.Re = self.beta_squared = self.CFL = self.lid_velocity = None
+        self.u_lid = self.v_lid = None
+
+    # -- lifetime ------------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.ldc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- configuration -------------------------------------------------------------------------------
+    def set_path(self, path: str):
+        if path not in _PATHS:
+            raise ValueError(f"path must be one of {sorted(_PATHS)}")
+        _lib.check(self.lib.ldc_set_path(self._h, _PATHS[path]), "ldc_set_path")
+        self.path = path
+
+    @property
+    def resident_supported(self) -> bool:
+        return self.lib.ldc_resident_supported(self._h) == 0
+
+    def set_cases(self, Re, beta_squared=5.0, CFL=1.5, lid_velocity=1.0, corner_treatment="smoothing",
+                  corner_smoothing=0.15, u_lid=None, v_lid=None):
+        """Per-cavity physics.  Scalars broadcast over the batch; corner_treatment may be one string or a list."""
+        B = self.B
+        self.Re = _per_case(Re, B, "Re")
+        self.beta_squared = _per_case(beta_squared, B, "beta_squared")
+        self.CFL = _per_case(CFL, B, "CFL")
+        self.lid_velocity = _per_case(lid_velocity, B, "lid_velocity")
+        if u_lid is None:
+            cs = _per_case(corner_smoothing, B, "corner_smoothing")
+            methods = [corner_treatment] * B if isinstance(corner_treatment, str) else list(corner_treatment)
+            if len(methods) != B:
+                raise ValueError("corner_treatment must be one string or one per cavity")
+            u_lid = np.empty((B, self.nx + 1))
+            v_lid = np.empty((B, self.nx + 1))
+            for b in range(B):
+                u_lid[b], v_lid[b] = ops.lid_velocity_profile(self.level.x, methods[b], cs[b], self.lid_velocity[b],
+                                                              self.Lx)
+        self.u_lid = np.ascontiguousarray(u_lid, dtype=np.float64).reshape(B, self.nx + 1)
+        self.v_lid = (np.zeros_like(self.u_lid) if v_lid is None
+                      else np.ascontiguousarray(v_lid, dtype=np.float64).reshape(B, self.nx + 1))
+        _lib.check(self.lib.ldc_set_cases(self._h, _lib.ptr(self.Re), _lib.ptr(self.beta_squared), _lib.ptr(self.CFL),
+                                          _lib.ptr(self.lid_velocity), _lib.ptr(self.u_lid), _lib.ptr(self.v_lid)),
+                   "ldc_set_cases")
+        return self
+
+    # -- state ---------------------------------------------------------------------------------------
+    @property
+    def shape_full(self):
+        return (self.B, self.nx + 1, self.ny + 1)
+
+    @property
+    def shape_inner(self):
+        return (self.B, self.nx - 1, self.ny - 1)
+
+    def init_state(self):
+        _lib.check(self.lib.ldc_init_state(self._h), "ldc_init_state")
+        return self
+
+    def _as_in(self, a, shape, name):
+        if a is None:
+            return None
+        if hasattr(a, "data_ptr"):
+            if tuple(a.shape) != shape or str(a.dtype) != "torch.float64":
+                raise ValueError(f"{name} must be float64 of shape {shape}")
+            return a.contiguous()
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        if a.size != int(np.prod(shape)):
+            raise ValueError(f"{name} must have shape {shape}")
+        return a.reshape(shape)
+
+    def set_state(self, u=None, v=None, p=None):
+        u = self._as_in(u, self.shape_full, "u")
+        v = self._as_in(v, self.shape_full, "v")
+        p = self._as_in(p, self.shape_inner, "p")
+        _lib.check(self.lib.ldc_set_state(self._h, _lib.ptr(u), _lib.ptr(v), _lib.ptr(p)), "ldc_set_state")
+        return self
+
+    def get_state(self, out=None):
+        """(u, v, p) as NumPy arrays, or into the given (u, v, p) buffers (NumPy or torch, host or device)."""
+        if out is None:
+            out = (np.empty(self.shape_full), np.empty(self.shape_full), np.empty(self.shape_inner))
+        u, v, p = out
+        _lib.check(self.lib.ldc_get_state(self._h, _lib.ptr(u), _lib.ptr(v), _lib.ptr(p)), "ldc_get_state")
+        return u, v, p
+
+    # -- numerics ------------------------------------------------------------------------------------
+    def residual(self):
+        """(R_u, R_v, R_p, norms[B,3]) of the current state on all nodes."""
+        Ru, Rv, Rp = np.empty(self.shape_full), np.empty(self.shape_full), np.empty(self.shape_inner)
+        norms = np.empty((self.B, 3))
+        _lib.check(self.lib.ldc_residual(self._h, _lib.ptr(Ru), _lib.ptr(Rv), _lib.ptr(Rp), _lib.ptr(norms)),
+                   "ldc_residual")
+        return Ru, Rv, Rp, norms
+
+    def residual_norms(self):
+        norms = np.empty((self.B, 3))
+        _lib.check(self.lib.ldc_residual(self._h, None, None, None, _lib.ptr(norms)), "ldc_residual")
+        return norms
+
+    def step(self, n_steps: int = 1, freeze_pressure: bool = False, want_rel: bool = True):
+        """n_steps RK4 pseudo-steps of every cavity; returns [B,2] (u_res, v_res) of the last step."""
+        rel = np.empty((self.B, 2)) if want_rel else None
+        _lib.check(self.lib.ldc_step(self._h, int(n_steps), int(bool(freeze_pressure)), _lib.ptr(rel)), "ldc_step")
+        return rel
+
+    def solve(self, tolerance, max_iter: int, warmup: int = 0, freeze_pressure: bool = False,
+              nan_exit: bool = True) -> SolveResult:
+        tol = _per_case(tolerance, self.B, "tolerance")
+        iters = np.zeros(self.B, dtype=np.int64)
+        conv = np.zeros(self.B, dtype=np.int32)
+        divg = np.zeros(self.B, dtype=np.int32)
+        rel = np.zeros(self.B)
+        _lib.check(self.lib.ldc_solve(self._h, _lib.ptr(tol), int(max_iter), int(warmup), int(bool(freeze_pressure)),
+                                      int(bool(nan_exit)), _lib.ptr(iters), _lib.ptr(conv), _lib.ptr(divg),
+                                      _lib.ptr(rel)), "ldc_solve")
+        return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, self.last_kernel_ms)
+
+    def diagnostics(self):
+        """[B,3] = (energy, enstrophy, palinstrophy)."""
+        out = np.empty((self.B, 3))
+        W = np.ascontiguousarray(self.level.W)
+        _lib.check(self.lib.ldc_diagnostics(self._h, _lib.ptr(W), _lib.ptr(out)), "ldc_diagnostics")
+        return out
+
+    def prolongate_to(self, fine: "BatchedSpectralLDC", method: str = "fft", bc_quirk: bool = True):
+        """Coarse -> fine initial guess (prolongate_solution, multigrid/fsg.py:551-614)."""
+        Pxu = np.ascontiguousarray(ops.prolongation_matrix(self.nx + 1, fine.nx + 1, method))
+        Pyu = np.ascontiguousarray(ops.prolongation_matrix(self.ny + 1, fine.ny + 1, method))
+        Pxp = np.ascontiguousarray(ops.prolongation_matrix(self.nx - 1, fine.nx - 1, method))
+        Pyp = np.ascontiguousarray(ops.prolongation_matrix(self.ny - 1, fine.ny - 1, method))
+        _lib.check(self.lib.ldc_prolongate(self._h, fine._h, _lib.ptr(Pxu), _lib.ptr(Pyu), _lib.ptr(Pxp),
+                                           _lib.ptr(Pyp), int(bool(bc_quirk))), "ldc_prolongate")
+        return fine
+
+    def restrict_to(self, coarse: "BatchedSpectralLDC", method: str = "fft"):
+        Rxu = np.ascontiguousarray(ops.restriction_matrix(self.nx + 1, coarse.nx + 1, method))
+        Ryu = np.ascontiguousarray(ops.restriction_matrix(self.ny + 1, coarse.ny + 1, method))
+        Rxp = np.ascontiguousarray(ops.restriction_matrix(self.nx - 1, coarse.nx - 1, method))
+        Ryp = np.ascontiguousarray(ops.restriction_matrix(self.ny - 1, coarse.ny - 1, method))
+        _lib.check(self.lib.ldc_restrict(self._h, coarse._h, _lib.ptr(Rxu), _lib.ptr(Ryu), _lib.ptr(Rxp),
+                                         _lib.ptr(Ryp)), "ldc_restrict")
+        return coarse
+
+    # -- accounting ----------------------------------------------------------------------------------
+    @property
+    def launches(self) -> int:
+        return int(self.lib.ldc_launch_count(self._h))
+
+    @property
+    def last_kernel_ms(self) -> float:
+        return float(self.lib.ldc_last_kernel_ms(self._h))
+
+
+def fp64_peak_tflops(device: int = 0, which: str = "dmma") -> float:
+    """Live register-resident FP64 ceiling of the device: 'dmma', 'dfma' or 'mixed'."""
+    lib = _lib.load()
+    out = C.c_double()
+    _lib.check(lib.ldc_fp64_peak(device, {"dmma": 0, "dfma": 1, "mixed": 2}[which], C.byref(out)), "ldc_fp64_peak")
+    return out.value

@@ -1,0 +1,126 @@
+/*
+ * ldc_b200.h -- C ABI of the B200-native batched spectral lid-driven-cavity stepper.
+ *
+ * The reference (PN-CourseWork/02689-AdvancedNumericalAlgorithmP3) is pure Python and has no
+ * native boundary; this ABI is what a native binding for its spectral hot path binds to.  Each
+ * entry point names the reference code it replaces (paths relative to src/solvers/ of the
+ * reference).  All arrays are FP64, C-order.  Per cavity: u, v are (nx+1) x (ny+1) with x the slow
+ * axis (meshgrid indexing="ij", spectral/sg.py:108); p is the (nx-1) x (ny-1) inner grid
+ * (PN-PN-2, datastructures.py:282-353).  Batched arrays put the cavity index first.
+ *
+ * Conventions
+ *   - every function returns 0 (LDC_OK) or a positive error code; ldc_last_error() gives the text
+ *     of the last failure on the calling thread.  No C++ exception crosses the boundary.
+ *   - data pointers may be host or device pointers (detected with cudaPointerGetAttributes);
+ *     copies are enqueued on the handle's stream and host pointers are synchronised before return.
+ *   - the caller owns every buffer it passes; the handle owns the device state.
+ *   - one handle <-> one device + one stream + one polynomial order; a handle is not thread-safe,
+ *     distinct handles are independent.  There is no CPU fallback: every call needs a CUDA device.
+ */
+#ifndef LDC_B200_H
+#define LDC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ldc_handle ldc_t;
+
+enum {
+    LDC_OK = 0,
+    LDC_ERR_INVALID = 1,     /* bad argument */
+    LDC_ERR_CUDA = 2,        /* CUDA runtime failure (text in ldc_last_error) */
+    LDC_ERR_STATE = 3,       /* call order: operators / cases not set yet */
+    LDC_ERR_UNSUPPORTED = 4  /* requested kernel path cannot run this shape */
+};
+
+/* kernel path selection for ldc_step / ldc_solve */
+enum {
+    LDC_PATH_AUTO = 0,    /* resident DMMA kernel when the shape fits shared memory, else tiled */
+    LDC_PATH_TILED = 1,   /* state in global memory (L2), one launch per RK stage; any nx, ny */
+    LDC_PATH_RESIDENT = 2 /* state + operators resident in shared memory, FP64 DMMA, many steps per launch */
+};
+
+/* Library / build information: "ldc_b200 <version> sm_100a". */
+const char* ldc_version(void);
+const char* ldc_last_error(void);
+
+/* Allocate the device state of `batch` independent cavities of polynomial order (nx, ny).
+ * Replaces SpectralSolverFields.allocate (datastructures.py:282-353) / SpectralLevel
+ * (spectral/multigrid/fsg.py:262-354).  `cuda_stream` is a cudaStream_t (NULL = default stream). */
+int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_stream);
+void ldc_destroy(ldc_t* h);
+int ldc_set_path(ldc_t* h, int path);
+/* 0 when the resident DMMA path can run this handle's shape, else LDC_ERR_UNSUPPORTED. */
+int ldc_resident_supported(const ldc_t* h);
+
+/* 1-D operators shared by every cavity of the handle (host or device pointers, row-major):
+ *   Dx, Dxx : (nx+1) x (nx+1)   Dy, Dyy : (ny+1) x (ny+1)
+ *   Ix : (nx+1) x (nx-1)        Iy : (ny+1) x (ny-1)     inner -> full interpolation
+ * Replaces SGSolver._build_diff_matrices (spectral/sg.py:181-210) as the kernels' operand source;
+ * dx_min, dy_min are min(diff(nodes)) (spectral/sg.py:118-119). */
+int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const double* Dy, const double* Dyy,
+                      const double* Ix, const double* Iy, double dx_min, double dy_min);
+
+/* Per-cavity physics: Re, beta_squared, CFL, lid_velocity are [batch]; u_lid, v_lid are
+ * [batch][nx+1] lid profiles on the north boundary (spectral/operators/corner.py:80-112). */
+int ldc_set_cases(ldc_t* h, const double* Re, const double* beta2, const double* CFL, const double* lid_velocity,
+                  const double* u_lid, const double* v_lid);
+
+/* State transfer: u, v [batch][nx+1][ny+1]; p [batch][nx-1][ny-1].  NULL pointers are skipped. */
+int ldc_set_state(ldc_t* h, const double* u, const double* v, const double* p);
+int ldc_get_state(ldc_t* h, double* u, double* v, double* p);
+/* u = v = p = 0 then the lid column (spectral/sg.py:98, 250-253; multigrid/fsg.py:1141-1161). */
+int ldc_init_state(ldc_t* h);
+
+/* One residual evaluation of the current state on ALL nodes, exactly the reference formula
+ * (SGSolver._compute_residuals spectral/sg.py:278-346, MultigridSmoother._compute_residuals
+ * multigrid/fsg.py:857-910): Ru, Rv [batch][nx+1][ny+1], Rp [batch][nx-1][ny-1]; norms (may be
+ * NULL) receives [batch][3] = ||Ru||, ||Rv||, ||Rp|| (spectral/sg.py:463-473). */
+int ldc_residual(ldc_t* h, double* Ru, double* Rv, double* Rp, double* norms);
+
+/* n_steps RK4 pseudo-steps of every cavity, no convergence test (SGSolver.step spectral/sg.py:410-449
+ * with freeze_pressure=1: all four stages take grad(p^n); MultigridSmoother.step
+ * multigrid/fsg.py:956-995 with freeze_pressure=0).  rel (may be NULL) receives [batch][2] =
+ * (u_res, v_res) of the last step, ||phi^{n+1}-phi^n|| / (||phi^n|| + 1e-12). */
+int ldc_step(ldc_t* h, int64_t n_steps, int freeze_pressure, double* rel);
+
+/* Iterate every cavity until max(u_res, v_res) < tol[b] (after `warmup` unconditional iterations:
+ * 10 for base.solve base.py:283-286, 0 for solve_fsg multigrid/fsg.py:1174-1182), a non-finite
+ * residual (nan_exit=1, multigrid/fsg.py:1184-1202) or max_iter steps.  Outputs are [batch]:
+ * iters = steps taken, converged / diverged flags, rel_res = last max(u_res, v_res). */
+int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit,
+              int64_t* iters, int32_t* converged, int32_t* diverged, double* rel_res);
+
+/* Energy, enstrophy, palinstrophy with quadrature weights W[(nx+1)][(ny+1)]
+ * (spectral/sg.py:495-550); out is [batch][3]. */
+int ldc_diagnostics(ldc_t* h, const double* W, double* out);
+
+/* Coarse -> fine transfer of (u, v, p): U_f = Px U_c Py^T with dense 1-D maps
+ * Pxu (nfx+1)x(ncx+1), Pyu (nfy+1)x(ncy+1), Pxp (nfx-1)x(ncx-1), Pyp (nfy-1)x(ncy-1)
+ * (prolongate_solution multigrid/fsg.py:551-614).  bc_quirk=1 reproduces the reference's
+ * swapped-axes boundary re-enforcement (row 0 := 0, row -1 := lid_velocity, col 0 := 0, col -1 := 0)
+ * followed by initialize_lid (multigrid/fsg.py:950-954); bc_quirk=0 applies the plain wall + lid
+ * boundary conditions.  Both handles must share batch size, device and have their cases set. */
+int ldc_prolongate(ldc_t* coarse, ldc_t* fine, const double* Pxu, const double* Pyu, const double* Pxp,
+                   const double* Pyp, int bc_quirk);
+/* Fine -> coarse transfer U_c = Rx U_f Ry^T (restrict_solution multigrid/fsg.py:622-664; no caller in
+ * the reference's FSG driver) followed by the wall + lid boundary conditions on the coarse grid. */
+int ldc_restrict(ldc_t* fine, ldc_t* coarse, const double* Rxu, const double* Ryu, const double* Rxp,
+                 const double* Ryp);
+
+/* Kernel launches issued by this handle since creation (bench.py's gpu_launches claim) and device
+ * time in ms of the last ldc_step / ldc_solve call, measured with CUDA events on the handle's stream. */
+int64_t ldc_launch_count(const ldc_t* h);
+double ldc_last_kernel_ms(const ldc_t* h);
+
+/* FP64 ceilings of the device, measured live (roofline denominators): which = 0 register-resident
+ * DMMA (mma.sync m8n8k4 f64), 1 register-resident DFMA, 2 both pipes mixed.  TFLOP/s in *tflops. */
+int ldc_fp64_peak(int device, int which, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LDC_B200_H */

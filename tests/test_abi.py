@@ -1,0 +1,60 @@
+"""The C-ABI library builds for sm_100a, loads, and exports every symbol include/ldc_b200.h declares.
+No compute call is made (no GPU here)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+
+def header_functions():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "include", "ldc_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ldc_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    names = header_functions()
+    assert len(names) >= 18
+    lib = ctypes.CDLL(built_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/ldc_b200.h but not exported"
+
+
+def test_python_binding_covers_the_header(built_lib):
+    from ldc_b200 import _lib
+
+    assert sorted(_lib.SIGNATURES) == header_functions()
+    assert b"sm_100a" in _lib.load().ldc_version()
+
+
+def test_library_contains_sm100a_dmma_code(built_lib):
+    import shutil
+    import subprocess
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run([cuobjdump, "-sass", built_lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+    assert "DMMA.8x8x4" in out, "the resident kernel must issue FP64 tensor-core instructions"
+
+
+def test_no_cpu_fallback_without_a_device(built_lib):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(built_lib.LdcError, match="no CUDA device|CUDA"):
+        built_lib.BatchedSpectralLDC(8, batch=1)
+
+
+def test_product_never_imports_the_oracle():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "02689-advancednumericalalgorithmp3_b200")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(d, f)).read()
+                assert "oracle" not in src.replace("# oracle", ""), f"{f} mentions the oracle"
