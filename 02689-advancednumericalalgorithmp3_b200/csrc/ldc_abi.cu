@@ -418,9 +418,9 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     const bool resident = use_resident(h);
     if (h->path == LDC_PATH_RESIDENT && !resident)
         return fail(LDC_ERR_UNSUPPORTED, "resident path requested but the shape does not fit shared memory");
-    LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
     if (resident) {
         if ((rc = ensure_packed(h))) return rc;
+        LDC_CUDA(cudaEventRecord(h->ev0, h->stream));  // device time of the stepping kernels only
         ResParams P;
         P.ops = h->r_ops; P.square = h->square_ops ? 1 : 0;
         P.state = h->r_state; P.state_stride = h->r_state_stride;
@@ -442,6 +442,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         }
     } else {
         if ((rc = ensure_canonical(h))) return rc;
+        LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
         h->packed_valid = false;
         const long long chunk = 64;
         for (long long done = 0; done < max_iter; done += chunk) {

@@ -40,6 +40,8 @@ class BatchedSpectralLDC:
         self.lib = _lib.load()
         ny = nx if ny is None else ny
         self.nx, self.ny, self.B = int(nx), int(ny), int(batch)
+        if self.nx < 2 or self.ny < 2 or self.B < 1:
+            raise ValueError("need polynomial orders nx, ny >= 2 and batch >= 1")
         self.Lx, self.Ly, self.basis = float(Lx), float(Ly), basis
         self.device = int(device)
         self.level = ops.build_level(self.nx, self.ny, self.Lx, self.Ly, basis)

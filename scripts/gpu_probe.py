@@ -1,0 +1,38 @@
+"""GPU probe: FP64 ceilings + a first timing of the resident kernel at the bench shape."""
+import json
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, ".")
+sys.path.insert(0, "02689-advancednumericalalgorithmp3_b200")
+import __graft_entry__ as ge
+
+ge.build()
+import ldc_b200
+
+out = {}
+for w in ("dmma", "dfma", "mixed"):
+    out[f"fp64_{w}_tflops"] = ldc_b200.fp64_peak_tflops(0, w)
+print(out, flush=True)
+
+
+def fstep(N):
+    n, m = N + 1, N - 1
+    return 4 * (20 * n**3 + 2 * n * m * m + 2 * n * n * m)
+
+
+for N, B, K in ((64, 256, 400), (64, 148, 400), (64, 296, 400), (32, 1024, 1000), (30, 1, 2000), (16, 2048, 2000)):
+    Re = 400.0 * (1 + 0.05 * np.random.default_rng(0).uniform(-1, 1, B))
+    with ldc_b200.BatchedSpectralLDC(N, batch=B, path="resident") as s:
+        s.set_cases(Re).init_state()
+        s.step(50, want_rel=False)
+        t0 = time.time()
+        s.step(K, want_rel=False)
+        wall = time.time() - t0
+        ms = s.last_kernel_ms
+    rate = B * K / (ms * 1e-3)
+    out[f"N{N}_B{B}"] = dict(steps_per_s=rate, kernel_ms=ms, wall_ms=wall * 1e3, tflops=rate * fstep(N) / 1e12)
+    print(N, B, out[f"N{N}_B{B}"], flush=True)
+json.dump(out, open("gpurun_out/probe.json", "w"), indent=1)

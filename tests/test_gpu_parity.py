@@ -200,7 +200,7 @@ def test_resident_matches_tiled_at_bench_size(ldc, N):
 
 
 def test_error_paths(ldc):
-    with pytest.raises(ldc.LdcError):
+    with pytest.raises(ValueError):
         ldc.BatchedSpectralLDC(1, batch=1)
     with ldc.BatchedSpectralLDC(8, batch=1) as s:
         with pytest.raises(ldc.LdcError, match="ldc_set_cases"):
