@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- batched cavity pseudo-steps/sec at N=64 (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 5 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 5 --warmup 3
+    python bench.py --impl reference --steps 5 --warmup 3      # the CPU arm (oracle port on all host cores)
+
+Workload (BASELINE.json configs[2], SURVEY.md section 8d "Config 3"): Re = 400 (1 + 0.05 U(-1,1)), N = 64,
+256 cavities per GPU, corner_smoothing 0.15, CFL 1.5, beta^2 5, MultigridSmoother semantics (staged pressure),
+cold start (zeros + lid) advanced by the warm-up.  One bench "step" = PSEUDO pseudo-steps (full RK4 steps:
+4 residual evaluations + 4 stage updates + BCs + dt + convergence norms) of every cavity of the batch.
+One pseudo-step is 26.163 MFLOP by the reference's own GEMM count.
+
+value  : cavity pseudo-steps/s, whole job, state resident in HBM when the timed region starts, CUDA events
+e2e    : the same through the C ABI with HOST buffers: ldc_set_state (pinned host -> device), ldc_step,
+         ldc_get_state (device -> pinned host), all inside the timed region
+roofline: FP64 tensor (DMMA) bound; the denominator is measured live (ldc_fp64_peak) because
+         MEASURED_PEAKS.json carries no FP64 figure
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG_DIR = os.path.join(ROOT, "02689-advancednumericalalgorithmp3_b200")
+for _p in (ROOT, PKG_DIR):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "batched cavity pseudo-steps/sec at N=64"
+UNIT = "cavity-pseudo-steps/s"
+
+
+def f_step(N: int) -> float:
+    """Algorithmic FP64 flops of one pseudo-step: the reference's 12 GEMMs x 4 stages."""
+    n, m = N + 1, N - 1
+    return 4.0 * (20 * n**3 + 2 * n * m * m + 2 * n * n * m)
+
+
+def workload_config(args, world):
+    return {
+        "workload": f"Re=400 N={args.N} batch of {args.batch} cavities per GPU (Re jitter +-5%, seed 0), "
+                    "corner_smoothing=0.15 CFL=1.5 beta2=5, staged-pressure RK4 (MultigridSmoother.step semantics)",
+        "N": args.N, "cavities_per_gpu": args.batch, "cavities_total": args.batch * world,
+        "pseudo_steps_per_bench_step": args.pseudo, "flop_per_pseudo_step": f_step(args.N),
+        "l2": "flushed between timed steps (256 MiB write); state is shared-memory resident inside a launch",
+        "parallelism": f"cavity-sharded x{world}, no data-path collective",
+    }
+
+
+def reynolds(args, world):
+    import numpy as np
+
+    rng = np.random.default_rng(0)
+    # the first 256 values are exactly SURVEY 8d config 3; further ranks continue the same stream
+    return 400.0 * (1.0 + 0.05 * rng.uniform(-1.0, 1.0, args.batch * world))
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port, one single-threaded process per host core, each stepping its own cavity
+# ----------------------------------------------------------------------------------------------------------
+def cpu_worker(args):
+    """Child process: `windows` fixed-duration windows of oracle rk4_step calls; prints one JSON line."""
+    import numpy as np
+
+    from oracle import ldc_oracle as orc
+
+    lv = orc.build_level(args.N)
+    Re = float(reynolds(args, 1)[args.worker_index % args.batch])
+    case = orc.Case(Re=Re)
+    ul, vl = orc.lid_profile(lv.x, "smoothing", 0.15, 1.0, 1.0)
+    u, v, p = orc.initial_state(lv, ul, vl)
+    for _ in range(5):
+        orc.rk4_step(lv, u, v, p, case, ul, vl, False)
+    out = []
+    for _ in range(args.windows):
+        n, t0 = 0, time.perf_counter()
+        while True:
+            orc.rk4_step(lv, u, v, p, case, ul, vl, False)
+            n += 1
+            el = time.perf_counter() - t0
+            if el >= args.seconds:
+                break
+        out.append((n, el))
+    assert np.isfinite(u).all()
+    print(json.dumps(out), flush=True)
+
+
+def run_cpu_windows(args, windows: int, seconds: float):
+    """Spawn one worker per usable core; returns (cores, [aggregate cavity-steps/s per window])."""
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    if args.cpu_cores:
+        cores = min(cores, args.cpu_cores)
+    env = dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", "--worker-index", str(i),
+                               "--windows", str(windows), "--seconds", str(seconds), "--N", str(args.N),
+                               "--batch", str(args.batch)], stdout=subprocess.PIPE, env=env, text=True)
+             for i in range(cores)]
+    per = []
+    for pr in procs:
+        so, _ = pr.communicate()
+        if pr.returncode != 0:
+            raise RuntimeError("cpu worker failed")
+        per.append(json.loads(so.strip().splitlines()[-1]))
+    rates = []
+    for w in range(windows):
+        steps = sum(p[w][0] for p in per)
+        el = max(p[w][1] for p in per)
+        rates.append(steps / el)
+    return cores, rates
+
+
+def reference_arm(args):
+    """--impl reference: the reference's CPU algorithm (oracle port; the reference itself is Python under
+    /root/reference and does not exist on the GPU box) on every host core, same metric/config/unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    windows = args.steps + args.warmup
+    seconds = max(0.5, min(4.0, 150.0 / max(windows, 1)))
+    cores, rates = run_cpu_windows(args, windows, seconds)
+    timed = rates[args.warmup:]
+    value = sum(timed) / len(timed)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * args.pseudo * args.batch / value, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{cores} single-threaded processes x {seconds:.1f} s windows of oracle rk4_step at "
+                                   f"N={args.N} (one cavity each; the reference's joblib-style case parallelism)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------------
+# clocks
+# ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(device_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.rows.append((time.perf_counter(), ln.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, ln in self.rows:
+            if t0 is not None and not (t0 <= ts <= t1 + 0.2):
+                continue
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as ge
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; ldc_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+
+    # CPU baseline first (rank 0, single-GPU run only), before the GPU is busy and before CUDA is initialised here
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores, rates = run_cpu_windows(args, 2, 6.0)
+        cpu_baseline = {"value": rates[1], "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"{cores} single-threaded processes x 6 s (after a 6 s warm-up window) of oracle rk4_step "
+                                  f"at N={args.N}, one cavity each"}
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+    import ldc_b200
+
+    B, N, P = args.batch, args.N, args.pseudo
+    Re = reynolds(args, world)[rank * B:(rank + 1) * B]
+    s = ldc_b200.BatchedSpectralLDC(N, batch=B, device=local, path=args.path)
+    s.set_cases(Re, corner_smoothing=0.15).init_state()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # FP64 ceilings, measured live on this device
+    peaks = {k: ldc_b200.fp64_peak_tflops(local, k) for k in ("dmma", "dfma")}
+
+    # ---- device-resident throughput ("value") ----
+    for _ in range(args.warmup):
+        s.step(P, want_rel=False)
+    barrier()
+    clocks = ClockSampler(local)
+    time.sleep(0.3)
+    l0 = s.launches
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kms = []
+    barrier()
+    t0 = time.perf_counter()
+    for a, b in ev:
+        flush.fill_(1)            # evict L2 between timed steps (outside the event pair)
+        a.record()
+        s.step(P, want_rel=False)
+        b.record()
+        kms.append(None)
+        torch.cuda.synchronize()
+        kms[-1] = s.last_kernel_ms
+    barrier()
+    t1 = time.perf_counter()
+    launches = s.launches - l0
+    clk = clocks.stop(t0, t1)
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
+    kern_ms = torch.tensor([sum(kms)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kern_ms, op=dist.ReduceOp.MAX)
+    total_ms, kern_ms = float(total_ms.item()), float(kern_ms.item())
+    value = world * B * P * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers ("e2e") ----
+    pin = lambda shape: torch.empty(shape, dtype=torch.float64, pin_memory=True).numpy()
+    hu, hv, hp = pin(s.shape_full), pin(s.shape_full), pin(s.shape_inner)
+    s.get_state((hu, hv, hp))
+    hrel = np.empty((B, 2))
+    for _ in range(2):
+        s.set_state(hu, hv, hp)
+        s.step(P, want_rel=False)
+        s.get_state((hu, hv, hp))
+    barrier()
+    te0 = time.perf_counter()
+    for _ in range(args.steps):
+        s.set_state(hu, hv, hp)
+        hrel = s.step(P, want_rel=True)
+        s.get_state((hu, hv, hp))
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - te0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * P * args.steps / float(e2e_s.item())
+    h2d = hu.nbytes + hv.nbytes + hp.nbytes
+    d2h = h2d + hrel.nbytes
+
+    # ---- final gather (the only collective of the path): per-cavity residuals to every rank ----
+    rel_local = torch.from_numpy(np.ascontiguousarray(hrel.max(axis=1))).cuda()
+    if world > 1:
+        rel_all = torch.empty(world * B, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(rel_all, rel_local)
+    else:
+        rel_all = rel_local
+    finite = bool(torch.isfinite(rel_all).all().item())
+
+    # ---- time to tolerance, Re = 1000 (BASELINE config 2: FSG N=30 [15,30], cs=0.15) ----
+    tt = None
+    if rank == 0 and not args.no_time_to_tol:
+        torch.cuda.synchronize()
+        w0 = time.perf_counter()
+        r = ldc_b200.solve_fsg_batched(30, 1000.0, 1e-6, 500_000, corner_smoothing=0.15, device=local)
+        tt = {"config": "FSG Re=1000 N=30 levels [15,30] cs=0.15 tol=1e-6, single cavity", "wall_s": time.perf_counter() - w0,
+              "kernel_s": r.kernel_ms * 1e-3, "iterations": int(r.iterations[0]), "converged": bool(r.converged[0]),
+              "reference_iterations": 123483}
+
+    if rank == 0:
+        flop_launch = B * P * f_step(N)
+        achieved = flop_launch / (kern_ms / args.steps * 1e-3) / 1e12
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "tensor", "kernel": "k_resident_rk4 (FP64 DMMA, mma.sync m8n8k4)", "achieved": achieved,
+                         "peak": peaks["dmma"], "unit": "TFLOP/s", "frac": achieved / peaks["dmma"], "traffic": traffic,
+                         "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 on this GPU (ldc_fp64_peak); "
+                                        "MEASURED_PEAKS.json has no FP64 figure",
+                         "dfma_peak": peaks["dfma"], "flop_per_launch": flop_launch,
+                         "kernel_ms_per_launch": kern_ms / args.steps},
+            "all_finite": finite,
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        if tt is not None:
+            line["time_to_tol"] = tt
+        print(json.dumps(line), flush=True)
+    s.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--N", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=256, help="cavities per GPU")
+    ap.add_argument("--pseudo", type=int, default=200, help="RK4 pseudo-steps per bench step")
+    ap.add_argument("--path", default="auto", choices=["auto", "resident", "tiled"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-time-to-tol", action="store_true")
+    ap.add_argument("--cpu-cores", type=int, default=0)
+    # internal: CPU worker processes
+    ap.add_argument("--cpu-worker", action="store_true")
+    ap.add_argument("--worker-index", type=int, default=0)
+    ap.add_argument("--windows", type=int, default=1)
+    ap.add_argument("--seconds", type=float, default=5.0)
+    args = ap.parse_args()
+    if args.warmup < 3 and not args.cpu_worker:
+        args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.cpu_worker:
+        return cpu_worker(args)
+    if args.impl == "reference":
+        return reference_arm(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # convenience: re-launch under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main() or 0)
