@@ -90,7 +90,11 @@ struct ldc_handle {
     size_t r_state_stride = 0;    // doubles per cavity
     bool packed_valid = false;    // r_state holds the current state
     bool canon_valid = true;      // u, v, p hold the current state
-    int* ticket = nullptr;        // work-queue counters of the resident kernel
+    int* q_data = nullptr;        // work queue of the resident kernel (resident.cuh: CavityQueue)
+    unsigned* q_seq = nullptr;
+    unsigned* q_ctl = nullptr;
+    int num_sms = 0;
+    int res_slots = 0;            // CTAs of the resident kernel the chip holds at once
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_ms = 0.0;

@@ -196,7 +196,10 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
         h->r_state_stride = res_state_stride(h->MP);
         A_(r_ops, res_ops_size(h->MP, false));
         A_(r_state, B * h->r_state_stride);
+        A_(q_data, B); A_(q_seq, B); A_(q_ctl, 4);
     }
+    if (rc == LDC_OK && cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
+        rc = fail(LDC_ERR_CUDA, "ldc_create: cannot query the SM count");
 #undef A_
     if (rc == LDC_OK && cudaMallocHost((void**)&h->h_pinned, sizeof(int)) != cudaSuccess)
         rc = fail(LDC_ERR_CUDA, "ldc_create: cudaMallocHost failed");
@@ -221,7 +224,9 @@ void ldc_destroy(ldc_t* h) {
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
-    if (h->ticket) cudaFree(h->ticket);
+    if (h->q_data) cudaFree(h->q_data);
+    if (h->q_seq) cudaFree(h->q_seq);
+    if (h->q_ctl) cudaFree(h->q_ctl);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -389,13 +394,37 @@ __global__ void k_export_status(const CavityStatus* __restrict__ st, int B, long
     uv[2 * b + 1] = s.v_res;
 }
 
+// CTAs of the resident kernel that are resident on the whole chip at once for this handle's shape.
+template <int MP, int WM, int WN>
+static int resident_slots_t(ldc_handle* h) {
+    using C = ResCfg<MP, WM, WN>;
+    const size_t bytes = C::smem_doubles(h->square_ops) * sizeof(double);
+    LDC_CUDA(cudaFuncSetAttribute(k_resident_rk4<MP, WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int per_sm = 0;
+    LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resident_rk4<MP, WM, WN>, C::THREADS, bytes));
+    h->res_slots = std::max(1, per_sm) * h->num_sms;
+    return LDC_OK;
+}
+
+static int resident_slots(ldc_handle* h) {
+    switch (h->MP) {
+        case 16: return resident_slots_t<16, 2, 2>(h);
+        case 32: return resident_slots_t<32, 2, 2>(h);
+        case 48: return resident_slots_t<48, 2, 3>(h);
+        case 64: return resident_slots_t<64, 2, 4>(h);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "resident path: unsupported padded size");
+}
+
 template <int MP, int WM, int WN>
 static int launch_resident_t(ldc_handle* h, const ResParams& P) {
     using C = ResCfg<MP, WM, WN>;
     const size_t bytes = C::smem_doubles(h->square_ops) * sizeof(double);
     LDC_CUDA(cudaFuncSetAttribute(k_resident_rk4<MP, WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    k_resident_rk4<MP, WM, WN><<<h->B, C::THREADS, bytes, h->stream>>>(P);
-    h->launches += 1;
+    // persistent CTAs, as many as fit the chip at once, fed by the cavity queue
+    k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
+    k_resident_rk4<MP, WM, WN><<<std::min(h->B, h->res_slots), C::THREADS, bytes, h->stream>>>(P);
+    h->launches += 2;
     LDC_CUDA(cudaGetLastError());
     return LDC_OK;
 }
@@ -429,10 +458,21 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         P.dx_min = h->dx_min; P.dy_min = h->dy_min;
         P.status = h->status; P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.freeze = freeze;
         P.max_iter = max_iter;
+        P.q_data = h->q_data; P.q_seq = h->q_seq; P.q_ctl = h->q_ctl; P.B = h->B;
+        if ((rc = resident_slots(h))) return rc;
+        // steps per launch (the host looks at the active count between launches)
         const long long chunk = h->MP >= 64 ? 1024 : (h->MP >= 48 ? 2048 : (h->MP >= 32 ? 4096 : 16384));
         h->canon_valid = false;
         for (long long done = 0; done < max_iter; done += chunk) {
-            P.n_steps = std::min(chunk, max_iter - done);
+            const long long L = std::min(chunk, max_iter - done);
+            P.launch_end = done + L;
+            // steps per queue visit: the whole launch when every cavity has its own CTA slot, else ~64 visits per slot so
+            // that the tail of the launch (slots idling while the last visits finish) stays near 1.5 %
+            P.chunk = L;
+            if (h->B > h->res_slots) {
+                const long long c = (L * h->B + 64LL * h->res_slots - 1) / (64LL * h->res_slots);
+                P.chunk = std::min(L, std::max(4LL, c));
+            }
             if ((rc = launch_resident(h, P))) return rc;
             if (done + chunk < max_iter) {
                 int na = 0;

@@ -145,9 +145,109 @@ struct ResParams {
     CavityStatus* status;
     const double* tol;
     int warmup, nan_exit, freeze;
-    long long max_iter;   // absolute cap on status.iters
-    long long n_steps;    // steps per launch (chunk)
+    long long max_iter;    // absolute cap on status.iters for the whole solve
+    long long launch_end;  // a cavity leaves this launch once status.iters reaches launch_end
+    long long chunk;       // steps a CTA runs on one cavity before it hands the cavity back to the queue
+    // work queue of cavities (bounded MPMC ring, one slot per cavity): see CavityQueue
+    int* q_data;           // [B] cavity index
+    unsigned* q_seq;       // [B] slot sequence numbers
+    unsigned* q_ctl;       // head, tail, remaining
+    int B;
 };
+
+// Coherent (L2) access to a cavity's status: cavities migrate between SMs, so L1 must be bypassed.
+__device__ __forceinline__ CavityStatus load_status(const CavityStatus* p) {
+    CavityStatus s;
+    s.iters = __ldcg(&p->iters);
+    s.active = __ldcg(&p->active);
+    s.converged = __ldcg(&p->converged);
+    s.diverged = __ldcg(&p->diverged);
+    s.pad = 0;
+    s.u_res = __ldcg(&p->u_res);
+    s.v_res = __ldcg(&p->v_res);
+    s.umax = __ldcg(&p->umax);
+    s.vmax = __ldcg(&p->vmax);
+    return s;
+}
+__device__ __forceinline__ void store_status(CavityStatus* p, const CavityStatus& s) {
+    __stcg(&p->iters, s.iters);
+    __stcg(&p->active, s.active);
+    __stcg(&p->converged, s.converged);
+    __stcg(&p->diverged, s.diverged);
+    __stcg(&p->u_res, s.u_res);
+    __stcg(&p->v_res, s.v_res);
+    __stcg(&p->umax, s.umax);
+    __stcg(&p->vmax, s.vmax);
+}
+
+// Work queue of the resident kernel.  A launch runs min(B, #SM) persistent CTAs; each pops a cavity, advances it
+// by `chunk` RK4 steps with the state in shared memory, writes it back to L2 and, if the cavity still has steps
+// to do in this launch, pushes it to the tail.  B > #SM therefore costs no wave quantisation: every SM stays
+// busy until the whole batch is done, and a cavity that converges early frees its SM for the others.
+// Protocol: bounded ring with per-slot sequence numbers (slot free for ticket t when seq == t, full when
+// seq == t + 1); every CTA of the launch is co-resident, so the spins cannot deadlock.
+struct CavityQueue {
+    __device__ static int pop(const ResParams& P) {
+        const unsigned h = atomicAdd(&P.q_ctl[0], 1u);
+        const unsigned slot = h % (unsigned)P.B;
+        volatile unsigned* seq = P.q_seq + slot;
+        volatile unsigned* remaining = P.q_ctl + 2;
+        while (*seq != h + 1u) {
+            if (*remaining == 0u) return -1;
+            __nanosleep(200);
+        }
+        __threadfence();
+        const int b = *(volatile int*)(P.q_data + slot);
+        __threadfence();
+        *seq = h + (unsigned)P.B;
+        return b;
+    }
+    __device__ static void push(const ResParams& P, int b) {
+        const unsigned t = atomicAdd(&P.q_ctl[1], 1u);
+        const unsigned slot = t % (unsigned)P.B;
+        volatile unsigned* seq = P.q_seq + slot;
+        while (*seq != t) __nanosleep(100);
+        *(volatile int*)(P.q_data + slot) = b;
+        __threadfence();
+        *seq = t + 1u;
+    }
+    __device__ static void retire(const ResParams& P) { atomicSub(&P.q_ctl[2], 1u); }
+};
+
+// Fill the queue with the cavities that still have work in this launch, in index order (one block).
+__global__ void __launch_bounds__(1024) k_queue_init(const CavityStatus* __restrict__ status, int B, long long launch_end,
+                                                     int* __restrict__ q_data, unsigned* __restrict__ q_seq,
+                                                     unsigned* __restrict__ q_ctl) {
+    __shared__ int warp_cnt[32];
+    __shared__ int base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) base = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < B; b0 += blockDim.x) {
+        const int b = b0 + tid;
+        const bool live = b < B && status[b].active && status[b].iters < launch_end;
+        const unsigned bal = __ballot_sync(0xffffffffu, live);
+        if (lane == 0) warp_cnt[warp] = __popc(bal);
+        __syncthreads();
+        int off = base;
+        for (int w = 0; w < warp; ++w) off += warp_cnt[w];
+        if (live) q_data[off + __popc(bal & ((1u << lane) - 1u))] = b;
+        __syncthreads();
+        if (tid == 0) {
+            int tot = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += warp_cnt[w];
+            base += tot;
+        }
+        __syncthreads();
+    }
+    const int n = base;
+    for (int i = tid; i < B; i += blockDim.x) q_seq[i] = i < n ? (unsigned)i + 1u : (unsigned)i;
+    if (tid == 0) {
+        q_ctl[0] = 0u;
+        q_ctl[1] = (unsigned)n;
+        q_ctl[2] = (unsigned)n;
+    }
+}
 
 template <int MP, int WM, int WN>
 struct ResCfg {

@@ -5,15 +5,17 @@
 namespace ldc {
 
 // One velocity field F (u or v) through its five contractions, as 8x8x4 DMMA tiles:
-//   a1 = Dx F      a2 = F Dy^T      aL = Dxx (nu F) + (nu F) Dyy^T + [ Gx (-p)  |  (-p) Gy^T ]
+//   a1 = Dx F      a2 = F Dy^T      aL = (nu Dxx) F + F (nu Dyy)^T + [ (-Gx) p  |  p (-Gy)^T ]
 // aL collects every term of the momentum residual that is linear in the fields; P_LEFT picks the
-// pressure-gradient component (d/dx for the u equation, d/dy for the v equation).
+// pressure-gradient component (d/dx for the u equation, d/dy for the v equation).  The shared-memory copies
+// of Dxx, Dyy are pre-scaled by the cavity's nu = 1/Re and those of Gx, Gy are negated when they are loaded,
+// so the k loop is LDS + DMMA only.
 // Fragment layout of mma.m8n8k4.f64 (g = lane/4, t = lane%4): A[g][t], B[t][g], C[g][2t], C[g][2t+1].
 template <int MT, int NT, int LD, bool P_LEFT>
 __device__ __forceinline__ void field_pass(const double* __restrict__ sDa, const double* __restrict__ sDDa,
                                            const double* __restrict__ sDb, const double* __restrict__ sDDb,
                                            const double* __restrict__ sG, const double* __restrict__ sF,
-                                           const double* __restrict__ sP, double nu, int K4, int row0, int col0, int g,
+                                           const double* __restrict__ sP, int K4, int row0, int col0, int g,
                                            int t, double (&a1)[MT][NT][2], double (&a2)[MT][NT][2],
                                            double (&aL)[MT][NT][2]) {
     const int arow = (row0 + g) * LD + t;   // A fragment: element [row0 + 8 mt + g][k0 + t]
@@ -44,11 +46,7 @@ __device__ __forceinline__ void field_pass(const double* __restrict__ sDa, const
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) dmma884(a2[mt][nt][0], a2[mt][nt][1], fa[mt], d[nt]);
         }
-#pragma unroll
-        for (int mt = 0; mt < MT; ++mt) fa[mt] *= nu;
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) fb[nt] *= nu;
-        {   // aL += Dxx (nu F)
+        {   // aL += (nu Dxx) F
             double d[MT];
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt) d[mt] = sDDa[arow + mt * 8 * LD + k0];
@@ -57,7 +55,7 @@ __device__ __forceinline__ void field_pass(const double* __restrict__ sDa, const
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) dmma884(aL[mt][nt][0], aL[mt][nt][1], d[mt], fb[nt]);
         }
-        {   // aL += (nu F) Dyy^T
+        {   // aL += F (nu Dyy)^T
             double d[NT];
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) d[nt] = sDDb[brow + nt * 8 * LD + k0];
@@ -66,20 +64,20 @@ __device__ __forceinline__ void field_pass(const double* __restrict__ sDa, const
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) dmma884(aL[mt][nt][0], aL[mt][nt][1], fa[mt], d[nt]);
         }
-        if (P_LEFT) {   // aL += Gx (-p)
+        if (P_LEFT) {   // aL += (-Gx) p
             double d[MT], q[NT];
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt) d[mt] = sG[arow + mt * 8 * LD + k0];
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) q[nt] = -sP[bfld + k0 * LD + nt * 8];
+            for (int nt = 0; nt < NT; ++nt) q[nt] = sP[bfld + k0 * LD + nt * 8];
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) dmma884(aL[mt][nt][0], aL[mt][nt][1], d[mt], q[nt]);
-        } else {        // aL += (-p) Gy^T
+        } else {        // aL += p (-Gy)^T
             double d[NT], q[MT];
 #pragma unroll
-            for (int mt = 0; mt < MT; ++mt) q[mt] = -sP[arow + mt * 8 * LD + k0];
+            for (int mt = 0; mt < MT; ++mt) q[mt] = sP[arow + mt * 8 * LD + k0];
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) d[nt] = sG[brow + nt * 8 * LD + k0];
 #pragma unroll
