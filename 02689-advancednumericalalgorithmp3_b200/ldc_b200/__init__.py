@@ -7,7 +7,8 @@ from . import operators
 from ._lib import LIB_PATH, LdcError, load
 from .batched import BatchedSpectralLDC, SolveResult, fp64_peak_tflops
 from .fsg import FSGResult, solve_fsg_batched, solve_sg_batched
+from .solvers import FSGSolver, SGSolver
 
 __all__ = ["operators", "BatchedSpectralLDC", "SolveResult", "fp64_peak_tflops", "solve_fsg_batched",
-           "solve_sg_batched", "FSGResult", "LdcError", "LIB_PATH", "load"]
+           "solve_sg_batched", "FSGResult", "SGSolver", "FSGSolver", "LdcError", "LIB_PATH", "load"]
 __version__ = "0.1.0"

@@ -161,6 +161,8 @@ class LevelOperators:
     dx_min: float
     dy_min: float
     W: np.ndarray     # (nx+1, ny+1) tensor-product quadrature weights (spectral/sg.py:479-493)
+    wx: np.ndarray = None   # 1-D quadrature weights
+    wy: np.ndarray = None
 
     @property
     def shape_full(self):
@@ -196,7 +198,7 @@ def build_level(nx: int, ny: int, Lx: float = 1.0, Ly: float = 1.0, basis: str =
         y, Dy, Dyy, Iy, wy = _one_direction(ny, Ly, basis)
     return LevelOperators(nx=nx, ny=ny, Lx=Lx, Ly=Ly, basis=basis, x=x, y=y, Dx=Dx, Dy=Dy, Dxx=Dxx, Dyy=Dyy, Ix=Ix,
                           Iy=Iy, dx_min=float(np.min(np.diff(x))), dy_min=float(np.min(np.diff(y))),
-                          W=np.outer(wx, wy))
+                          W=np.outer(wx, wy), wx=wx, wy=wy)
 
 
 def hierarchy_orders(n_fine: int, n_levels: int, coarsest_n: int = 12):

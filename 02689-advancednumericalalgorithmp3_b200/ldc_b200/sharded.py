@@ -1,0 +1,121 @@
+"""Sweeps of independent cavities sharded over the GPUs of one node.
+
+Cavities never talk to each other, so each rank solves a contiguous block of the batch on its own GPU with
+no collective on the stepping path.  `torch.distributed` (NCCL over NVLink on the GPU box, gloo in the CPU
+tests) is used once, at the end: an all-gather of the per-cavity results (iteration counts, flags, residuals)
+and a gather of the fields.  One process per GPU, launched with torchrun.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from .fsg import FSGResult, solve_fsg_batched, solve_sg_batched
+
+
+def shard_bounds(n_cases: int, world: int):
+    """Contiguous blocks [lo, hi) per rank; the first n_cases % world ranks get one extra cavity."""
+    base, extra = divmod(int(n_cases), int(world))
+    bounds, lo = [], 0
+    for r in range(world):
+        hi = lo + base + (1 if r < extra else 0)
+        bounds.append((lo, hi))
+        lo = hi
+    return bounds
+
+
+@dataclass
+class SweepResult:
+    iterations: np.ndarray   # int64 [B]
+    converged: np.ndarray    # bool [B]
+    diverged: np.ndarray     # bool [B]
+    rel_residual: np.ndarray  # float64 [B]
+    u: np.ndarray | None     # [B, n, n] on the ranks that asked for fields, else None
+    v: np.ndarray | None
+    p: np.ndarray | None
+    kernel_ms: float         # max over ranks
+    bounds: list
+
+
+def _dist():
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return None
+    return dist
+
+
+def _comm_device():
+    import torch
+
+    dist = _dist()
+    if dist is not None and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def _allgather_blocks(local: np.ndarray, counts, dtype):
+    """All-gather of per-rank blocks with different leading sizes (padded to the largest block)."""
+    import torch
+
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1:
+        return np.ascontiguousarray(local)
+    dev = _comm_device()
+    world, pad = dist.get_world_size(), max(counts)
+    tail = tuple(local.shape[1:])
+    buf = torch.zeros((pad,) + tail, dtype=dtype, device=dev)
+    if local.shape[0]:
+        buf[:local.shape[0]] = torch.from_numpy(np.ascontiguousarray(local)).to(dev)
+    out = torch.empty((world * pad,) + tail, dtype=dtype, device=dev)
+    dist.all_gather_into_tensor(out, buf)
+    out = out.cpu().numpy().reshape((world, pad) + tail)
+    return np.concatenate([out[r, :counts[r]] for r in range(world)], axis=0)
+
+
+def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fsg", fields: str = "rank0",
+                local_solver=None, device=None, **solver_kw) -> SweepResult:
+    """Solve B = len(Re) cavities (per-cavity Re and corner_smoothing; everything in solver_kw is shared),
+    sharded over the ranks of the initialised process group (or on this process alone if there is none).
+
+    kind   : "fsg" (solve_fsg_batched) or "sg" (solve_sg_batched)
+    fields : "rank0" gathers u, v, p on rank 0 only, "all" on every rank, "none" skips the field gather
+    local_solver : override of the per-rank solver (tests); signature of solve_fsg_batched
+    """
+    import torch
+
+    Re = np.atleast_1d(np.asarray(Re, dtype=np.float64))
+    cs = np.broadcast_to(np.asarray(corner_smoothing, dtype=np.float64), Re.shape).copy()
+    tol = np.broadcast_to(np.asarray(tolerance, dtype=np.float64), Re.shape).copy()
+    dist = _dist()
+    rank = dist.get_rank() if dist else 0
+    world = dist.get_world_size() if dist else 1
+    bounds = shard_bounds(Re.size, world)
+    lo, hi = bounds[rank]
+    counts = [b - a for a, b in bounds]
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    fn = local_solver or (solve_fsg_batched if kind == "fsg" else solve_sg_batched)
+    n1 = N + 1
+    if hi > lo:
+        r: FSGResult = fn(N, Re[lo:hi], tol[lo:hi], max_iter, corner_smoothing=cs[lo:hi], device=device, **solver_kw)
+    else:  # more ranks than cavities
+        z = np.zeros
+        r = FSGResult(z((0, n1, n1)), z((0, n1, n1)), z((0, N - 1, N - 1)), z(0, dtype=np.int64), z(0, dtype=bool),
+                      z(0, dtype=bool), z(0))
+    scal = np.stack([r.iterations.astype(np.float64), r.converged.astype(np.float64), r.diverged.astype(np.float64),
+                     r.rel_residual], axis=1) if hi > lo else np.zeros((0, 4))
+    scal = _allgather_blocks(scal, counts, torch.float64)
+    kms = np.array([[r.kernel_ms]])
+    kms = _allgather_blocks(kms, [1] * world, torch.float64).max()
+    u = v = p = None
+    if fields != "none":
+        # NCCL has no variable-size gather: all-gather the padded blocks, keep them where asked
+        gu = _allgather_blocks(r.u, counts, torch.float64)
+        gv = _allgather_blocks(r.v, counts, torch.float64)
+        gp = _allgather_blocks(r.p, counts, torch.float64)
+        if fields == "all" or rank == 0:
+            u, v, p = gu, gv, gp
+    return SweepResult(np.rint(scal[:, 0]).astype(np.int64), scal[:, 1] > 0.5, scal[:, 2] > 0.5, scal[:, 3], u, v, p,
+                       float(kms), bounds)

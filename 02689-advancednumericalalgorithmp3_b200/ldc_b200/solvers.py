@@ -1,0 +1,208 @@
+"""Drop-in solver classes for `solver=spectral/sg` and `solver=spectral/fsg`.
+
+Same class names, constructor keywords (= the YAML keys of conf/solver/spectral/{sg,fsg}.yaml), public
+attributes and error behaviour as the reference's `solvers.spectral.sg.SGSolver` (src/solvers/spectral/sg.py:29-101)
+and `solvers.spectral.fsg.FSGSolver` (src/solvers/spectral/fsg.py:19-129), so `main.py` (run_solver,
+main.py:75-120) can instantiate them through Hydra's `_target_` unchanged.  The numerics of `solve()` run in
+the CUDA library through the C ABI (one cavity = a batch of one); nothing here falls back to the CPU.
+
+Beyond the reference surface, both classes accept `device=` (CUDA device index, default 0) -- optional, so the
+reference's YAML files stay valid.
+"""
+from __future__ import annotations
+
+import logging
+import time
+
+import numpy as np
+
+from . import operators as ops
+from .batched import BatchedSpectralLDC
+from .datastructures import Fields, Metrics, SolverArrays, SpectralParameters, TimeSeries
+from .fsg import solve_fsg_batched
+from .postprocess import streamfunction_vortex_metrics
+
+log = logging.getLogger(__name__)
+
+_TRANSFER = {"prolongation": ("fft", "polynomial"), "restriction": ("fft", "injection")}
+
+
+class SGSolver:
+    """Single-grid pseudospectral artificial-compressibility solver (reference: spectral/sg.py:29-449)."""
+
+    Parameters = SpectralParameters
+
+    def __init__(self, params=None, device: int = 0, **kwargs):
+        if params is None:
+            params = self.Parameters(**kwargs)  # unknown key -> TypeError, as in the reference (base.py:47-52)
+        self.params = params
+        self.device = int(device)
+        self.metrics = Metrics()
+        self.time_series = None
+        basis = str(params.basis_type).lower()
+        if basis not in ops.BASES:
+            raise ValueError(f"Unknown basis_type: {params.basis_type}. Use 'legendre' or 'chebyshev'")
+        self.basis_type = basis
+        # validates the corner method exactly where the reference does (corner.py:219-223)
+        lv = ops.build_level(params.nx, params.ny, params.Lx, params.Ly, basis)
+        self.level = lv
+        ops.lid_velocity_profile(lv.x, params.corner_treatment, params.corner_smoothing, params.lid_velocity, params.Lx)
+
+        # grids and operators under the reference's attribute names (sg.py:103-119, 181-210, 479-493)
+        self.x_full, self.y_full = np.meshgrid(lv.x, lv.y, indexing="ij")
+        self.x_inner, self.y_inner = lv.x[1:-1], lv.y[1:-1]
+        self.x_reduced, self.y_reduced = np.meshgrid(self.x_inner, self.y_inner, indexing="ij")
+        self.dx_min, self.dy_min = lv.dx_min, lv.dy_min
+        self.Dx_1d, self.Dy_1d, self.Dxx_1d, self.Dyy_1d = lv.Dx, lv.Dy, lv.Dxx, lv.Dyy
+        self.Interp_x, self.Interp_y = lv.Ix, lv.Iy
+        self.w_x, self.w_y, self.W_2d = lv.wx, lv.wy, lv.W
+        self.shape_full = (params.nx + 1, params.ny + 1)
+        self.shape_inner = (params.nx - 1, params.ny - 1)
+        self.arrays = SolverArrays.allocate(self.shape_full[0] * self.shape_full[1],
+                                            self.shape_inner[0] * self.shape_inner[1])
+        self.fields = Fields(u=np.zeros(self.x_full.size), v=np.zeros(self.x_full.size), p=np.zeros(self.x_full.size),
+                             x=self.x_full.ravel().copy(), y=self.y_full.ravel().copy())
+        self.u_2d = self.arrays.u.reshape(self.shape_full)
+        self.v_2d = self.arrays.v.reshape(self.shape_full)
+        self.p_2d = self.arrays.p.reshape(self.shape_inner)
+        u_lid, v_lid = ops.lid_velocity_profile(lv.x, params.corner_treatment, params.corner_smoothing,
+                                                params.lid_velocity, params.Lx)
+        self.u_2d[:, -1] = u_lid  # _initialize_lid_velocity (sg.py:250-253)
+        self.v_2d[:, -1] = v_lid
+        self._gpu = None
+
+    # ---- device handle ------------------------------------------------------------------------------------
+    def _batch(self) -> BatchedSpectralLDC:
+        if self._gpu is None:
+            p = self.params
+            self._gpu = BatchedSpectralLDC(p.nx, p.ny, 1, p.Lx, p.Ly, self.basis_type, self.device)
+            self._gpu.set_cases(p.Re, p.beta_squared, p.CFL, p.lid_velocity, p.corner_treatment, p.corner_smoothing)
+        return self._gpu
+
+    def close(self):
+        if self._gpu is not None:
+            self._gpu.close()
+            self._gpu = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _push_state(self):
+        self._batch().set_state(self.u_2d[None], self.v_2d[None], self.p_2d[None])
+
+    def _pull_state(self):
+        u, v, p = self._batch().get_state()
+        self.arrays.u[:] = u.ravel()
+        self.arrays.v[:] = v.ravel()
+        self.arrays.p[:] = p.ravel()
+
+    def _pull_residuals(self):
+        Ru, Rv, Rp, norms = self._batch().residual()
+        self.arrays.R_u[:] = Ru.ravel()
+        self.arrays.R_v[:] = Rv.ravel()
+        self.arrays.R_p[:] = Rp.ravel()
+        return norms[0]
+
+    # ---- reference API --------------------------------------------------------------------------------------
+    def step(self):
+        """One RK4 pseudo-step with SGSolver semantics (frozen pressure gradient; sg.py:410-449)."""
+        self._push_state()
+        self._batch().step(1, freeze_pressure=True, want_rel=False)
+        self._pull_state()
+        return self.arrays.u, self.arrays.v, self.arrays.p
+
+    def _compute_algebraic_residuals(self):
+        return {"u_residual": float(np.linalg.norm(self.arrays.R_u)), "v_residual": float(np.linalg.norm(self.arrays.R_v)),
+                "continuity_residual": float(np.linalg.norm(self.arrays.R_p))}
+
+    def _extrapolate_to_full_grid(self, inner_2d):
+        return ops.extrapolate_pressure_to_full(np.asarray(inner_2d))
+
+    def _finalize_fields(self):
+        """fields.p = inner pressure linearly extrapolated to the full grid (sg.py:451-461, 144-179)."""
+        self.fields.u[:] = self.arrays.u
+        self.fields.v[:] = self.arrays.v
+        self.fields.p[:] = self._extrapolate_to_full_grid(self.p_2d).ravel()
+
+    def _compute_energy(self):
+        return float(self._diagnostics()[0])
+
+    def _compute_enstrophy(self):
+        return float(self._diagnostics()[1])
+
+    def _compute_palinstrophy(self):
+        return float(self._diagnostics()[2])
+
+    def _diagnostics(self):
+        self._push_state()
+        return self._batch().diagnostics()[0]
+
+    def compute_vortex_metrics(self) -> dict:
+        """Streamfunction-based vortex metrics (sg.py:556-743) by tensor-product fast diagonalisation."""
+        return streamfunction_vortex_metrics(self.level, self.u_2d, self.v_2d)
+
+    def solve(self, tolerance: float = None, max_iter: int = None):
+        """base.solve (base.py:202-330) for the spectral single grid: iterate SGSolver.step until
+        max(||du||/(||u||+1e-12), same for v) < tolerance after a 10-iteration warm-up."""
+        tol = self.params.tolerance if tolerance is None else tolerance
+        max_iter = self.params.max_iterations if max_iter is None else max_iter
+        g = self._batch()
+        t0 = time.time()
+        self._push_state()
+        r = g.solve(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
+        diverged = bool(r.diverged[0])
+        # the reference has no NaN exit on this path: it keeps stepping NaNs until max_iter
+        iters = int(max_iter) if diverged else int(r.iterations[0])
+        self._pull_state()
+        wall = time.time() - t0
+        norms = self._pull_residuals()
+        E, Z, Pal = g.diagnostics()[0]
+        self._store_results(float(r.rel_residual[0]), iters, bool(r.converged[0]), wall, norms, (E, Z, Pal))
+
+    def _store_results(self, rel, iters, converged, wall, norms, ezp):
+        self._finalize_fields()
+        self.time_series = TimeSeries(rel_iter_residual=[rel], u_residual=[float(norms[0])], v_residual=[float(norms[1])],
+                                      continuity_residual=[float(norms[2])], energy=[float(ezp[0])],
+                                      enstrophy=[float(ezp[1])], palinstrophy=[float(ezp[2])])
+        try:
+            vm = self.compute_vortex_metrics()
+        except Exception as e:  # base.py:156-160 swallows these too
+            log.warning(f"Failed to compute vortex metrics: {e}")
+            vm = {}
+        self.metrics = Metrics(iterations=iters, converged=converged, final_residual=rel, wall_time_seconds=wall,
+                               u_momentum_residual=float(norms[0]), v_momentum_residual=float(norms[1]),
+                               continuity_residual=float(norms[2]), final_energy=float(ezp[0]),
+                               final_enstrophy=float(ezp[1]), final_palinstrophy=float(ezp[2]),
+                               **{k: float(v) for k, v in vm.items() if k in Metrics.__dataclass_fields__})
+
+
+class FSGSolver(SGSolver):
+    """Coarse-to-fine grid sequencing (reference: spectral/fsg.py:19-129, multigrid/fsg.py:1053-1221)."""
+
+    def solve(self, tolerance: float = None, max_iter: int = None):
+        p = self.params
+        tol = p.tolerance if tolerance is None else tolerance
+        max_iter = p.max_iterations if max_iter is None else max_iter
+        if p.prolongation_method not in _TRANSFER["prolongation"]:
+            raise ValueError(f"Unknown prolongation method: {p.prolongation_method}. Use 'fft' or 'polynomial'.")
+        if p.restriction_method not in _TRANSFER["restriction"]:
+            raise ValueError(f"Unknown restriction method: {p.restriction_method}. Use 'fft' or 'injection'.")
+        t0 = time.time()
+        out = solve_fsg_batched(p.nx, p.Re, tol, int(max_iter), n_levels=p.n_levels,
+                                coarse_tolerance_factor=p.coarse_tolerance_factor, prolongation=p.prolongation_method,
+                                beta_squared=p.beta_squared, CFL=p.CFL, lid_velocity=p.lid_velocity,
+                                corner_treatment=p.corner_treatment, corner_smoothing=p.corner_smoothing, Lx=p.Lx, Ly=p.Ly,
+                                basis=self.basis_type, device=self.device)
+        wall = time.time() - t0
+        self.arrays.u[:] = out.u[0].ravel()
+        self.arrays.v[:] = out.v[0].ravel()
+        self.arrays.p[:] = out.p[0].ravel()
+        converged = bool(out.converged[0])
+        self._push_state()
+        norms = self._pull_residuals()
+        ezp = self._batch().diagnostics()[0]
+        # fsg.py:107-114: a one-entry history whose rel_iter is tol (converged) or 10 tol (not)
+        self._store_results(tol if converged else tol * 10, int(out.iterations[0]), converged, wall, norms, ezp)

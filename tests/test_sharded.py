@@ -1,0 +1,90 @@
+"""Host logic of the multi-GPU sweep (ldc_b200/sharded.py) on CPU: world_size-2 gloo process group with a
+deterministic stand-in for the per-rank GPU solver.  The GPU numerics are covered by the -m gpu tests; here the
+subject is the sharding, the padded all-gather and the result ordering."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from ldc_b200.sharded import shard_bounds
+
+
+def test_shard_bounds_cover_the_batch():
+    assert shard_bounds(1024, 8) == [(i * 128, (i + 1) * 128) for i in range(8)]
+    assert shard_bounds(5, 2) == [(0, 3), (3, 5)]
+    assert shard_bounds(1, 4) == [(0, 1), (1, 1), (1, 1), (1, 1)]
+    for B, W in ((7, 3), (64, 8), (3, 8)):
+        b = shard_bounds(B, W)
+        assert b[0][0] == 0 and b[-1][1] == B and all(b[i][1] == b[i + 1][0] for i in range(W - 1))
+
+
+def _fake_solver(N, Re, tol, max_iter, *, corner_smoothing, device, **kw):
+    """Stand-in with the signature / result type of solve_fsg_batched: every output is a function of the case."""
+    from ldc_b200.fsg import FSGResult
+
+    Re = np.asarray(Re)
+    B, n = Re.size, N + 1
+    base = np.arange(n * n, dtype=np.float64).reshape(n, n)
+    u = Re[:, None, None] * base
+    v = corner_smoothing[:, None, None] * base
+    p = (Re + corner_smoothing)[:, None, None] * np.ones((N - 1, N - 1))
+    div = Re > 900
+    return FSGResult(u, v, p, (10 * Re).astype(np.int64), ~div, div, np.where(div, np.nan, 1e-7 * Re), kernel_ms=float(B))
+
+
+def _worker(rank, world, port, B, q):
+    import torch.distributed as dist
+
+    from ldc_b200.sharded import solve_sweep
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        Re = np.linspace(100, 1000, B)
+        cs = np.linspace(0.02, 0.35, B)
+        r = solve_sweep(6, Re, cs, 1e-6, 100, fields="rank0", local_solver=_fake_solver)
+        q.put((rank, r.iterations, r.converged, r.diverged, r.rel_residual, None if r.u is None else r.u.copy(),
+               None if r.p is None else r.p.copy(), r.kernel_ms, r.bounds))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("B", [5, 8, 1])
+def test_sweep_sharded_over_two_gloo_ranks_equals_unsharded(B):
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, B, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted((q.get(timeout=120) for _ in procs), key=lambda t: t[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    Re = np.linspace(100, 1000, B)
+    cs = np.linspace(0.02, 0.35, B)
+    ref = _fake_solver(6, Re, None, 100, corner_smoothing=cs, device=0)
+    for rank, it, conv, div, rel, u, p, kms, bounds in got:
+        assert np.array_equal(it, ref.iterations) and np.array_equal(conv, ref.converged) and np.array_equal(div, ref.diverged)
+        assert np.array_equal(np.isnan(rel), np.isnan(ref.rel_residual))
+        assert np.allclose(rel[~np.isnan(rel)], ref.rel_residual[~np.isnan(rel)])
+        assert bounds == shard_bounds(B, 2)
+        assert kms == max(hi - lo for lo, hi in bounds)
+        if rank == 0:
+            assert np.array_equal(u, ref.u) and np.array_equal(p, ref.p)
+        else:
+            assert u is None and p is None
+
+
+def test_sweep_without_process_group_runs_locally():
+    from ldc_b200.sharded import solve_sweep
+
+    Re = np.array([100.0, 400.0, 950.0])
+    r = solve_sweep(6, Re, 0.15, 1e-6, 100, local_solver=_fake_solver)
+    assert r.bounds == [(0, 3)] and list(r.iterations) == [1000, 4000, 9500] and list(r.diverged) == [False, False, True]
+    assert r.u.shape == (3, 7, 7)
