@@ -6,6 +6,7 @@
 
 #include "common.cuh"
 #include "peak.cuh"
+#include "resident_eo_main.cuh"
 #include "resident_main.cuh"
 #include "tiled.cuh"
 
@@ -129,31 +130,66 @@ static bool resident_ok(const ldc_handle* h) {
     return bytes <= (size_t)max_optin;
 }
 
-static bool use_resident(const ldc_handle* h) {
-    if (h->path == LDC_PATH_TILED) return false;
-    return resident_ok(h);
+static bool eo_shape_ok(const ldc_handle* h) { return h->nx == h->ny && eo_pick_hp(h->mx) != 0; }
+
+static size_t eo_smem_bytes(int HP) {
+    switch (HP) {
+        case 8: return EoCfg<8, 1>::smem_doubles() * sizeof(double);
+        case 16: return EoCfg<16, 1>::smem_doubles() * sizeof(double);
+        case 24: return EoCfg<24, 1>::smem_doubles() * sizeof(double);
+        case 32: return EoCfg<32, 2>::smem_doubles() * sizeof(double);
+    }
+    return 0;
+}
+
+// the even-odd kernel needs one set of operators for both directions (checked bit for bit in ldc_set_operators)
+static bool eo_ok(const ldc_handle* h) {
+    if (!eo_shape_ok(h) || !h->square_ops) return false;
+    int max_optin = 0;
+    if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return false;
+    return eo_smem_bytes(h->HP) <= (size_t)max_optin;
+}
+
+// 0 tiled, 1 resident, 2 even-odd resident
+static int pick_kernel(const ldc_handle* h) {
+    if (h->path == LDC_PATH_TILED) return 0;
+    if (h->path == LDC_PATH_RESIDENT) return resident_ok(h) ? 1 : -1;
+    if (h->path == LDC_PATH_RESIDENT_EO) return eo_ok(h) ? 2 : -1;
+    if (eo_ok(h)) return 2;
+    return resident_ok(h) ? 1 : 0;
 }
 
 // canonical <-> packed state synchronisation
 static int ensure_canonical(ldc_handle* h) {
     if (h->canon_valid) return LDC_OK;
     const int n1 = h->n1x;
-    k_unpack_state<<<dim3((n1 * n1 + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride, n1,
-                                                                             h->MP);
+    const dim3 grid((n1 * n1 + 255) / 256, h->B);
+    if (h->packed_valid == 2)
+        k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->e_state, h->e_state_stride, n1, h->HP);
+    else
+        k_unpack_state<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride, n1, h->MP);
     h->launches += 1;
     LDC_CUDA(cudaGetLastError());
     h->canon_valid = true;
     return LDC_OK;
 }
 
-static int ensure_packed(ldc_handle* h) {
-    if (h->packed_valid) return LDC_OK;
-    const int MP = h->MP, LD = res_ld(MP);
-    k_pack_state<<<dim3((MP * LD + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride,
-                                                                           h->n1x, MP);
+static int ensure_packed(ldc_handle* h, int kind) {
+    if (h->packed_valid == kind) return LDC_OK;
+    int rc = ensure_canonical(h);
+    if (rc) return rc;
+    if (kind == 2) {
+        const int HP = h->HP, LD = eo_ld(HP);
+        k_pack_state_eo<<<dim3((std::max(HP * LD, 2 * HP) + 255) / 256, h->B), 256, 0, h->stream>>>(
+            h->u, h->v, h->p, h->e_state, h->e_state_stride, h->n1x, HP);
+    } else {
+        const int MP = h->MP, LD = res_ld(MP);
+        k_pack_state<<<dim3((MP * LD + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride,
+                                                                               h->n1x, MP);
+    }
     h->launches += 1;
     LDC_CUDA(cudaGetLastError());
-    h->packed_valid = true;
+    h->packed_valid = kind;
     return LDC_OK;
 }
 
@@ -198,6 +234,12 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
         A_(r_state, B * h->r_state_stride);
         A_(q_data, B); A_(q_seq, B); A_(q_ctl, 4);
     }
+    if (rc == LDC_OK && eo_shape_ok(h)) {
+        h->HP = eo_pick_hp(h->mx);
+        h->e_state_stride = eo_state_stride(h->HP);
+        A_(e_ops, eo_ops_size(h->HP));
+        A_(e_state, B * h->e_state_stride);
+    }
     if (rc == LDC_OK && cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
         rc = fail(LDC_ERR_CUDA, "ldc_create: cannot query the SM count");
 #undef A_
@@ -220,7 +262,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -234,7 +276,9 @@ void ldc_destroy(ldc_t* h) {
 }
 
 int ldc_set_path(ldc_t* h, int path) {
-    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT_EO) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (path == LDC_PATH_RESIDENT_EO && !eo_shape_ok(h))
+        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the even-odd resident path needs nx == ny and nx - 1 <= 64");
     if (path == LDC_PATH_RESIDENT && !resident_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the resident path needs nx == ny and nx - 1 <= 64");
     h->path = path;
@@ -296,6 +340,13 @@ int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const doubl
                                                                  vecs + 4 * MP, n1, MP);
         h->launches += 4;
     }
+    if (h->e_ops && h->square_ops) {
+        const int HP = h->HP, n1 = h->n1x, m = h->mx;
+        double* DI = h->pfull;  // scratch: D I (n1 x m)
+        k_left_mul<<<grid2d(n1, m, 1), kBlock2d, 0, h->stream>>>(h->Dx, h->Ix, DI, n1, n1, m, nullptr);
+        k_pack_ops_eo<<<(HP * eo_ld(HP) + T - 1) / T, T, 0, h->stream>>>(h->Dx, h->Dxx, DI, h->e_ops, n1, HP);
+        h->launches += 2;
+    }
     LDC_CUDA(cudaGetLastError());
     LDC_CUDA(cudaStreamSynchronize(h->stream));
     h->ops_set = true;
@@ -327,7 +378,7 @@ int ldc_set_state(ldc_t* h, const double* u, const double* v, const double* p) {
     if ((rc = copy_in(h, h->u, u, h->B * nf))) return rc;
     if ((rc = copy_in(h, h->v, v, h->B * nf))) return rc;
     if ((rc = copy_in(h, h->p, p, h->B * ni))) return rc;
-    h->packed_valid = false;
+    h->packed_valid = 0;
     return LDC_OK;
 }
 
@@ -352,7 +403,7 @@ int ldc_init_state(ldc_t* h) {
     h->launches += 1;
     LDC_CUDA(cudaGetLastError());
     h->canon_valid = true;
-    h->packed_valid = false;
+    h->packed_valid = 0;
     return LDC_OK;
 }
 
@@ -429,6 +480,48 @@ static int launch_resident_t(ldc_handle* h, const ResParams& P) {
     return LDC_OK;
 }
 
+template <int HP, int NT>
+static int eo_slots_t(ldc_handle* h) {
+    using C = EoCfg<HP, NT>;
+    const size_t bytes = C::smem_doubles() * sizeof(double);
+    LDC_CUDA(cudaFuncSetAttribute(k_resident_eo<HP, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int per_sm = 0;
+    LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resident_eo<HP, NT>, C::THREADS, bytes));
+    h->res_slots = std::max(1, per_sm) * h->num_sms;
+    return LDC_OK;
+}
+
+static int eo_slots(ldc_handle* h) {
+    switch (h->HP) {
+        case 8: return eo_slots_t<8, 1>(h);
+        case 16: return eo_slots_t<16, 1>(h);
+        case 24: return eo_slots_t<24, 1>(h);
+        case 32: return eo_slots_t<32, 2>(h);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "even-odd resident path: unsupported padded size");
+}
+
+template <int HP, int NT>
+static int launch_eo_t(ldc_handle* h, const ResParams& P) {
+    using C = EoCfg<HP, NT>;
+    const size_t bytes = C::smem_doubles() * sizeof(double);
+    k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
+    k_resident_eo<HP, NT><<<std::min(h->B, h->res_slots), C::THREADS, bytes, h->stream>>>(P);
+    h->launches += 2;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+static int launch_eo(ldc_handle* h, const ResParams& P) {
+    switch (h->HP) {
+        case 8: return launch_eo_t<8, 1>(h, P);
+        case 16: return launch_eo_t<16, 1>(h, P);
+        case 24: return launch_eo_t<24, 1>(h, P);
+        case 32: return launch_eo_t<32, 2>(h, P);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "even-odd resident path: unsupported padded size");
+}
+
 static int launch_resident(ldc_handle* h, const ResParams& P) {
     switch (h->MP) {
         case 16: return launch_resident_t<16, 2, 2>(h, P);
@@ -444,24 +537,26 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
     h->launches += 1;
     int rc;
-    const bool resident = use_resident(h);
-    if (h->path == LDC_PATH_RESIDENT && !resident)
-        return fail(LDC_ERR_UNSUPPORTED, "resident path requested but the shape does not fit shared memory");
+    const int kernel = pick_kernel(h);
+    if (kernel < 0)
+        return fail(LDC_ERR_UNSUPPORTED, "the requested resident path cannot run this shape (shared memory, or x / y "
+                                         "operators differ for the even-odd kernel)");
+    const bool resident = kernel > 0, eo = kernel == 2;
     if (resident) {
-        if ((rc = ensure_packed(h))) return rc;
+        if ((rc = ensure_packed(h, kernel))) return rc;
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));  // device time of the stepping kernels only
         ResParams P;
-        P.ops = h->r_ops; P.square = h->square_ops ? 1 : 0;
-        P.state = h->r_state; P.state_stride = h->r_state_stride;
+        P.ops = eo ? h->e_ops : h->r_ops; P.square = h->square_ops ? 1 : 0;
+        P.state = eo ? h->e_state : h->r_state; P.state_stride = eo ? h->e_state_stride : h->r_state_stride;
         P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
-        P.n1 = h->n1x; P.m = h->mx; P.K4 = (h->mx + 3) / 4 * 4;
+        P.n1 = h->n1x; P.m = h->mx; P.K4 = ((eo ? eo_half(h->mx) : h->mx) + 3) / 4 * 4;
         P.dx_min = h->dx_min; P.dy_min = h->dy_min;
         P.status = h->status; P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.freeze = freeze;
         P.max_iter = max_iter;
         P.q_data = h->q_data; P.q_seq = h->q_seq; P.q_ctl = h->q_ctl; P.B = h->B;
-        if ((rc = resident_slots(h))) return rc;
+        if ((rc = eo ? eo_slots(h) : resident_slots(h))) return rc;
         // steps per launch (the host looks at the active count between launches)
-        const long long chunk = h->MP >= 64 ? 1024 : (h->MP >= 48 ? 2048 : (h->MP >= 32 ? 4096 : 16384));
+        const long long chunk = h->mx >= 49 ? 1024 : (h->mx >= 33 ? 2048 : (h->mx >= 17 ? 4096 : 16384));
         h->canon_valid = false;
         for (long long done = 0; done < max_iter; done += chunk) {
             const long long L = std::min(chunk, max_iter - done);
@@ -473,7 +568,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
                 const long long c = (L * h->B + 64LL * h->res_slots - 1) / (64LL * h->res_slots);
                 P.chunk = std::min(L, std::max(4LL, c));
             }
-            if ((rc = launch_resident(h, P))) return rc;
+            if ((rc = eo ? launch_eo(h, P) : launch_resident(h, P))) return rc;
             if (done + chunk < max_iter) {
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
@@ -483,7 +578,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     } else {
         if ((rc = ensure_canonical(h))) return rc;
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
-        h->packed_valid = false;
+        h->packed_valid = 0;
         const long long chunk = 64;
         for (long long done = 0; done < max_iter; done += chunk) {
             const long long n = std::min(chunk, max_iter - done);
@@ -638,7 +733,7 @@ static int transfer_fields(ldc_t* src, ldc_t* dst, const double* Pxu, const doub
     if (tmp_alloc) cudaFree(tmp_alloc);
     if (e != cudaSuccess) return fail(LDC_ERR_CUDA, std::string(who) + ": " + cudaGetErrorString(e));
     dst->canon_valid = true;
-    dst->packed_valid = false;
+    dst->packed_valid = 0;
     return LDC_OK;
 }
 

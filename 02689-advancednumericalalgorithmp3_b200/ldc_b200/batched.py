@@ -13,7 +13,8 @@ import numpy as np
 from . import _lib
 from . import operators as ops
 
-_PATHS = {"auto": _lib.LDC_PATH_AUTO, "tiled": _lib.LDC_PATH_TILED, "resident": _lib.LDC_PATH_RESIDENT}
+_PATHS = {"auto": _lib.LDC_PATH_AUTO, "tiled": _lib.LDC_PATH_TILED, "resident": _lib.LDC_PATH_RESIDENT,
+          "resident_eo": _lib.LDC_PATH_RESIDENT_EO}
 
 
 @dataclass

@@ -38,9 +38,11 @@ enum {
 
 /* kernel path selection for ldc_step / ldc_solve */
 enum {
-    LDC_PATH_AUTO = 0,    /* resident DMMA kernel when the shape fits shared memory, else tiled */
-    LDC_PATH_TILED = 1,   /* state in global memory (L2), one launch per RK stage; any nx, ny */
-    LDC_PATH_RESIDENT = 2 /* state + operators resident in shared memory, FP64 DMMA, many steps per launch */
+    LDC_PATH_AUTO = 0,        /* even-odd resident kernel when the shape allows, else resident, else tiled */
+    LDC_PATH_TILED = 1,       /* state in global memory (L2), one launch per RK stage; any nx, ny */
+    LDC_PATH_RESIDENT = 2,    /* state + operators resident in shared memory, FP64 DMMA, many steps per launch */
+    LDC_PATH_RESIDENT_EO = 3  /* resident + even-odd (parity) splitting of the operators: half the DMMA work;
+                                 needs nx == ny, identical x / y operators and nx - 1 <= 64 */
 };
 
 /* Library / build information: "ldc_b200 <version> sm_100a". */

@@ -5,7 +5,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-PATHS = ["tiled", "resident"]
+PATHS = ["tiled", "resident", "resident_eo"]
 
 
 def rel(a, b):
@@ -139,18 +139,19 @@ def test_fsg_solve_iteration_count_and_fields(ldc, golden, path):
     out.finest.close()
 
 
-def test_fsg_reference_configs_resident(ldc, golden):
-    """BASELINE configs on the resident path: Ghia Re=100 N=32 (FSG and SG), Botella Re=1000 N=30 cs=0.15,
+@pytest.mark.parametrize("path", ["resident", "resident_eo"])
+def test_fsg_reference_configs_resident(ldc, golden, path):
+    """BASELINE configs on the resident paths: Ghia Re=100 N=32 (FSG and SG), Botella Re=1000 N=30 cs=0.15,
     Re=400 N=64 -- iteration counts +-1 and converged fields <= 1e-10 against the reference."""
     g = golden.solves
     for tag, N, Re in (("fsg_Re100_N32", 32, 100.0), ("fsg_Re1000_N30_cs015", 30, 1000.0), ("fsg_Re400_N64", 64, 400.0)):
-        out = ldc.solve_fsg_batched(N, Re, 1e-6, 500_000 if N == 30 else 10_000_000, path="resident")
+        out = ldc.solve_fsg_batched(N, Re, 1e-6, 500_000 if N == 30 else 10_000_000, path=path)
         meta = g[f"{tag}_meta"]
         assert abs(int(out.iterations[0]) - int(meta[0])) <= 1, (tag, out.iterations, meta[0])
         assert out.converged[0]
         for f in ("u", "v", "p"):
             assert rel(getattr(out, f)[0], g[f"{tag}_{f}"]) < 1e-10, (tag, f)
-    out = ldc.solve_sg_batched(32, 100.0, 1e-6, 10_000_000, path="resident")
+    out = ldc.solve_sg_batched(32, 100.0, 1e-6, 10_000_000, path=path)
     meta = g["sg_Re100_N32_meta"]
     assert abs(int(out.iterations[0]) - int(meta[0])) <= 1 and out.converged[0]
     for f in ("u", "v", "p"):
@@ -169,15 +170,16 @@ def test_divergence_does_not_poison_batch_mates(ldc, golden):
     assert rel(out.u[1], g["fsg_Re1000_N30_cs015_u"]) < 1e-10
 
 
-def test_batch_is_bitwise_independent_of_its_composition(ldc):
+@pytest.mark.parametrize("path", ["resident", "resident_eo"])
+def test_batch_is_bitwise_independent_of_its_composition(ldc, path):
     """A cavity's trajectory must not depend on its batch-mates or its slot (deterministic reductions)."""
     N, K = 32, 50
     Re = np.array([100.0, 400.0, 1000.0, 400.0])
-    with ldc.BatchedSpectralLDC(N, batch=4, path="resident") as s:
+    with ldc.BatchedSpectralLDC(N, batch=4, path=path) as s:
         s.set_cases(Re).init_state()
         s.step(K)
         u4, v4, p4 = s.get_state()
-    with ldc.BatchedSpectralLDC(N, batch=1, path="resident") as s:
+    with ldc.BatchedSpectralLDC(N, batch=1, path=path) as s:
         s.set_cases(400.0).init_state()
         s.step(K)
         u1, v1, p1 = s.get_state()
@@ -195,8 +197,29 @@ def test_resident_matches_tiled_at_bench_size(ldc, N):
             s.set_cases(Re).init_state()
             s.step(40)
             res[path] = s.get_state()
-    for a, b in zip(res["resident"], res["tiled"]):
+    for path in ("resident", "resident_eo"):
+        for a, b in zip(res[path], res["tiled"]):
+            assert rel(a, b) < 1e-11, path
+
+
+@pytest.mark.parametrize("N", [12, 15, 40, 48, 63])
+def test_even_odd_kernel_every_padded_size(ldc, N):
+    """Even and odd interior counts, every padded half size (8, 16, 24, 32), random BC-violating start and
+    per-cavity physics: the even-odd kernel against the plain-FMA tiled path, including the convergence norms."""
+    rng = np.random.default_rng(N)
+    B = 3
+    u, v = 0.1 * rng.standard_normal((2, B, N + 1, N + 1))
+    p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
+    Re = np.array([80.0, 400.0, 1500.0])
+    out = {}
+    for path in ("tiled", "resident_eo"):
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            s.set_cases(Re, beta_squared=[5.0, 3.0, 7.0], corner_smoothing=[0.05, 0.15, 0.3]).set_state(u, v, p)
+            r = s.step(3, freeze_pressure=(N % 2 == 0))
+            out[path] = (*s.get_state(), r)
+    for a, b in zip(out["resident_eo"][:3], out["tiled"][:3]):
         assert rel(a, b) < 1e-11
+    assert np.allclose(out["resident_eo"][3], out["tiled"][3], rtol=1e-9)
 
 
 def test_error_paths(ldc):
@@ -211,6 +234,15 @@ def test_error_paths(ldc):
         assert not s.resident_supported
         with pytest.raises(ldc.LdcError):
             s.set_path("resident")
+        with pytest.raises(ldc.LdcError):
+            s.set_path("resident_eo")
+    # different x / y operators: the even-odd kernel refuses, auto falls back to the plain resident kernel
+    with ldc.BatchedSpectralLDC(16, 16, batch=1, Lx=1.0, Ly=2.0, path="resident_eo") as s:
+        s.set_cases(100.0).init_state()
+        with pytest.raises(ldc.LdcError, match="even-odd"):
+            s.step(1)
+        s.set_path("auto")
+        s.step(2)
 
 
 # ---- the reference's solver interface (drop-in classes) ---------------------------------------------------
