@@ -290,6 +290,16 @@ int ldc_resident_supported(const ldc_t* h) {
     return resident_ok(h) ? LDC_OK : LDC_ERR_UNSUPPORTED;
 }
 
+const char* ldc_kernel_name(const ldc_t* h) {
+    if (!h) return "unsupported";
+    switch (pick_kernel(h)) {
+        case 0: return "tiled";
+        case 1: return "k_resident_rk4";
+        case 2: return "k_resident_eo";
+    }
+    return "unsupported";
+}
+
 int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const double* Dy, const double* Dyy, const double* Ix,
                       const double* Iy, double dx_min, double dy_min) {
     if (!h || !Dx || !Dxx || !Dy || !Dyy || !Ix || !Iy) return fail(LDC_ERR_INVALID, "ldc_set_operators: null argument");

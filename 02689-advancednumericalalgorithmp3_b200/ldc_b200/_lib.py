@@ -24,6 +24,7 @@ SIGNATURES = {
     "ldc_destroy": (None, [_vp]),
     "ldc_set_path": (C.c_int, [_vp, C.c_int]),
     "ldc_resident_supported": (C.c_int, [_vp]),
+    "ldc_kernel_name": (C.c_char_p, [_vp]),
     "ldc_set_operators": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_double, C.c_double]),
     "ldc_set_cases": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ldc_set_state": (C.c_int, [_vp, _vp, _vp, _vp]),

@@ -86,6 +86,11 @@ class BatchedSpectralLDC:
     def resident_supported(self) -> bool:
         return self.lib.ldc_resident_supported(self._h) == 0
 
+    @property
+    def kernel_name(self) -> str:
+        """Stepping kernel ldc_step / ldc_solve will launch for this handle and path."""
+        return self.lib.ldc_kernel_name(self._h).decode()
+
     def set_cases(self, Re, beta_squared=5.0, CFL=1.5, lid_velocity=1.0, corner_treatment="smoothing",
                   corner_smoothing=0.15, u_lid=None, v_lid=None):
         """Per-cavity physics.  Scalars broadcast over the batch; corner_treatment may be one string or a list."""

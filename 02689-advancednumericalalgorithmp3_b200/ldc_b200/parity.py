@@ -99,8 +99,8 @@ def merge_field(Fab: np.ndarray, m: int):
 
 def residual_interior_parity(level, u, v, p, Re, beta2):
     """NumPy model of what the `eo` kernel computes: the momentum and continuity residuals at the interior
-    nodes, evaluated entirely through h x h parity blocks.  Used by the tests to pin the formulation against the
-    oracle (`oracle.ldc_oracle.residual`) before it is trusted in CUDA.  Square grids (nx == ny) only."""
+    nodes, evaluated entirely through h x h parity blocks.  tests/test_parity.py pins this formulation against
+    the reference residual before it is trusted in CUDA.  Square grids (nx == ny) only."""
     n = level.nx + 1
     m = n - 2
     D, DD = level.Dx, level.Dxx

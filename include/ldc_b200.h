@@ -57,6 +57,9 @@ void ldc_destroy(ldc_t* h);
 int ldc_set_path(ldc_t* h, int path);
 /* 0 when the resident DMMA path can run this handle's shape, else LDC_ERR_UNSUPPORTED. */
 int ldc_resident_supported(const ldc_t* h);
+/* Name of the stepping kernel ldc_step / ldc_solve launch for this handle with its current path and operators:
+ * "k_resident_eo", "k_resident_rk4", "tiled" (or "unsupported" when the forced path cannot run the shape). */
+const char* ldc_kernel_name(const ldc_t* h);
 
 /* 1-D operators shared by every cavity of the handle (host or device pointers, row-major):
  *   Dx, Dxx : (nx+1) x (nx+1)   Dy, Dyy : (ny+1) x (ny+1)

@@ -23,9 +23,10 @@ def fstep(N):
     return 4 * (20 * n**3 + 2 * n * m * m + 2 * n * n * m)
 
 
-for N, B, K in ((64, 256, 400), (64, 148, 400), (64, 296, 400), (32, 1024, 1000), (30, 1, 2000), (16, 2048, 2000)):
+CASES = [(64, 256, 400), (64, 148, 400), (64, 1024, 200), (48, 512, 400), (32, 1024, 1000), (30, 1, 2000), (16, 2048, 2000)]
+for path, (N, B, K) in [(p, c) for c in CASES for p in ("resident", "resident_eo")]:
     Re = 400.0 * (1 + 0.05 * np.random.default_rng(0).uniform(-1, 1, B))
-    with ldc_b200.BatchedSpectralLDC(N, batch=B, path="resident") as s:
+    with ldc_b200.BatchedSpectralLDC(N, batch=B, path=path) as s:
         s.set_cases(Re).init_state()
         s.step(50, want_rel=False)
         t0 = time.time()
@@ -33,6 +34,6 @@ for N, B, K in ((64, 256, 400), (64, 148, 400), (64, 296, 400), (32, 1024, 1000)
         wall = time.time() - t0
         ms = s.last_kernel_ms
     rate = B * K / (ms * 1e-3)
-    out[f"N{N}_B{B}"] = dict(steps_per_s=rate, kernel_ms=ms, wall_ms=wall * 1e3, tflops=rate * fstep(N) / 1e12)
-    print(N, B, out[f"N{N}_B{B}"], flush=True)
+    out[f"{path}_N{N}_B{B}"] = dict(steps_per_s=rate, kernel_ms=ms, wall_ms=wall * 1e3, tflops=rate * fstep(N) / 1e12)
+    print(path, N, B, out[f"{path}_N{N}_B{B}"], flush=True)
 json.dump(out, open("gpurun_out/probe.json", "w"), indent=1)
