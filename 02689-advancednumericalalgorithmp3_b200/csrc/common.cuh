@@ -88,12 +88,15 @@ struct ldc_handle {
     double* r_ops = nullptr;
     double* r_state = nullptr;
     size_t r_state_stride = 0;    // doubles per cavity
-    int packed_valid = 0;         // which packed record holds the current state: 0 none, 1 r_state, 2 e_state
+    int packed_valid = 0;         // which packed record holds the current state: 0 none, 1 r_state, 2 e_state, 3 s_state (buffer 0)
     // even-odd resident path (resident_eo.cuh)
     int HP = 0;
     double* e_ops = nullptr;
     double* e_state = nullptr;
     size_t e_state_stride = 0;
+    // streamed even-odd path (stream_eo.cuh): three rotating copies of the packed state + per-tile partial sums
+    double* s_state = nullptr;
+    double* s_partials = nullptr;
     bool canon_valid = true;      // u, v, p hold the current state
     int* q_data = nullptr;        // work queue of the resident kernel (resident.cuh: CavityQueue)
     unsigned* q_seq = nullptr;

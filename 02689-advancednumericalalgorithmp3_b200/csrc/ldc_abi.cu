@@ -8,6 +8,7 @@
 #include "peak.cuh"
 #include "resident_eo_main.cuh"
 #include "resident_main.cuh"
+#include "stream_eo.cuh"
 #include "tiled.cuh"
 
 namespace ldc {
@@ -150,13 +151,21 @@ static bool eo_ok(const ldc_handle* h) {
     return eo_smem_bytes(h->HP) <= (size_t)max_optin;
 }
 
-// 0 tiled, 1 resident, 2 even-odd resident
+static bool stream_shape_ok(const ldc_handle* h) {
+    const int hh = eo_half(h->mx);
+    return h->nx == h->ny && hh > 32 && hh <= ST_HP;
+}
+static bool stream_ok(const ldc_handle* h) { return stream_shape_ok(h) && h->square_ops; }
+
+// 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd
 static int pick_kernel(const ldc_handle* h) {
     if (h->path == LDC_PATH_TILED) return 0;
     if (h->path == LDC_PATH_RESIDENT) return resident_ok(h) ? 1 : -1;
     if (h->path == LDC_PATH_RESIDENT_EO) return eo_ok(h) ? 2 : -1;
+    if (h->path == LDC_PATH_STREAM_EO) return stream_ok(h) ? 3 : -1;
     if (eo_ok(h)) return 2;
-    return resident_ok(h) ? 1 : 0;
+    if (resident_ok(h)) return 1;
+    return stream_ok(h) ? 3 : 0;
 }
 
 // canonical <-> packed state synchronisation
@@ -164,7 +173,9 @@ static int ensure_canonical(ldc_handle* h) {
     if (h->canon_valid) return LDC_OK;
     const int n1 = h->n1x;
     const dim3 grid((n1 * n1 + 255) / 256, h->B);
-    if (h->packed_valid == 2)
+    if (h->packed_valid == 3)
+        k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->s_state, h->e_state_stride, n1, ST_HP);
+    else if (h->packed_valid == 2)
         k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->e_state, h->e_state_stride, n1, h->HP);
     else
         k_unpack_state<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride, n1, h->MP);
@@ -178,10 +189,10 @@ static int ensure_packed(ldc_handle* h, int kind) {
     if (h->packed_valid == kind) return LDC_OK;
     int rc = ensure_canonical(h);
     if (rc) return rc;
-    if (kind == 2) {
+    if (kind == 2 || kind == 3) {
         const int HP = h->HP, LD = eo_ld(HP);
         k_pack_state_eo<<<dim3((std::max(HP * LD, 2 * HP) + 255) / 256, h->B), 256, 0, h->stream>>>(
-            h->u, h->v, h->p, h->e_state, h->e_state_stride, h->n1x, HP);
+            h->u, h->v, h->p, kind == 3 ? h->s_state : h->e_state, h->e_state_stride, h->n1x, HP);
     } else {
         const int MP = h->MP, LD = res_ld(MP);
         k_pack_state<<<dim3((MP * LD + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride,
@@ -239,6 +250,12 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
         h->e_state_stride = eo_state_stride(h->HP);
         A_(e_ops, eo_ops_size(h->HP));
         A_(e_state, B * h->e_state_stride);
+    } else if (rc == LDC_OK && stream_shape_ok(h)) {
+        h->HP = ST_HP;
+        h->e_state_stride = eo_state_stride(ST_HP);
+        A_(e_ops, eo_ops_size(ST_HP));
+        A_(s_state, 3 * B * h->e_state_stride);
+        A_(s_partials, B * ST_TILES * 8);
     }
     if (rc == LDC_OK && cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
         rc = fail(LDC_ERR_CUDA, "ldc_create: cannot query the SM count");
@@ -262,7 +279,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -276,7 +293,9 @@ void ldc_destroy(ldc_t* h) {
 }
 
 int ldc_set_path(ldc_t* h, int path) {
-    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT_EO) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_STREAM_EO) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (path == LDC_PATH_STREAM_EO && !stream_shape_ok(h))
+        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the streamed even-odd path needs nx == ny and 66 <= nx <= 128");
     if (path == LDC_PATH_RESIDENT_EO && !eo_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the even-odd resident path needs nx == ny and nx - 1 <= 64");
     if (path == LDC_PATH_RESIDENT && !resident_shape_ok(h))
@@ -296,6 +315,7 @@ const char* ldc_kernel_name(const ldc_t* h) {
         case 0: return "tiled";
         case 1: return "k_resident_rk4";
         case 2: return "k_resident_eo";
+        case 3: return "k_stream_stage";
     }
     return "unsupported";
 }
@@ -551,8 +571,46 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     if (kernel < 0)
         return fail(LDC_ERR_UNSUPPORTED, "the requested resident path cannot run this shape (shared memory, or x / y "
                                          "operators differ for the even-odd kernel)");
-    const bool resident = kernel > 0, eo = kernel == 2;
-    if (resident) {
+    const bool resident = kernel == 1 || kernel == 2, eo = kernel == 2;
+    if (kernel == 3) {
+        if ((rc = ensure_packed(h, 3))) return rc;
+        const size_t smem = ST_SMEM_DOUBLES * sizeof(double);
+        LDC_CUDA(cudaFuncSetAttribute(k_stream_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
+        StreamParams P;
+        P.ops = h->e_ops;
+        const size_t bs = (size_t)h->B * h->e_state_stride;
+        P.buf[0] = h->s_state; P.buf[1] = h->s_state + bs; P.buf[2] = h->s_state + 2 * bs;
+        P.stride = h->e_state_stride;
+        P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
+        P.dt = h->dt; P.n1 = h->n1x; P.m = h->mx; P.K4 = (eo_half(h->mx) + 3) / 4 * 4;
+        P.status = h->status; P.partials = h->s_partials; P.freeze = freeze;
+        k_stream_begin<<<h->B, 256, 0, h->stream>>>(h->s_state, h->e_state_stride, h->mx, h->Re, h->beta2, h->CFL, h->lidvel,
+                                                    h->dx_min, h->dy_min, h->dt, h->status);
+        h->launches += 1;
+        h->canon_valid = false;
+        const long long chunk = 256;
+        for (long long done = 0; done < max_iter; ++done) {
+            for (int stg = 0; stg < 4; ++stg) {
+                P.stage = stg;
+                P.bc_edges = (done == 0 && stg == 0) ? 0 : 1;
+                k_stream_stage<<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
+            }
+            k_stream_end<<<h->B, 128, 0, h->stream>>>(P, done == 0 ? 1 : 0, tol_dev, warmup, max_iter, nan_exit, h->dx_min,
+                                                       h->dy_min, h->dt);
+            h->launches += 5;
+            if ((done + 1) % chunk == 0 && done + 1 < max_iter) {
+                LDC_CUDA(cudaGetLastError());
+                int na = 0;
+                if ((rc = count_active(h, &na))) return rc;
+                if (na == 0) break;
+            }
+        }
+        // every cavity's record back into buffer 0
+        k_stream_normalise<<<dim3(32, h->B), 256, 0, h->stream>>>(h->s_state, bs, h->e_state_stride, h->status);
+        k_stream_clear_pad<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 2;
+    } else if (resident) {
         if ((rc = ensure_packed(h, kernel))) return rc;
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));  // device time of the stepping kernels only
         ResParams P;

@@ -1,0 +1,512 @@
+// Streamed even-odd path for grids whose state does not fit one SM (65 <= nx - 1 <= 128, e.g. N = 128).
+//
+// Same parity algebra as the resident even-odd kernel (resident_eo.cuh), but a cavity is spread over
+// (HP/16)^2 CTAs: each CTA owns a 16 x 16 tile of all four parity blocks, streams the operand panels it needs
+// from L2 through shared memory in K-chunks of 16 and runs one RK stage; one launch per stage, state in three
+// rotating global buffers (phi^n, stage in, stage out).  Eight cavities at N = 128 thus occupy 128 CTAs instead
+// of 8 SMs.  Per-cavity reductions (dt, convergence norms) are per-tile partials reduced in fixed order by
+// k_stream_end, so results do not depend on scheduling.
+#pragma once
+#include "resident_eo_kernel.cuh"
+
+namespace ldc {
+
+constexpr int ST_HP = 64, ST_LD = ST_HP + 4, ST_BLK = ST_HP * ST_LD;   // global parity blocks (eo layout, HP = 64)
+constexpr int ST_T = 16;                 // tile edge (rows and columns of each parity block)
+constexpr int ST_KC = 16, ST_LDK = 20;   // K-chunk and padded chunk row (= 4 mod 8: conflict-free fragments)
+constexpr int ST_PANEL = ST_T * ST_LDK;  // doubles per staged chunk panel (row-type: T x KC, column-type: KC x T)
+constexpr int ST_TILES = (ST_HP / ST_T) * (ST_HP / ST_T);
+constexpr int ST_THREADS = 128;          // 4 warps: (row half) x (u equation | v equation)
+constexpr int ST_ME = 2 * ST_HP;
+// shared memory: 36 chunk panels + boundary-column vectors (8 x HP) + boundary lines in parity form (16 x HP)
+// + divergence exchange (2 x 16 x 32) + reduction scratch
+constexpr size_t ST_SMEM_DOUBLES = 36 * ST_PANEL + 8 * ST_HP + 16 * ST_HP + 2 * 16 * 32 + 32;
+
+struct StreamParams {
+    const double* ops;            // eo packed operators, HP = 64
+    double* buf[3];               // rotating state buffers (eo packed records)
+    size_t stride;                // doubles per cavity record
+    const double *Re, *beta2, *CFL, *lidvel, *ulid, *vlid;
+    const double* dt;             // [B]
+    int n1, m, K4;
+    CavityStatus* status;         // status.pad = index of the buffer holding phi^n
+    double* partials;             // [B][ST_TILES][8]: s0..s3, max|u|, max|v|
+    int stage, freeze, bc_edges;  // bc_edges = 0: boundary lines as stored with phi^n (first stage after a load)
+};
+
+__device__ __forceinline__ int st_in(int cur, int stage) { return stage == 0 ? cur : (stage == 2 ? (cur + 2) % 3 : (cur + 1) % 3); }
+__device__ __forceinline__ int st_out(int cur, int stage) { return (stage & 1) ? (cur + 2) % 3 : (cur + 1) % 3; }
+
+// One K-chunk of the contractions of the warp's field (see eo_field_pass): operands come from staged panels.
+//   sOa: 6 operator row panels at the tile rows   sOb: 6 operator row panels at the tile columns
+//   sFa: 4 row panels of the field                 sFb: 4 column panels of the field
+//   sPa / sPb: 4 row / column panels of the pressure
+template <bool P_LEFT>
+__device__ __forceinline__ void st_chunk(const double* __restrict__ sOa, const double* __restrict__ sOb,
+                                         const double* __restrict__ sFa, const double* __restrict__ sFb,
+                                         const double* __restrict__ sPa, const double* __restrict__ sPb, int ksteps,
+                                         int wr, int g, int t, double (&a1)[4][2][2], double (&a2)[4][2][2],
+                                         double (&aL)[4][2][2]) {
+    constexpr int NT = 2;
+    const int arow = (wr + g) * ST_LDK + t;   // row-type panel: X[wr + g][k + t]
+    const int brow = g * ST_LDK + t;          // operator rows at the tile columns: Op[8 nt + g][k + t]
+    const int bfld = t * ST_LDK + g;          // column-type panel: F[k + t][8 nt + g]
+#pragma unroll 1
+    for (int ks = 0; ks < ksteps; ++ks) {
+        const int k0 = 4 * ks;
+        double FA[4], FB[4][NT];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            FA[q] = sFa[q * ST_PANEL + arow + k0];
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) FB[q][nt] = sFb[q * ST_PANEL + bfld + k0 * ST_LDK + nt * 8];
+        }
+        {
+            double dA[2], ddA[2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                dA[a] = sOa[a * ST_PANEL + arow + k0];
+                ddA[a] = sOa[(2 + a) * ST_PANEL + arow + k0];
+            }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
+                    }
+        }
+        {
+            double dB[2][NT], ddB[2][NT];
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    dB[b][nt] = sOb[b * ST_PANEL + brow + nt * 8 * ST_LDK + k0];
+                    ddB[b][nt] = sOb[(2 + b) * ST_PANEL + brow + nt * 8 * ST_LDK + k0];
+                }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
+                    }
+        }
+        if (P_LEFT) {
+            double gA[2], PB[4][NT];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) gA[a] = sOa[(4 + a) * ST_PANEL + arow + k0];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) PB[q][nt] = sPb[q * ST_PANEL + bfld + k0 * ST_LDK + nt * 8];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
+        } else {
+            double PA[4], gB[2][NT];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) PA[q] = sPa[q * ST_PANEL + arow + k0];
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) gB[b][nt] = sOb[(4 + b) * ST_PANEL + brow + nt * 8 * ST_LDK + k0];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], PA[2 * a + (1 - b)], gB[b][nt]);
+        }
+    }
+}
+
+}  // namespace ldc
+
+namespace ldc {
+
+// Boundary-line corrections + nonlinear assembly for the warp's field (cf. eo_assemble), with the thread's own
+// stage values of u and v in registers.  On return aL = momentum residual blocks, a1 = d(field)/dx (IS_U) or
+// d(field)/dy (!IS_U) blocks.
+template <bool IS_U>
+__device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, const double* __restrict__ sEdgeF, double nu,
+                                            int i, int c0, int t, const double (&uo)[4][2][2], const double (&vo)[4][2][2],
+                                            double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    constexpr int HP = ST_HP;
+    double d0i[2], dNi[2], dd0i[2], ddNi[2], Si[2], Ni[2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        d0i[a] = sVec[(0 + a) * HP + i];
+        dNi[a] = sVec[(2 + a) * HP + i];
+        dd0i[a] = sVec[(4 + a) * HP + i];
+        ddNi[a] = sVec[(6 + a) * HP + i];
+        Si[a] = sEdgeF[(4 + a) * HP + i];
+        Ni[a] = sEdgeF[(6 + a) * HP + i];
+    }
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int j = c0 + nt * 8 + 2 * t + hh;
+            double dx[4], dy[4];
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
+                const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
+                const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    const int q = 2 * a + b;
+                    dx[q] = a1[q][nt][hh] + d0i[a] * Wj + dNi[a] * Ej;
+                    dy[q] = a2[q][nt][hh] + Si[a] * d0j + Ni[a] * dNj;
+                    aL[q][nt][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                }
+            }
+            double ur[4], vr[4], fx[4], fy[4], cv[4], cq[4];
+            eo_to_points(uo[0][nt][hh], uo[1][nt][hh], uo[2][nt][hh], uo[3][nt][hh], ur);
+            eo_to_points(vo[0][nt][hh], vo[1][nt][hh], vo[2][nt][hh], vo[3][nt][hh], vr);
+            eo_to_points(dx[0], dx[1], dx[2], dx[3], fx);
+            eo_to_points(dy[0], dy[1], dy[2], dy[3], fy);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cv[q] = ur[q] * fx[q] + vr[q] * fy[q];
+            eo_from_points4(cv, cq);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                aL[q][nt][hh] = fma(-0.25, cq[q], aL[q][nt][hh]);
+                a1[q][nt][hh] = IS_U ? dx[q] : dy[q];
+            }
+        }
+}
+
+// One RK stage of every active cavity: grid (ST_TILES, B), 128 threads.
+__global__ void __launch_bounds__(ST_THREADS, 2) k_stream_stage(const StreamParams P) {
+    extern __shared__ __align__(16) double smem[];
+    double* sPan = smem;
+    double* sVec = sPan + 36 * ST_PANEL;
+    double* sEdgeP = sVec + 8 * ST_HP;
+    double* sX = sEdgeP + 16 * ST_HP;
+    double* sRed = sX + 2 * 16 * 32;
+
+    const int b = blockIdx.y;
+    const CavityStatus st = P.status[b];
+    if (!st.active) return;
+    const int tile = blockIdx.x, r0 = (tile / (ST_HP / ST_T)) * ST_T, c0 = (tile % (ST_HP / ST_T)) * ST_T;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int tw = warp & 1, fld = warp >> 1, wr = 8 * tw;
+    const int m = P.m, h = eo_half(m), centre = (m & 1) ? h - 1 : -1;
+    if (r0 >= h || c0 >= h) return;   // tile lies in the zero padding of the blocks
+    const int cur = st.pad;
+    const double* recN = P.buf[cur] + (size_t)b * P.stride;                       // phi^n
+    const double* recI = P.buf[st_in(cur, P.stage)] + (size_t)b * P.stride;       // stage input
+    double* recO = P.buf[st_out(cur, P.stage)] + (size_t)b * P.stride;            // stage output
+    const double* recP = P.freeze ? recN : recI;                                  // pressure operand
+    const double nu = 1.0 / P.Re[b], beta2 = P.beta2[b];
+
+    // ---- boundary-column vectors and boundary lines in parity form ----
+    for (int e = tid; e < 8 * ST_HP; e += ST_THREADS) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    for (int e = tid; e < 8 * ST_HP; e += ST_THREADS) {
+        const int line = e / ST_HP, k = e % ST_HP;   // uW uE uS uN vW vE vS vN
+        double x = 0.0, y = 0.0;
+        if (k < h) {
+            if (P.bc_edges) {
+                if ((line & 3) == 3) {
+                    const double* lid = (line < 4 ? P.ulid : P.vlid) + (size_t)b * P.n1 + 1;
+                    x = lid[k];
+                    y = lid[m - 1 - k];
+                }
+            } else {
+                const double* src = recN + 12 * ST_BLK + line * ST_ME;
+                x = __ldcg(src + k);
+                y = __ldcg(src + m - 1 - k);
+            }
+        }
+        sEdgeP[2 * line * ST_HP + k] = 0.5 * (x + y);
+        sEdgeP[(2 * line + 1) * ST_HP + k] = 0.5 * (x - y);
+    }
+
+    double a1[4][2][2], a2[4][2][2], aL[4][2][2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+
+    // ---- K loop: stage 36 chunk panels, contract ----
+    const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
+    for (int k0 = 0; k0 < P.K4; k0 += ST_KC) {
+        __syncthreads();   // previous chunk fully consumed (also orders the sVec / sEdgeP writes before their use)
+#pragma unroll
+        for (int p = 0; p < 36; ++p) {
+            const double* src;
+            double scale = 1.0;
+            if (p < 6) {            // operator rows at the tile rows
+                src = P.ops + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;
+                scale = (p == 2 || p == 3) ? nu : (p >= 4 ? -1.0 : 1.0);
+            } else if (p < 12) {    // operator rows at the tile columns
+                src = P.ops + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;
+                scale = (p == 8 || p == 9) ? nu : (p >= 10 ? -1.0 : 1.0);
+            } else if (p < 24) {    // row panels of u, v (stage input) and p
+                const double* rec = p < 20 ? recI : recP;
+                src = rec + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;
+            } else {                // column panels of u, v, p
+                const double* rec = p < 32 ? recI : recP;
+                src = rec + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;
+            }
+            double2 v2 = p < 12 ? __ldg(reinterpret_cast<const double2*>(src)) : __ldcg(reinterpret_cast<const double2*>(src));
+            v2.x *= scale;
+            v2.y *= scale;
+            *reinterpret_cast<double2*>(sPan + p * ST_PANEL + lr * ST_LDK + lc) = v2;
+        }
+        __syncthreads();
+        const int ksteps = min(ST_KC, P.K4 - k0) / 4;
+        if (fld == 0)
+            st_chunk<true>(sPan, sPan + 6 * ST_PANEL, sPan + 12 * ST_PANEL, sPan + 24 * ST_PANEL, sPan + 20 * ST_PANEL,
+                           sPan + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+        else
+            st_chunk<false>(sPan, sPan + 6 * ST_PANEL, sPan + 16 * ST_PANEL, sPan + 28 * ST_PANEL, sPan + 20 * ST_PANEL,
+                            sPan + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+    }
+
+    // ---- epilogue: the thread's own elements of all four blocks ----
+    const int i = r0 + wr + g;
+    double uo[4][2][2], vo[4][2][2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            const int e = i * ST_LD + c0 + nt * 8 + 2 * t;
+            const double2 a = __ldcg(reinterpret_cast<const double2*>(recI + (size_t)q * ST_BLK + e));
+            const double2 c = __ldcg(reinterpret_cast<const double2*>(recI + (size_t)(4 + q) * ST_BLK + e));
+            uo[q][nt][0] = a.x; uo[q][nt][1] = a.y;
+            vo[q][nt][0] = c.x; vo[q][nt][1] = c.y;
+        }
+    if (fld == 0) st_assemble<true>(sVec, sEdgeP, nu, i, c0, t, uo, vo, a1, a2, aL);
+    else st_assemble<false>(sVec, sEdgeP + 8 * ST_HP, nu, i, c0, t, uo, vo, a1, a2, aL);
+
+    const double adt = rk_alpha(P.stage) * P.dt[b];
+    const bool last = (P.stage == 3);
+    double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
+    const double wi = (i == centre) ? 0.5 : 1.0;
+    // momentum update of the warp's field; the v warps hand dv/dy to the u warps for the pressure update
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+        const int j = c0 + nt * 8 + 2 * t;
+        const int e = i * ST_LD + j;
+        const double w0 = 4.0 * wi * (j == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j + 1 == centre ? 0.5 : 1.0);
+        double fn[4][2];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const size_t off = (size_t)(4 * fld + q) * ST_BLK + e;
+            const double2 f0 = __ldcg(reinterpret_cast<const double2*>(recN + off));
+            fn[q][0] = f0.x + adt * aL[q][nt][0];
+            fn[q][1] = f0.y + adt * aL[q][nt][1];
+            if (last) {
+                double d;
+                d = fn[q][0] - f0.x; s0 = fma(w0 * d, d, s0); s1 = fma(w0 * f0.x, f0.x, s1);
+                d = fn[q][1] - f0.y; s0 = fma(w1 * d, d, s0); s1 = fma(w1 * f0.y, f0.y, s1);
+            }
+            __stcg(reinterpret_cast<double2*>(recO + off), make_double2(fn[q][0], fn[q][1]));
+            if (fld == 1) {
+                sX[(tw * 16 + (q * 2 + nt) * 2 + 0) * 32 + lane] = a1[q][nt][0];
+                sX[(tw * 16 + (q * 2 + nt) * 2 + 1) * 32 + lane] = a1[q][nt][1];
+            }
+        }
+        if (last) {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                double fr[4];
+                eo_to_points(fn[0][hh], fn[1][hh], fn[2][hh], fn[3][hh], fr);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) mx = nanmax(mx, fabs(fr[q]));
+            }
+        }
+    }
+    __syncthreads();
+    if (fld == 0) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            const int e = i * ST_LD + c0 + nt * 8 + 2 * t;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const size_t off = (size_t)(8 + q) * ST_BLK + e;
+                const double2 p0 = __ldcg(reinterpret_cast<const double2*>(recN + off));
+                const double dv0 = a1[q][nt][0] + sX[(tw * 16 + (q * 2 + nt) * 2 + 0) * 32 + lane];
+                const double dv1 = a1[q][nt][1] + sX[(tw * 16 + (q * 2 + nt) * 2 + 1) * 32 + lane];
+                __stcg(reinterpret_cast<double2*>(recO + off),
+                       make_double2(p0.x + adt * (-beta2 * dv0), p0.y + adt * (-beta2 * dv1)));
+            }
+        }
+    }
+    if (last) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            mx = nanmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        }
+        if (lane == 0) {
+            sRed[warp * 4 + 0] = s0;
+            sRed[warp * 4 + 1] = s1;
+            sRed[warp * 4 + 2] = mx;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double* out = P.partials + ((size_t)b * ST_TILES + tile) * 8;
+            out[0] = sRed[0] + sRed[4];                 // u: sum d^2   (warps 0, 1)
+            out[1] = sRed[1] + sRed[5];                 // u: sum u_n^2
+            out[2] = sRed[8] + sRed[12];                // v            (warps 2, 3)
+            out[3] = sRed[9] + sRed[13];
+            out[4] = nanmax(sRed[2], sRed[6]);
+            out[5] = nanmax(sRed[10], sRed[14]);
+        }
+    }
+}
+
+}  // namespace ldc
+
+namespace ldc {
+
+// Start of a run: max|u|, max|v| of the packed state (buffer 0) and the first dt.
+__global__ void __launch_bounds__(256) k_stream_begin(const double* __restrict__ buf0, size_t stride, int m,
+                                                      const double* __restrict__ Re, const double* __restrict__ beta2,
+                                                      const double* __restrict__ CFL, const double* __restrict__ lidvel,
+                                                      double dx_min, double dy_min, double* __restrict__ dt,
+                                                      CavityStatus* __restrict__ status) {
+    __shared__ double sh[2 * 32];
+    const int b = blockIdx.x, h = eo_half(m);
+    const double* rec = buf0 + (size_t)b * stride;
+    double mx[2] = {0.0, 0.0};
+    bool isnan_[2] = {false, false};
+    for (int e = threadIdx.x; e < h * h; e += blockDim.x) {
+        const int o = (e / h) * ST_LD + e % h;
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double* B = rec + (size_t)4 * f * ST_BLK + o;
+            double r[4];
+            eo_to_points(B[0], B[ST_BLK], B[2 * ST_BLK], B[3 * ST_BLK], r);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                isnan_[f] |= (r[q] != r[q]);
+                mx[f] = fmax(mx[f], fabs(r[q]));
+            }
+        }
+    }
+    const double* ed = rec + 12 * ST_BLK;
+    for (int e = threadIdx.x; e < 4 * ST_ME + 4; e += blockDim.x) {
+        const int q = e < 4 * ST_ME ? e : 8 * ST_ME + (e - 4 * ST_ME);
+        const double a = ed[q], c = ed[q + (e < 4 * ST_ME ? 4 * ST_ME : 4)];
+        isnan_[0] |= (a != a);
+        isnan_[1] |= (c != c);
+        mx[0] = fmax(mx[0], fabs(a));
+        mx[1] = fmax(mx[1], fabs(c));
+    }
+    double flag[2] = {isnan_[0] ? 1.0 : 0.0, isnan_[1] ? 1.0 : 0.0};
+    block_reduce<2, true>(mx, sh);
+    block_reduce<2, true>(flag, sh);
+    if (threadIdx.x == 0) {
+        const double um = flag[0] > 0.0 ? nan("") : mx[0], vm = flag[1] > 0.0 ? nan("") : mx[1];
+        status[b].umax = um;
+        status[b].vmax = vm;
+        const double ua = (lidvel[b] > um) ? lidvel[b] : um, va = (1e-10 > vm) ? 1e-10 : vm;
+        const double nu = 1.0 / Re[b];
+        const double lam_x = (ua + sqrt(ua * ua + beta2[b])) / dx_min + nu / (dx_min * dx_min);
+        const double lam_y = (va + sqrt(va * va + beta2[b])) / dy_min + nu / (dy_min * dy_min);
+        dt[b] = CFL[b] / (lam_x + lam_y);
+    }
+}
+
+// End of an RK4 step: reduce the tile partials in fixed order, add the boundary lines, convergence bookkeeping,
+// next dt, rotate the buffers and store the boundary-condition lines with the new state.
+__global__ void __launch_bounds__(128) k_stream_end(StreamParams P, int first, const double* __restrict__ tol, int warmup,
+                                                    long long max_iter, int nan_exit, double dx_min, double dy_min,
+                                                    double* __restrict__ dt) {
+    __shared__ double sh[6 * 32];
+    const int b = blockIdx.x;
+    CavityStatus st = P.status[b];
+    if (!st.active) return;
+    const int m = P.m, n1 = P.n1, cur = st.pad, nxt = (cur + 2) % 3;
+    const double* ed = P.buf[cur] + (size_t)b * P.stride + 12 * ST_BLK;   // boundary lines of phi^n
+    double* edn = P.buf[nxt] + (size_t)b * P.stride + 12 * ST_BLK;
+    const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
+    double s[4] = {0, 0, 0, 0}, bm[2] = {0, 0};
+    for (int e = threadIdx.x; e < m; e += blockDim.x) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double lid = (f ? vl : ul)[e + 1];
+            const double* L = ed + f * 4 * ST_ME;
+            const double w = first ? L[e] : 0.0, ea = first ? L[ST_ME + e] : 0.0, so = first ? L[2 * ST_ME + e] : 0.0;
+            const double no = first ? L[3 * ST_ME + e] : lid;
+            const double dn = lid - no;
+            s[2 * f] += w * w + ea * ea + so * so + dn * dn;
+            s[2 * f + 1] += w * w + ea * ea + so * so + no * no;
+            bm[f] = nanmax(bm[f], fabs(lid));
+            double* Ln = edn + f * 4 * ST_ME;
+            Ln[e] = 0.0; Ln[ST_ME + e] = 0.0; Ln[2 * ST_ME + e] = 0.0; Ln[3 * ST_ME + e] = lid;
+        }
+    }
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double* c = ed + 8 * ST_ME + 4 * f;   // c00 c0N cN0 cNN
+            const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
+            const double c0 = first ? c[0] : 0.0, c1 = first ? c[1] : l0, c2 = first ? c[2] : 0.0, c3 = first ? c[3] : lN;
+            const double d1 = l0 - c1, d3 = lN - c3;
+            s[2 * f] += c0 * c0 + d1 * d1 + c2 * c2 + d3 * d3;
+            s[2 * f + 1] += c0 * c0 + c1 * c1 + c2 * c2 + c3 * c3;
+            bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
+            double* cn = edn + 8 * ST_ME + 4 * f;
+            cn[0] = 0.0; cn[1] = l0; cn[2] = 0.0; cn[3] = lN;
+        }
+    }
+    // deterministic CTA reduction of the 4 sums + 2 maxima
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    cta_reduce<4>(s, bm, sh, warp, lane);
+    if (threadIdx.x == 0) {
+        double mx[2] = {0, 0};
+        const double* part = P.partials + (size_t)b * ST_TILES * 8;
+        for (int tl = 0; tl < ST_TILES; ++tl) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s[q] += part[tl * 8 + q];
+            mx[0] = nanmax(mx[0], part[tl * 8 + 4]);
+            mx[1] = nanmax(mx[1], part[tl * 8 + 5]);
+        }
+        const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+        update_status(st, ures, vres, tol ? tol[b] : -1.0, warmup, max_iter, nan_exit);
+        st.umax = nanmax(mx[0], bm[0]);
+        st.vmax = nanmax(mx[1], bm[1]);
+        st.pad = nxt;
+        P.status[b] = st;
+        const double lidv = P.lidvel[b], b2 = P.beta2[b], nu = 1.0 / P.Re[b];
+        const double ua = (lidv > st.umax) ? lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
+        const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu / (dx_min * dx_min);
+        const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu / (dy_min * dy_min);
+        dt[b] = P.CFL[b] / (lam_x + lam_y);
+    }
+}
+
+// After a run: move every cavity's record into buffer 0 so that the next run (or an unpack) finds it there.
+__global__ void k_stream_normalise(double* __restrict__ bufs, size_t buf_stride, size_t stride, CavityStatus* __restrict__ status) {
+    const int b = blockIdx.y, cur = status[b].pad;
+    if (cur == 0) return;
+    const double2* src = reinterpret_cast<const double2*>(bufs + cur * buf_stride + (size_t)b * stride);
+    double2* dst = reinterpret_cast<double2*>(bufs + (size_t)b * stride);
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < stride / 2; e += (size_t)gridDim.x * blockDim.x)
+        dst[e] = src[e];
+}
+__global__ void k_stream_clear_pad(CavityStatus* __restrict__ status, int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) status[b].pad = 0;
+}
+
+}  // namespace ldc

@@ -24,11 +24,15 @@ def fstep(N):
 
 
 CASES = [(64, 256, 400), (64, 148, 400), (64, 1024, 200), (48, 512, 400), (32, 1024, 1000), (30, 1, 2000), (16, 2048, 2000)]
-for path, (N, B, K) in [(p, c) for c in CASES for p in ("resident", "resident_eo")]:
+BIG = [(128, 8, 100), (128, 64, 50), (96, 64, 100)]
+RUNS = [(p, c) for c in CASES for p in ("resident", "resident_eo")] + [(p, c) for c in BIG for p in ("tiled", "stream_eo")]
+if len(sys.argv) > 1 and sys.argv[1] == "big":
+    RUNS = [(p, c) for c in BIG for p in ("tiled", "stream_eo")]
+for path, (N, B, K) in RUNS:
     Re = 400.0 * (1 + 0.05 * np.random.default_rng(0).uniform(-1, 1, B))
     with ldc_b200.BatchedSpectralLDC(N, batch=B, path=path) as s:
         s.set_cases(Re).init_state()
-        s.step(50, want_rel=False)
+        s.step(50 if N <= 64 else 5, want_rel=False)
         t0 = time.time()
         s.step(K, want_rel=False)
         wall = time.time() - t0

@@ -222,6 +222,45 @@ def test_even_odd_kernel_every_padded_size(ldc, N):
     assert np.allclose(out["resident_eo"][3], out["tiled"][3], rtol=1e-9)
 
 
+@pytest.mark.parametrize("N", [66, 80, 97, 128])
+def test_streamed_even_odd_kernel_large_grids(ldc, N):
+    """Grids beyond one SM's shared memory (the N = 128 config): the streamed even-odd path against the plain-FMA
+    tiled path from a random BC-violating start, both pressure semantics, plus a continued run (buffer rotation)."""
+    rng = np.random.default_rng(N)
+    B = 2
+    u, v = 0.1 * rng.standard_normal((2, B, N + 1, N + 1))
+    p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
+    Re = np.array([400.0, 5000.0])
+    out = {}
+    for path in ("tiled", "stream_eo"):
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            assert s.kernel_name == ("tiled" if path == "tiled" else "k_stream_stage")
+            s.set_cases(Re, corner_smoothing=[0.15, 0.05]).set_state(u, v, p)
+            s.step(2, freeze_pressure=(N % 2 == 0))
+            r = s.step(3, freeze_pressure=(N % 2 == 0))   # second call: state comes back from the rotated buffers
+            out[path] = (*s.get_state(), r)
+    for a, b in zip(out["stream_eo"][:3], out["tiled"][:3]):
+        assert rel(a, b) < 1e-10
+    assert np.allclose(out["stream_eo"][3], out["tiled"][3], rtol=1e-8)
+    with ldc.BatchedSpectralLDC(N, batch=1) as s:
+        assert s.kernel_name == "k_stream_stage"   # the default path for these sizes
+
+
+def test_streamed_solve_stops_converged_cavities(ldc):
+    """ldc_solve on the streamed path: per-cavity convergence, iteration counts equal to the tiled path."""
+    N = 66
+    res = {}
+    for path in ("tiled", "stream_eo"):
+        with ldc.BatchedSpectralLDC(N, batch=2, path=path) as s:
+            s.set_cases([100.0, 400.0]).init_state()
+            r = s.solve([1e-2, 3e-3], 3000, warmup=0)
+            res[path] = (r.iterations.copy(), r.converged.copy(), s.get_state())
+    assert np.array_equal(res["tiled"][0], res["stream_eo"][0]) and res["tiled"][1].all() and res["stream_eo"][1].all()
+    assert res["tiled"][0][0] != res["tiled"][0][1]
+    for a, b in zip(res["stream_eo"][2], res["tiled"][2]):
+        assert rel(a, b) < 1e-10
+
+
 def test_error_paths(ldc):
     with pytest.raises(ValueError):
         ldc.BatchedSpectralLDC(1, batch=1)
