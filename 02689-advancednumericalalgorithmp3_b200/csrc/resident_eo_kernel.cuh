@@ -121,7 +121,7 @@ __device__ __forceinline__ void eo_from_points4(const double (&r)[4], double (&q
 template <int NT, int LD, int BLK, int HP, bool IS_U>
 __device__ __forceinline__ void eo_assemble(const double* __restrict__ sVec, const double* __restrict__ sEdgeF,
                                             const double* __restrict__ sU, const double* __restrict__ sV, double nu,
-                                            int r0, int c0, int g, int t, double (&a1)[4][NT][2],
+                                            bool bc_lines, int r0, int c0, int g, int t, double (&a1)[4][NT][2],
                                             double (&a2)[4][NT][2], double (&aL)[4][NT][2]) {
     // sVec: d0_S d0_A dN_S dN_A dd0_S dd0_A ddN_S ddN_A ; sEdgeF: W_S W_A E_S E_A S_S S_A N_S N_A (parity forms)
     const int i = r0 + g;
@@ -141,17 +141,33 @@ __device__ __forceinline__ void eo_assemble(const double* __restrict__ sVec, con
         for (int hh = 0; hh < 2; ++hh) {
             const int j = c0 + nt * 8 + 2 * t + hh;
             double dx[4], dy[4];
+            if (bc_lines) {
+                // the boundary lines are the boundary conditions (always, after the first stage): W = E = S = 0, so only
+                // the lid line N contributes, and only to the y-derivatives
 #pragma unroll
-            for (int b = 0; b < 2; ++b) {
-                const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
-                const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
-                const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+                for (int b = 0; b < 2; ++b) {
+                    const double dNj = sVec[(2 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
 #pragma unroll
-                for (int a = 0; a < 2; ++a) {
-                    const int q = 2 * a + b;
-                    dx[q] = a1[q][nt][hh] + d0i[a] * Wj + dNi[a] * Ej;
-                    dy[q] = a2[q][nt][hh] + Si[a] * d0j + Ni[a] * dNj;
-                    aL[q][nt][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                    for (int a = 0; a < 2; ++a) {
+                        const int q = 2 * a + b;
+                        dx[q] = a1[q][nt][hh];
+                        dy[q] = fma(Ni[a], dNj, a2[q][nt][hh]);
+                        aL[q][nt][hh] = fma(nu * Ni[a], ddNj, aL[q][nt][hh]);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
+                    const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
+                    const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a) {
+                        const int q = 2 * a + b;
+                        dx[q] = a1[q][nt][hh] + d0i[a] * Wj + dNi[a] * Ej;
+                        dy[q] = a2[q][nt][hh] + Si[a] * d0j + Ni[a] * dNj;
+                        aL[q][nt][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                    }
                 }
             }
             // convective term at the four mirror points, back to parity form

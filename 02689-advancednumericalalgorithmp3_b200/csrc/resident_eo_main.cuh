@@ -69,6 +69,20 @@ __global__ void __launch_bounds__(EoCfg<HP, NT>::THREADS, 1) k_resident_eo(const
             }
         }
         __syncthreads();
+        // do the stored boundary lines already equal the boundary conditions (bitwise)?  True for every visit but the
+        // first one after a load from a general state (cold start is BC-clean too).
+        bool bc_lines;
+        {
+            int dirty = 0;
+            for (int e = tid; e < ME; e += C::THREADS) {
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    const double* ed = sEdge + f * 4 * ME;
+                    dirty |= (ed[e] != 0.0) | (ed[ME + e] != 0.0) | (ed[2 * ME + e] != 0.0) | (ed[3 * ME + e] != sLid[f * ME + e]);
+                }
+            }
+            bc_lines = !__syncthreads_or(dirty);
+        }
         // parity forms of the eight boundary lines and of the lid line
         for (int e = tid; e < 10 * HP; e += C::THREADS) {
             const int line = e / HP, k = e % HP;
