@@ -97,6 +97,7 @@ struct ldc_handle {
     // streamed even-odd path (stream_eo.cuh): three rotating copies of the packed state + per-tile partial sums
     double* s_state = nullptr;
     double* s_partials = nullptr;
+    double* s_opsc = nullptr;     // per-cavity scaled operator copies
     bool canon_valid = true;      // u, v, p hold the current state
     int* q_data = nullptr;        // work queue of the resident kernel (resident.cuh: CavityQueue)
     unsigned* q_seq = nullptr;

@@ -256,6 +256,7 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
         A_(e_ops, eo_ops_size(ST_HP));
         A_(s_state, 3 * B * h->e_state_stride);
         A_(s_partials, B * ST_TILES * 8);
+        A_(s_opsc, B * 6 * ST_BLK);
     }
     if (rc == LDC_OK && cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
         rc = fail(LDC_ERR_CUDA, "ldc_create: cannot query the SM count");
@@ -279,7 +280,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -574,11 +575,17 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     const bool resident = kernel == 1 || kernel == 2, eo = kernel == 2;
     if (kernel == 3) {
         if ((rc = ensure_packed(h, 3))) return rc;
-        const size_t smem = ST_SMEM_DOUBLES * sizeof(double);
-        LDC_CUDA(cudaFuncSetAttribute(k_stream_stage, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // few CTAs (one per SM): double-buffer the chunk panels inside the CTA; many: two CTAs per SM overlap each other
+        const bool db = (long long)h->B * ST_TILES <= h->num_sms;
+        const size_t smem = st_smem_doubles(db) * sizeof(double);
+        if (db) LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
         StreamParams P;
         P.ops = h->e_ops;
+        P.opsc = h->s_opsc;
+        k_stream_scale_ops<<<dim3(32, h->B), 256, 0, h->stream>>>(h->e_ops, h->Re, h->s_opsc);
+        h->launches += 1;
         const size_t bs = (size_t)h->B * h->e_state_stride;
         P.buf[0] = h->s_state; P.buf[1] = h->s_state + bs; P.buf[2] = h->s_state + 2 * bs;
         P.stride = h->e_state_stride;
@@ -594,7 +601,8 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
             for (int stg = 0; stg < 4; ++stg) {
                 P.stage = stg;
                 P.bc_edges = (done == 0 && stg == 0) ? 0 : 1;
-                k_stream_stage<<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
+                if (db) k_stream_stage<true><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
+                else k_stream_stage<false><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
             }
             k_stream_end<<<h->B, 128, 0, h->stream>>>(P, done == 0 ? 1 : 0, tol_dev, warmup, max_iter, nan_exit, h->dx_min,
                                                        h->dy_min, h->dt);

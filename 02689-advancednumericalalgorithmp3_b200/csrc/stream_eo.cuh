@@ -18,12 +18,14 @@ constexpr int ST_PANEL = ST_T * ST_LDK;  // doubles per staged chunk panel (row-
 constexpr int ST_TILES = (ST_HP / ST_T) * (ST_HP / ST_T);
 constexpr int ST_THREADS = 128;          // 4 warps: (row half) x (u equation | v equation)
 constexpr int ST_ME = 2 * ST_HP;
-// shared memory: 36 chunk panels + boundary-column vectors (8 x HP) + boundary lines in parity form (16 x HP)
+// shared memory: 36 chunk panels (x 2 when double-buffered: few CTAs, one per SM; single-buffered two CTAs share an
+// SM and overlap each other's loads) + boundary-column vectors (8 x HP) + boundary lines in parity form (16 x HP)
 // + divergence exchange (2 x 16 x 32) + reduction scratch
-constexpr size_t ST_SMEM_DOUBLES = 36 * ST_PANEL + 8 * ST_HP + 16 * ST_HP + 2 * 16 * 32 + 32;
+constexpr size_t st_smem_doubles(bool db) { return (size_t)(db ? 2 : 1) * 36 * ST_PANEL + 8 * ST_HP + 16 * ST_HP + 2 * 16 * 32 + 32; }
 
 struct StreamParams {
     const double* ops;            // eo packed operators, HP = 64
+    const double* opsc;           // [B][6 blocks] per-cavity copies: D, nu DD, -G (cp.async sources)
     double* buf[3];               // rotating state buffers (eo packed records)
     size_t stride;                // doubles per cavity record
     const double *Re, *beta2, *CFL, *lidvel, *ulid, *vlid;
@@ -33,6 +35,22 @@ struct StreamParams {
     double* partials;             // [B][ST_TILES][8]: s0..s3, max|u|, max|v|
     int stage, freeze, bc_edges;  // bc_edges = 0: boundary lines as stored with phi^n (first stage after a load)
 };
+
+__device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+// per-cavity operator copies for the streamed kernel: D as is, DD scaled by nu = 1/Re, G negated
+__global__ void k_stream_scale_ops(const double* __restrict__ ops, const double* __restrict__ Re, double* __restrict__ opsc) {
+    const int b = blockIdx.y;
+    const double nu = 1.0 / Re[b];
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 6 * ST_BLK; e += gridDim.x * blockDim.x) {
+        const int blk = e / ST_BLK;
+        const double sc = blk < 2 ? 1.0 : (blk < 4 ? nu : -1.0);
+        opsc[(size_t)b * 6 * ST_BLK + e] = sc * ops[e];
+    }
+}
 
 __device__ __forceinline__ int st_in(int cur, int stage) { return stage == 0 ? cur : (stage == 2 ? (cur + 2) % 3 : (cur + 1) % 3); }
 __device__ __forceinline__ int st_out(int cur, int stage) { return (stage & 1) ? (cur + 2) % 3 : (cur + 1) % 3; }
@@ -140,7 +158,7 @@ namespace ldc {
 // d(field)/dy (!IS_U) blocks.
 template <bool IS_U>
 __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, const double* __restrict__ sEdgeF, double nu,
-                                            int i, int c0, int t, const double (&uo)[4][2][2], const double (&vo)[4][2][2],
+                                            bool bc_lines, int i, int c0, int t, const double (&uo)[4][2][2], const double (&vo)[4][2][2],
                                             double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int HP = ST_HP;
     double d0i[2], dNi[2], dd0i[2], ddNi[2], Si[2], Ni[2];
@@ -159,17 +177,31 @@ __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, con
         for (int hh = 0; hh < 2; ++hh) {
             const int j = c0 + nt * 8 + 2 * t + hh;
             double dx[4], dy[4];
+            if (bc_lines) {   // W = E = S = 0: only the lid line contributes, and only to the y-derivatives
 #pragma unroll
-            for (int b = 0; b < 2; ++b) {
-                const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
-                const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
-                const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+                for (int b = 0; b < 2; ++b) {
+                    const double dNj = sVec[(2 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
 #pragma unroll
-                for (int a = 0; a < 2; ++a) {
-                    const int q = 2 * a + b;
-                    dx[q] = a1[q][nt][hh] + d0i[a] * Wj + dNi[a] * Ej;
-                    dy[q] = a2[q][nt][hh] + Si[a] * d0j + Ni[a] * dNj;
-                    aL[q][nt][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                    for (int a = 0; a < 2; ++a) {
+                        const int q = 2 * a + b;
+                        dx[q] = a1[q][nt][hh];
+                        dy[q] = fma(Ni[a], dNj, a2[q][nt][hh]);
+                        aL[q][nt][hh] = fma(nu * Ni[a], ddNj, aL[q][nt][hh]);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
+                    const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
+                    const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a) {
+                        const int q = 2 * a + b;
+                        dx[q] = a1[q][nt][hh] + d0i[a] * Wj + dNi[a] * Ej;
+                        dy[q] = a2[q][nt][hh] + Si[a] * d0j + Ni[a] * dNj;
+                        aL[q][nt][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                    }
                 }
             }
             double ur[4], vr[4], fx[4], fy[4], cv[4], cq[4];
@@ -188,11 +220,12 @@ __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, con
         }
 }
 
-// One RK stage of every active cavity: grid (ST_TILES, B), 128 threads.
-__global__ void __launch_bounds__(ST_THREADS, 2) k_stream_stage(const StreamParams P) {
+// One RK stage of every active cavity: grid (ST_TILES, B), 128 threads.  DB = double-buffered chunk panels.
+template <bool DB>
+__global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const StreamParams P) {
     extern __shared__ __align__(16) double smem[];
     double* sPan = smem;
-    double* sVec = sPan + 36 * ST_PANEL;
+    double* sVec = sPan + (DB ? 2 : 1) * 36 * ST_PANEL;
     double* sEdgeP = sVec + 8 * ST_HP;
     double* sX = sEdgeP + 16 * ST_HP;
     double* sRed = sX + 2 * 16 * 32;
@@ -242,40 +275,42 @@ __global__ void __launch_bounds__(ST_THREADS, 2) k_stream_stage(const StreamPara
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
 
-    // ---- K loop: stage 36 chunk panels, contract ----
+    // ---- K loop: the 36 chunk panels arrive by cp.async into two alternating buffers while the previous chunk is
+    // contracted (operators come pre-scaled per cavity from P.opsc: D, nu DD, -G) ----
     const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
-    for (int k0 = 0; k0 < P.K4; k0 += ST_KC) {
-        __syncthreads();   // previous chunk fully consumed (also orders the sVec / sEdgeP writes before their use)
+    const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
+    auto issue = [&](int k0, double* buf) {
 #pragma unroll
         for (int p = 0; p < 36; ++p) {
             const double* src;
-            double scale = 1.0;
-            if (p < 6) {            // operator rows at the tile rows
-                src = P.ops + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;
-                scale = (p == 2 || p == 3) ? nu : (p >= 4 ? -1.0 : 1.0);
-            } else if (p < 12) {    // operator rows at the tile columns
-                src = P.ops + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;
-                scale = (p == 8 || p == 9) ? nu : (p >= 10 ? -1.0 : 1.0);
-            } else if (p < 24) {    // row panels of u, v (stage input) and p
-                const double* rec = p < 20 ? recI : recP;
-                src = rec + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;
-            } else {                // column panels of u, v, p
-                const double* rec = p < 32 ? recI : recP;
-                src = rec + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;
-            }
-            double2 v2 = p < 12 ? __ldg(reinterpret_cast<const double2*>(src)) : __ldcg(reinterpret_cast<const double2*>(src));
-            v2.x *= scale;
-            v2.y *= scale;
-            *reinterpret_cast<double2*>(sPan + p * ST_PANEL + lr * ST_LDK + lc) = v2;
+            if (p < 6) src = opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;                 // operator rows at the tile rows
+            else if (p < 12) src = opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
+            else if (p < 24) src = (p < 20 ? recI : recP) + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;   // row panels
+            else src = (p < 32 ? recI : recP) + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;               // column panels
+            cp_async16(buf + p * ST_PANEL + lr * ST_LDK + lc, src);
         }
-        __syncthreads();
-        const int ksteps = min(ST_KC, P.K4 - k0) / 4;
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const int nchunks = (P.K4 + ST_KC - 1) / ST_KC;
+    issue(0, sPan);
+    for (int c = 0; c < nchunks; ++c) {
+        double* cur_buf = sPan + (DB ? (c & 1) * 36 * ST_PANEL : 0);
+        if (DB && c + 1 < nchunks) {
+            issue((c + 1) * ST_KC, sPan + ((c + 1) & 1) * 36 * ST_PANEL);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();   // chunk c has landed for every thread (also orders the sVec / sEdgeP writes before their use)
+        const int ksteps = min(ST_KC, P.K4 - c * ST_KC) / 4;
         if (fld == 0)
-            st_chunk<true>(sPan, sPan + 6 * ST_PANEL, sPan + 12 * ST_PANEL, sPan + 24 * ST_PANEL, sPan + 20 * ST_PANEL,
-                           sPan + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+            st_chunk<true>(cur_buf, cur_buf + 6 * ST_PANEL, cur_buf + 12 * ST_PANEL, cur_buf + 24 * ST_PANEL,
+                           cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
         else
-            st_chunk<false>(sPan, sPan + 6 * ST_PANEL, sPan + 16 * ST_PANEL, sPan + 28 * ST_PANEL, sPan + 20 * ST_PANEL,
-                            sPan + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+            st_chunk<false>(cur_buf, cur_buf + 6 * ST_PANEL, cur_buf + 16 * ST_PANEL, cur_buf + 28 * ST_PANEL,
+                            cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+        __syncthreads();   // chunk c consumed: its buffer may be refilled by the next issue
+        if (!DB && c + 1 < nchunks) issue((c + 1) * ST_KC, sPan);
     }
 
     // ---- epilogue: the thread's own elements of all four blocks ----
@@ -291,8 +326,8 @@ __global__ void __launch_bounds__(ST_THREADS, 2) k_stream_stage(const StreamPara
             uo[q][nt][0] = a.x; uo[q][nt][1] = a.y;
             vo[q][nt][0] = c.x; vo[q][nt][1] = c.y;
         }
-    if (fld == 0) st_assemble<true>(sVec, sEdgeP, nu, i, c0, t, uo, vo, a1, a2, aL);
-    else st_assemble<false>(sVec, sEdgeP + 8 * ST_HP, nu, i, c0, t, uo, vo, a1, a2, aL);
+    if (fld == 0) st_assemble<true>(sVec, sEdgeP, nu, P.bc_edges != 0, i, c0, t, uo, vo, a1, a2, aL);
+    else st_assemble<false>(sVec, sEdgeP + 8 * ST_HP, nu, P.bc_edges != 0, i, c0, t, uo, vo, a1, a2, aL);
 
     const double adt = rk_alpha(P.stage) * P.dt[b];
     const bool last = (P.stage == 3);
