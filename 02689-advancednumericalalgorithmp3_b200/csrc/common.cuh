@@ -105,6 +105,11 @@ struct ldc_handle {
     int num_sms = 0;
     int res_slots = 0;            // CTAs of the resident kernel the chip holds at once
 
+    // per-iteration history of ldc_solve_history: [B][hist_cap][7] records + the quadrature weights
+    double* hist = nullptr;
+    size_t hist_cap = 0;
+    double* Wq = nullptr;
+
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_ms = 0.0;
     int64_t launches = 0;

@@ -280,7 +280,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->hist, h->Wq};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -724,6 +724,70 @@ int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int fre
     } else {
         k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
         h->launches += 1;
+    }
+    return export_status(h, iters, converged, diverged, rel_res, nullptr);
+}
+
+int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t max_iter, int warmup, int freeze_pressure,
+                      int nan_exit, const double* W, double* hist, int64_t hist_cap, int64_t* iters, int32_t* converged,
+                      int32_t* diverged, double* rel_res) {
+    int rc = check_ready(h, "ldc_solve_history");
+    if (rc) return rc;
+    if (!tol || !W || !hist || hist_cap < 1 || start_iter < 0 || max_iter < start_iter || warmup < 0)
+        return fail(LDC_ERR_INVALID, "ldc_solve_history: bad argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    const size_t nf = (size_t)h->n1x * h->n1y, B = h->B;
+    if (!h->Wq && (rc = dalloc(&h->Wq, nf))) return rc;
+    if (h->hist_cap < (size_t)hist_cap) {
+        if (h->hist) cudaFree(h->hist);
+        h->hist = nullptr;
+        h->hist_cap = 0;
+        if ((rc = dalloc(&h->hist, B * (size_t)hist_cap * HIST_W))) return rc;
+        h->hist_cap = (size_t)hist_cap;
+    }
+    if ((rc = copy_in(h, h->tol, tol, B))) return rc;
+    if ((rc = copy_in(h, h->Wq, W, nf))) return rc;
+    if ((rc = ensure_canonical(h))) return rc;
+    h->packed_valid = 0;
+    LDC_CUDA(cudaMemsetAsync(h->hist, 0, B * h->hist_cap * HIST_W * sizeof(double), h->stream));
+    if (start_iter == 0) {
+        k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 1;
+    }
+    LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
+    const long long end = std::min<long long>(max_iter, start_iter + hist_cap);
+    const int nfull = (int)nf, ninner = h->mx * h->my;
+    for (long long it = start_iter; it < end; ++it) {
+        launch_tiled_step(h, freeze_pressure ? 1 : 0, warmup, max_iter, nan_exit ? 1 : 0, h->tol);
+        const long long slot = it - start_iter;
+        // h->Ru, Rv, Rp still hold the last stage's residual (what the reference's arrays.R_* hold after step())
+        k_hist_norms<<<h->B, RED_THREADS, 0, h->stream>>>(h->Ru, h->Rv, h->Rp, nfull, ninner, h->status, it, slot, h->hist_cap,
+                                                         h->hist);
+        k_vorticity<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(h->u, h->v, h->Dx, h->DyT, h->pfull, h->n1x,
+                                                                              h->n1y);
+        k_hist_diag<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->pfull, h->Dx, h->DyT, h->Wq, h->n1x, h->n1y, h->status,
+                                                        it, slot, h->hist_cap, h->hist);
+        h->launches += 3;
+        if ((slot + 1) % 256 == 0 && it + 1 < end) {
+            LDC_CUDA(cudaGetLastError());
+            int na = 0;
+            if ((rc = count_active(h, &na))) return rc;
+            if (na == 0) break;
+        }
+    }
+    LDC_CUDA(cudaEventRecord(h->ev1, h->stream));
+    LDC_CUDA(cudaEventSynchronize(h->ev1));
+    float ms = 0;
+    LDC_CUDA(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    h->last_ms = ms;
+    LDC_CUDA(cudaGetLastError());
+    if (h->hist_cap == (size_t)hist_cap) {
+        if ((rc = copy_out(h, hist, h->hist, B * h->hist_cap * HIST_W * sizeof(double)))) return rc;
+    } else {
+        for (size_t b = 0; b < B; ++b)
+            if ((rc = copy_out(h, hist + b * (size_t)hist_cap * HIST_W, h->hist + b * h->hist_cap * HIST_W,
+                               (size_t)hist_cap * HIST_W * sizeof(double))))
+                return rc;
     }
     return export_status(h, iters, converged, diverged, rel_res, nullptr);
 }

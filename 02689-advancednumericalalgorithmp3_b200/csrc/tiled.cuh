@@ -327,6 +327,71 @@ k_diagnostics(const double* __restrict__ u, const double* __restrict__ v, const 
     }
 }
 
+// ---- per-iteration history (base.solve, base.py:243-313) ----------------------------------------------------------
+// One record per cavity and iteration: [rel_iter, ||R_u||, ||R_v||, ||R_p||, E, Z, P].  `it` is the 0-based index of the
+// iteration that has just been taken; a cavity records iff it took that step (status.iters == it + 1).
+constexpr int HIST_W = 7;
+
+// rel_iter = max(u_res, v_res) (Python max: first wins unless the second is strictly greater) and the norms of the LAST
+// stage's residual on all nodes, as _compute_algebraic_residuals reads them from arrays.R_* (spectral/sg.py:463-473).
+__global__ void __launch_bounds__(RED_THREADS)
+k_hist_norms(const double* __restrict__ Ru, const double* __restrict__ Rv, const double* __restrict__ Rp, int nfull,
+             int ninner, const CavityStatus* __restrict__ status, long long it, long long slot, size_t cap,
+             double* __restrict__ hist) {
+    __shared__ double sh[3 * 32];
+    const int b = blockIdx.x;
+    if (status[b].iters != it + 1) return;
+    double s[3] = {0, 0, 0};
+    for (int e = threadIdx.x; e < nfull; e += blockDim.x) {
+        const double a = Ru[(size_t)b * nfull + e], c = Rv[(size_t)b * nfull + e];
+        s[0] = fma(a, a, s[0]);
+        s[1] = fma(c, c, s[1]);
+    }
+    for (int e = threadIdx.x; e < ninner; e += blockDim.x) {
+        const double a = Rp[(size_t)b * ninner + e];
+        s[2] = fma(a, a, s[2]);
+    }
+    block_reduce<3, false>(s, sh);
+    if (threadIdx.x == 0) {
+        double* r = hist + ((size_t)b * cap + slot) * HIST_W;
+        const double ur = status[b].u_res, vr = status[b].v_res;
+        r[0] = (vr > ur) ? vr : ur;
+        r[1] = sqrt(s[0]);
+        r[2] = sqrt(s[1]);
+        r[3] = sqrt(s[2]);
+    }
+}
+
+// E, Z, P of the new state (spectral/sg.py:495-550); om = vorticity from k_vorticity.
+__global__ void __launch_bounds__(RED_THREADS)
+k_hist_diag(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ om,
+            const double* __restrict__ Dx, const double* __restrict__ DyT, const double* __restrict__ W, int n1x, int n1y,
+            const CavityStatus* __restrict__ status, long long it, long long slot, size_t cap, double* __restrict__ hist) {
+    __shared__ double sh[3 * 32];
+    const int b = blockIdx.x;
+    if (status[b].iters != it + 1) return;
+    const int nfull = n1x * n1y;
+    const size_t off = (size_t)b * nfull;
+    double s[3] = {0, 0, 0};
+    for (int e = threadIdx.x; e < nfull; e += blockDim.x) {
+        const int i = e / n1y, j = e % n1y;
+        double gx = 0, gy = 0;
+        for (int k = 0; k < n1x; ++k) gx = fma(Dx[i * n1x + k], om[off + k * n1y + j], gx);
+        for (int k = 0; k < n1y; ++k) gy = fma(om[off + i * n1y + k], DyT[k * n1y + j], gy);
+        const double w = W[e], uu = u[off + e], vv = v[off + e], oo = om[off + e];
+        s[0] += w * (uu * uu + vv * vv);
+        s[1] += w * oo * oo;
+        s[2] += w * (gx * gx + gy * gy);
+    }
+    block_reduce<3, false>(s, sh);
+    if (threadIdx.x == 0) {
+        double* r = hist + ((size_t)b * cap + slot) * HIST_W;
+        r[4] = 0.5 * s[0];
+        r[5] = 0.5 * s[1];
+        r[6] = 0.5 * s[2];
+    }
+}
+
 // u = v = p = 0 then the lid column.
 __global__ void k_init_state(double* __restrict__ u, double* __restrict__ v, double* __restrict__ p,
                              const double* __restrict__ ulid, const double* __restrict__ vlid, int n1x, int n1y) {

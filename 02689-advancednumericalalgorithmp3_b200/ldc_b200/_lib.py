@@ -33,6 +33,8 @@ SIGNATURES = {
     "ldc_residual": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "ldc_step": (C.c_int, [_vp, C.c_int64, C.c_int, _vp]),
     "ldc_solve": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]),
+    "ldc_solve_history": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int64, _vp, _vp,
+                                    _vp, _vp]),
     "ldc_diagnostics": (C.c_int, [_vp, _vp, _vp]),
     "ldc_prolongate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "ldc_restrict": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),

@@ -189,6 +189,41 @@ class BatchedSpectralLDC:
                                       _lib.ptr(rel)), "ldc_solve")
         return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, self.last_kernel_ms)
 
+    def solve_history(self, tolerance, max_iter: int, warmup: int = 10, freeze_pressure: bool = True,
+                      nan_exit: bool = False, chunk: int = 8192):
+        """`solve` with the per-iteration records of base.solve (base.py:243-313).
+
+        Returns (SolveResult, history) where history[b] is an (iterations_b, 7) array, one row per iteration taken:
+        rel_iter, ||R_u||, ||R_v||, ||R_p|| (last stage's residual), energy, enstrophy, palinstrophy.  The solve is
+        streamed through `ldc_solve_history` in chunks of `chunk` iterations so that host and device memory stay
+        bounded whatever max_iter is.
+        """
+        tol = _per_case(tolerance, self.B, "tolerance")
+        iters = np.zeros(self.B, dtype=np.int64)
+        conv = np.zeros(self.B, dtype=np.int32)
+        divg = np.zeros(self.B, dtype=np.int32)
+        rel = np.zeros(self.B)
+        W = np.ascontiguousarray(self.level.W)
+        chunk = int(max(1, min(chunk, max_iter)))
+        buf = np.zeros((self.B, chunk, 7))
+        rows = [[] for _ in range(self.B)]
+        start, ms = 0, 0.0
+        while start < max_iter:
+            _lib.check(self.lib.ldc_solve_history(self._h, _lib.ptr(tol), start, int(max_iter), int(warmup),
+                                                  int(bool(freeze_pressure)), int(bool(nan_exit)), _lib.ptr(W),
+                                                  _lib.ptr(buf), chunk, _lib.ptr(iters), _lib.ptr(conv), _lib.ptr(divg),
+                                                  _lib.ptr(rel)), "ldc_solve_history")
+            ms += self.last_kernel_ms
+            for b in range(self.B):
+                taken = int(min(iters[b], start + chunk)) - start
+                if taken > 0:
+                    rows[b].append(buf[b, :taken].copy())
+            start += chunk
+            if not np.any((iters >= start) & (conv == 0) & (divg == 0)):
+                break
+        hist = [np.concatenate(r) if r else np.zeros((0, 7)) for r in rows]
+        return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, ms), hist
+
     def diagnostics(self):
         """[B,3] = (energy, enstrophy, palinstrophy)."""
         out = np.empty((self.B, 3))

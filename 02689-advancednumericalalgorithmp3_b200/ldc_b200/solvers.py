@@ -6,8 +6,10 @@ and `solvers.spectral.fsg.FSGSolver` (src/solvers/spectral/fsg.py:19-129), so `m
 main.py:75-120) can instantiate them through Hydra's `_target_` unchanged.  The numerics of `solve()` run in
 the CUDA library through the C ABI (one cavity = a batch of one); nothing here falls back to the CPU.
 
-Beyond the reference surface, both classes accept `device=` (CUDA device index, default 0) -- optional, so the
-reference's YAML files stay valid.
+Beyond the reference surface, both classes accept `device=` (CUDA device index, default 0) and `history=`
+(default True: `SGSolver.solve` records the reference's per-iteration TimeSeries, base.py:243-313, on the
+launch-per-stage path; False: the resident DMMA kernel runs the whole solve and the TimeSeries holds the final
+record only) -- both optional, so the reference's YAML files stay valid.
 """
 from __future__ import annotations
 
@@ -32,7 +34,10 @@ class SGSolver:
 
     Parameters = SpectralParameters
 
-    def __init__(self, params=None, device: int = 0, **kwargs):
+    MAX_TIMESERIES_POINTS = 1000  # base.py:100 (_store_results default)
+
+    def __init__(self, params=None, device: int = 0, history: bool = True, **kwargs):
+        self.history = bool(history)
         if params is None:
             params = self.Parameters(**kwargs)  # unknown key -> TypeError, as in the reference (base.py:47-52)
         self.params = params
@@ -152,7 +157,12 @@ class SGSolver:
         g = self._batch()
         t0 = time.time()
         self._push_state()
-        r = g.solve(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
+        hist = None
+        if self.history:
+            r, hists = g.solve_history(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
+            hist = hists[0][10:]  # base.py:262: records are kept for i >= 10 only
+        else:
+            r = g.solve(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
         diverged = bool(r.diverged[0])
         # the reference has no NaN exit on this path: it keeps stepping NaNs until max_iter
         iters = int(max_iter) if diverged else int(r.iterations[0])
@@ -160,13 +170,31 @@ class SGSolver:
         wall = time.time() - t0
         norms = self._pull_residuals()
         E, Z, Pal = g.diagnostics()[0]
-        self._store_results(float(r.rel_residual[0]), iters, bool(r.converged[0]), wall, norms, (E, Z, Pal))
+        self._store_results(float(r.rel_residual[0]), iters, bool(r.converged[0]), wall, norms, (E, Z, Pal), hist)
 
-    def _store_results(self, rel, iters, converged, wall, norms, ezp):
+    @classmethod
+    def _downsample(cls, col):
+        """base.py:137-141: at most MAX_TIMESERIES_POINTS entries, picked at linspace(0, L-1, ., dtype=int)."""
+        col = [float(x) for x in col]
+        if len(col) <= cls.MAX_TIMESERIES_POINTS:
+            return col
+        idx = np.linspace(0, len(col) - 1, cls.MAX_TIMESERIES_POINTS, dtype=int)
+        return [col[i] for i in idx]
+
+    def _store_results(self, rel, iters, converged, wall, norms, ezp, hist=None):
         self._finalize_fields()
-        self.time_series = TimeSeries(rel_iter_residual=[rel], u_residual=[float(norms[0])], v_residual=[float(norms[1])],
-                                      continuity_residual=[float(norms[2])], energy=[float(ezp[0])],
-                                      enstrophy=[float(ezp[1])], palinstrophy=[float(ezp[2])])
+        if hist is not None:
+            # base.py:125-153: the full per-iteration history, down-sampled; Metrics take the FINAL (not sampled) values
+            cols = [self._downsample(hist[:, k]) for k in range(7)]
+            self.time_series = TimeSeries(*cols)
+            if len(hist):
+                rel, norms, ezp = float(hist[-1, 0]), hist[-1, 1:4], hist[-1, 4:7]
+            else:
+                rel, norms, ezp = float("inf"), (0.0, 0.0, 0.0), (0.0, 0.0, 0.0)
+        else:
+            self.time_series = TimeSeries(rel_iter_residual=[rel], u_residual=[float(norms[0])],
+                                          v_residual=[float(norms[1])], continuity_residual=[float(norms[2])],
+                                          energy=[float(ezp[0])], enstrophy=[float(ezp[1])], palinstrophy=[float(ezp[2])])
         try:
             vm = self.compute_vortex_metrics()
         except Exception as e:  # base.py:156-160 swallows these too

@@ -101,6 +101,17 @@ int ldc_step(ldc_t* h, int64_t n_steps, int freeze_pressure, double* rel);
 int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit,
               int64_t* iters, int32_t* converged, int32_t* diverged, double* rel_res);
 
+/* base.solve with its per-iteration records (base.py:243-313): ldc_solve on the launch-per-stage path, and after every
+ * iteration i (0-based) of a cavity, hist[b][i - start_iter][7] = { rel_iter = max(u_res, v_res), ||R_u||, ||R_v||, ||R_p||
+ * of the LAST stage's residual on all nodes (what arrays.R_* hold after step(), spectral/sg.py:463-473), energy,
+ * enstrophy, palinstrophy of the new state with quadrature weights W[(nx+1)][(ny+1)] (spectral/sg.py:495-550) }.
+ * The call takes at most hist_cap iterations: the caller streams a long solve in chunks, start_iter = 0 starts a solve
+ * (status reset), start_iter > 0 continues the previous call of this handle (iters keeps counting; max_iter is absolute).
+ * Rows of iterations a cavity did not take stay zero; the reference keeps rows i >= 10 only (base.py:262-276). */
+int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t max_iter, int warmup, int freeze_pressure,
+                      int nan_exit, const double* W, double* hist, int64_t hist_cap, int64_t* iters, int32_t* converged,
+                      int32_t* diverged, double* rel_res);
+
 /* Energy, enstrophy, palinstrophy with quadrature weights W[(nx+1)][(ny+1)]
  * (spectral/sg.py:495-550); out is [batch][3]. */
 int ldc_diagnostics(ldc_t* h, const double* W, double* out);

@@ -423,7 +423,8 @@ def solve_sg(N: int, case: Case, tol: float, max_iter: int, Lx=1.0, Ly=1.0, hist
         ur, vr, Ru, Rv, Rp = rk4_step(lv, u, v, p, case, u_lid, v_lid, freeze_pressure=True)
         rel = max(ur, vr)
         if history:
-            hist.append((rel, np.linalg.norm(Ru), np.linalg.norm(Rv), np.linalg.norm(Rp)))
+            # base.py:258-276: residual norms of the LAST stage's residual, then E, Z, P of the new state
+            hist.append((rel, np.linalg.norm(Ru), np.linalg.norm(Rv), np.linalg.norm(Rp)) + tuple(diagnostics(lv, u, v)))
         conv = (i >= 10) and (rel < tol)
         if conv:
             break

@@ -1,0 +1,87 @@
+"""Per-iteration TimeSeries of `solver=spectral/sg` (base.py:243-313, 125-153).
+CPU: the oracle against the reference-minted fixture and the down-sampling rule.  GPU: ldc_solve_history through the
+drop-in SGSolver against the same fixture (tolerance 1e-9 relative on every record, iteration count exact)."""
+import numpy as np
+import pytest
+
+KW = dict(name="spectral", Re=100.0, lid_velocity=1.0, Lx=1.0, Ly=1.0, nx=16, ny=16, tolerance=1e-6,
+          max_iterations=10_000_000, basis_type="chebyshev", CFL=1.5, beta_squared=5.0, corner_treatment="smoothing",
+          corner_smoothing=0.15, multigrid="none")
+
+
+def relcols(a, b):
+    return np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300), axis=0)
+
+
+def test_oracle_history_matches_reference(golden):
+    from oracle import ldc_oracle as orc
+
+    g = golden.history
+    out = orc.solve_sg(16, orc.Case(Re=100.0), 1e-6, 40, history=True)
+    h = out["history"][10:]
+    assert h.shape == g["short_series"].shape == (30, 7)
+    assert relcols(h, g["short_series"]).max() < 1e-11
+
+
+def test_downsample_rule():
+    import sys
+
+    from ldc_b200.solvers import SGSolver
+
+    col = np.arange(14145, dtype=float)
+    out = SGSolver._downsample(col)
+    assert len(out) == 1000 and out[0] == 0.0 and out[-1] == 14144.0
+    assert out == [float(i) for i in np.linspace(0, 14144, 1000, dtype=int)]
+    assert SGSolver._downsample(col[:1000]) == list(col[:1000])
+
+
+@pytest.mark.gpu
+def test_short_history_matches_reference(built_lib, golden):
+    g = golden.history
+    s = built_lib.SGSolver(**KW)
+    s.solve(max_iter=40)
+    ts = s.time_series
+    got = np.array([ts.rel_iter_residual, ts.u_residual, ts.v_residual, ts.continuity_residual, ts.energy, ts.enstrophy,
+                    ts.palinstrophy]).T
+    assert got.shape == (30, 7)
+    assert relcols(got, g["short_series"]).max() < 1e-10
+    assert s.metrics.iterations == int(g["short_iterations"]) and not s.metrics.converged
+    s.close()
+
+
+@pytest.mark.gpu
+def test_full_history_and_metrics_match_reference(built_lib, golden):
+    g = golden.history
+    s = built_lib.SGSolver(**KW)
+    s.solve()
+    meta = g["full_meta"]
+    assert s.metrics.iterations == int(meta[0]) and s.metrics.converged
+    ts = s.time_series
+    got = np.array([ts.rel_iter_residual, ts.u_residual, ts.v_residual, ts.continuity_residual, ts.energy, ts.enstrophy,
+                    ts.palinstrophy]).T
+    assert got.shape == g["full_series"].shape == (1000, 7)
+    # the trajectory is contractive: records agree to ~1e-12 early and stay within 1e-8 relative of the tiny late residuals
+    assert relcols(got, g["full_series"]).max() < 1e-8
+    m = s.metrics
+    mine = np.array([m.final_residual, m.u_momentum_residual, m.v_momentum_residual, m.continuity_residual, m.final_energy,
+                     m.final_enstrophy, m.final_palinstrophy])
+    assert np.max(np.abs(mine - meta[2:]) / np.abs(meta[2:])) < 1e-8
+    # chunked streaming (several ldc_solve_history calls) gives the same records as one call
+    with built_lib.BatchedSpectralLDC(16, batch=2) as b:
+        b.set_cases([100.0, 150.0]).init_state()
+        r1, h1 = b.solve_history(1e-4, 3000, chunk=4096)
+        b.init_state()
+        r2, h2 = b.solve_history(1e-4, 3000, chunk=250)
+        assert np.array_equal(r1.iterations, r2.iterations) and r1.iterations[0] != r1.iterations[1]
+        for a, c, it in zip(h1, h2, r1.iterations):
+            assert a.shape == (it, 7) and np.array_equal(a, c)
+    s.close()
+
+
+@pytest.mark.gpu
+def test_history_off_uses_the_resident_kernel(built_lib, golden):
+    s = built_lib.SGSolver(history=False, **KW)
+    s.solve()
+    assert s.metrics.iterations == int(golden.history["full_meta"][0])
+    assert len(s.time_series.rel_iter_residual) == 1
+    s.close()
