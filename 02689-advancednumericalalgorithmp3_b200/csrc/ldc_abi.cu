@@ -10,6 +10,7 @@
 #include "resident_main.cuh"
 #include "stream_eo.cuh"
 #include "tiled.cuh"
+#include "validate.cuh"
 
 namespace ldc {
 thread_local std::string g_last_error;
@@ -817,6 +818,55 @@ int ldc_diagnostics(ldc_t* h, const double* W, double* out) {
         cudaStreamSynchronize(h->stream);
         cudaFree(tmpW);
     }
+    return rc;
+}
+
+int ldc_validation_errors(ldc_t* h, int64_t nq, const int32_t* cell, const double* tx, const double* ty, const int32_t* mask,
+                          const double* ref_u, const double* ref_v, double* out) {
+    int rc = check_ready(h, "ldc_validation_errors");
+    if (rc) return rc;
+    if (nq < 0 || !out || (nq > 0 && (!cell || !tx || !ty || !mask || !ref_u || !ref_v)))
+        return fail(LDC_ERR_INVALID, "ldc_validation_errors: bad argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = ensure_canonical(h))) return rc;
+    const size_t n = (size_t)std::max<int64_t>(nq, 1), B = h->B;
+    // one scratch block: tx ty ref_u ref_v [n doubles each] | partial [B][CHUNKS][5] | out [B][3] | cell mask [n ints each]
+    double* d = nullptr;
+    const size_t nd = 4 * n + B * VAL_CHUNKS * 5 + B * 3;
+    LDC_CUDA(cudaMalloc((void**)&d, nd * sizeof(double) + 2 * n * sizeof(int)));
+    double *dtx = d, *dty = d + n, *dru = d + 2 * n, *drv = d + 3 * n, *dpart = d + 4 * n, *dout = dpart + B * VAL_CHUNKS * 5;
+    int *dcell = reinterpret_cast<int*>(d + nd), *dmask = dcell + n;
+    // host pointers are range-checked here (a bad cell index would read outside the state arrays)
+    if (nq > 0 && !is_device_ptr(cell)) {
+        const int lim = (h->n1x - 1) * h->n1y;
+        for (int64_t q = 0; q < nq; ++q)
+            if (mask[q] && (cell[q] < 0 || cell[q] >= lim || cell[q] % h->n1y == h->n1y - 1)) {
+                cudaFree(d);
+                return fail(LDC_ERR_INVALID, "ldc_validation_errors: cell index outside the grid");
+            }
+    }
+    rc = LDC_OK;
+    if (nq > 0) {
+        if (!rc) rc = copy_in(h, dtx, tx, nq);
+        if (!rc) rc = copy_in(h, dty, ty, nq);
+        if (!rc) rc = copy_in(h, dru, ref_u, nq);
+        if (!rc) rc = copy_in(h, drv, ref_v, nq);
+        const cudaMemcpyKind kind = is_device_ptr(cell) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        if (!rc && (cudaMemcpyAsync(dcell, cell, nq * sizeof(int), kind, h->stream) != cudaSuccess ||
+                    cudaMemcpyAsync(dmask, mask, nq * sizeof(int), kind, h->stream) != cudaSuccess ||
+                    cudaStreamSynchronize(h->stream) != cudaSuccess))
+            rc = fail(LDC_ERR_CUDA, "ldc_validation_errors: copy of the point plan failed");
+    }
+    if (!rc) {
+        k_val_partial<<<dim3(VAL_CHUNKS, h->B), RED_THREADS, 0, h->stream>>>(h->u, h->v, h->n1x * h->n1y, h->n1y, nq, dcell, dtx,
+                                                                           dty, dmask, dru, drv, dpart);
+        k_val_final<<<(h->B + 127) / 128, 128, 0, h->stream>>>(dpart, h->B, dout);
+        h->launches += 2;
+        if (cudaGetLastError() != cudaSuccess) rc = fail(LDC_ERR_CUDA, "ldc_validation_errors: launch failed");
+    }
+    if (!rc) rc = copy_out(h, out, dout, B * 3 * sizeof(double));
+    cudaStreamSynchronize(h->stream);
+    cudaFree(d);
     return rc;
 }
 

@@ -36,6 +36,7 @@ SIGNATURES = {
     "ldc_solve_history": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int64, _vp, _vp,
                                     _vp, _vp]),
     "ldc_diagnostics": (C.c_int, [_vp, _vp, _vp]),
+    "ldc_validation_errors": (C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ldc_prolongate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "ldc_restrict": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "ldc_launch_count": (C.c_int64, [_vp]),

@@ -231,6 +231,20 @@ class BatchedSpectralLDC:
         _lib.check(self.lib.ldc_diagnostics(self._h, _lib.ptr(W), _lib.ptr(out)), "ldc_diagnostics")
         return out
 
+    def validation_errors(self, plan, ref_u, ref_v):
+        """[B,3] = (u_L2_error, v_L2_error, n_valid) against a stored solution at scattered points
+        (compute_validation_errors, base.py:970-1054); `plan` is a `validation.BilinearPlan` for this grid."""
+        ref_u = np.ascontiguousarray(ref_u, dtype=np.float64).ravel()
+        ref_v = np.ascontiguousarray(ref_v, dtype=np.float64).ravel()
+        nq = plan.cell.size
+        if not (ref_u.size == ref_v.size == plan.tx.size == plan.ty.size == plan.mask.size == nq):
+            raise ValueError("plan and reference arrays must have one entry per point")
+        out = np.empty((self.B, 3))
+        _lib.check(self.lib.ldc_validation_errors(self._h, nq, _lib.ptr(plan.cell), _lib.ptr(plan.tx), _lib.ptr(plan.ty),
+                                                  _lib.ptr(plan.mask), _lib.ptr(ref_u), _lib.ptr(ref_v), _lib.ptr(out)),
+                   "ldc_validation_errors")
+        return out
+
     def prolongate_to(self, fine: "BatchedSpectralLDC", method: str = "fft", bc_quirk: bool = True):
         """Coarse -> fine initial guess (prolongate_solution, multigrid/fsg.py:551-614)."""
         Pxu = np.ascontiguousarray(ops.prolongation_matrix(self.nx + 1, fine.nx + 1, method))

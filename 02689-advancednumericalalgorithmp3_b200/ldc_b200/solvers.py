@@ -149,6 +149,16 @@ class SGSolver:
         """Streamfunction-based vortex metrics (sg.py:556-743) by tensor-product fast diagonalisation."""
         return streamfunction_vortex_metrics(self.level, self.u_2d, self.v_2d)
 
+    def compute_validation_errors(self, reference_dir: str = "data/validation/fv", save_plots: bool = True) -> dict:
+        """L2 errors against the stored FV solutions (base.py:970-1054) -- PyVista-free: the .vts files are parsed by
+        `ldc_b200.vts` and the bilinear evaluation + norms run on the device.  As in the reference, `reference_dir` is
+        accepted but the two directories data/validation/{fv,fv-regu} (relative to the working directory) are the ones
+        read.  The error-distribution plots (matplotlib, base.py:1056-1120) are not produced here."""
+        from .validation import compute_validation_errors
+
+        self._push_state()
+        return compute_validation_errors(self._batch(), self.params.Re)
+
     def solve(self, tolerance: float = None, max_iter: int = None):
         """base.solve (base.py:202-330) for the spectral single grid: iterate SGSolver.step until
         max(||du||/(||u||+1e-12), same for v) < tolerance after a 10-iteration warm-up."""

@@ -116,6 +116,16 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
  * (spectral/sg.py:495-550); out is [batch][3]. */
 int ldc_diagnostics(ldc_t* h, const double* W, double* out);
 
+/* compute_validation_errors (base.py:970-1054) for every cavity of the handle: u, v are evaluated at nq scattered points by
+ * bilinear interpolation on the collocation grid (_evaluate_at_points base.py:1122-1160: SciPy RegularGridInterpolator,
+ * method="linear") and compared with a stored solution (ref_u, ref_v) [nq]:
+ *   out[b] = { ||u - ref_u|| / (||ref_u|| + 1e-12), same for v, number of points used }
+ * over the points with mask != 0 whose interpolated values are not NaN.  The caller supplies the interpolation plan, shared
+ * by the batch: cell[q] = ix * (ny+1) + iy of the lower grid node of the cell holding point q, tx, ty = normalised
+ * distances inside that cell; mask[q] = 0 drops a point (outside the domain, or within 1e-10 of the walls, base.py:1022-1027). */
+int ldc_validation_errors(ldc_t* h, int64_t nq, const int32_t* cell, const double* tx, const double* ty, const int32_t* mask,
+                          const double* ref_u, const double* ref_v, double* out);
+
 /* Coarse -> fine transfer of (u, v, p): U_f = Px U_c Py^T with dense 1-D maps
  * Pxu (nfx+1)x(ncx+1), Pyu (nfy+1)x(ncy+1), Pxp (nfx-1)x(ncx-1), Pyp (nfy-1)x(ncy-1)
  * (prolongate_solution multigrid/fsg.py:551-614).  bc_quirk=1 reproduces the reference's

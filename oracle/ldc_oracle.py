@@ -378,6 +378,28 @@ def diagnostics(lv: Level, u, v):
     return E, Z, P
 
 
+def evaluate_at_points(lv: Level, u, v, xq, yq):
+    """Bilinear evaluation of u, v at scattered points, as the reference does it (base.py:1122-1160): the fields are
+    re-laid out as (y, x) and handed to SciPy's RegularGridInterpolator(method="linear", fill_value=nan)."""
+    from scipy.interpolate import RegularGridInterpolator
+
+    pts = np.column_stack([yq, xq])
+    fu = RegularGridInterpolator((lv.y, lv.x), np.ascontiguousarray(u.T), method="linear", bounds_error=False, fill_value=np.nan)
+    fv = RegularGridInterpolator((lv.y, lv.x), np.ascontiguousarray(v.T), method="linear", bounds_error=False, fill_value=np.nan)
+    return fu(pts), fv(pts)
+
+
+def validation_errors(lv: Level, u, v, xq, yq, ref_u, ref_v, Lx=1.0, Ly=1.0):
+    """(u_L2_error, v_L2_error, n_valid) against a stored solution.  base.py:1015-1040."""
+    cu, cv = evaluate_at_points(lv, u, v, xq, yq)
+    margin = 1e-10
+    interior = (xq > margin) & (xq < Lx - margin) & (yq > margin) & (yq < Ly - margin)
+    valid = interior & ~(np.isnan(cu) | np.isnan(cv))
+    eu = np.linalg.norm(cu[valid] - ref_u[valid]) / (np.linalg.norm(ref_u[valid]) + 1e-12)
+    ev = np.linalg.norm(cv[valid] - ref_v[valid]) / (np.linalg.norm(ref_v[valid]) + 1e-12)
+    return float(eu), float(ev), int(np.sum(valid))
+
+
 def extrapolate_pressure(p: np.ndarray) -> np.ndarray:
     """Inner (m x m) -> full (n x n) by linear extrapolation; corners = mean of two neighbours.
     spectral/sg.py:144-179."""
