@@ -113,7 +113,7 @@ def test_solver_compute_validation_errors(built_lib, golden, tmp_path, monkeypat
     pts = np.column_stack([g["x"], g["y"], np.zeros(g["x"].size)])
     vts.write_vts(str(d / "solution.vts"), pts, (128, 128, 1), {"u": g["ref_u"], "v": g["ref_v"]})
     monkeypatch.chdir(tmp_path)
-    s = built_lib.FSGSolver(name="spectral_fsg", Re=100.0, nx=24, ny=24, tolerance=1e-6, max_iterations=10, n_levels=2,
+    s = built_lib.FSGSolver(name="spectral_fsg", Re=100.0, nx=24, ny=24, basis_type="chebyshev", max_iterations=10, n_levels=2,
                             multigrid="fsg")
     s.arrays.u[:] = g["u"].ravel()
     s.arrays.v[:] = g["v"].ravel()
