@@ -97,9 +97,14 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
     if device is None:
         device = torch.cuda.current_device() if torch.cuda.is_available() else 0
     fn = local_solver or (solve_fsg_batched if kind == "fsg" else solve_sg_batched)
+    # per-cavity keyword inputs (beta_squared, CFL, lid_velocity arrays; a list of corner treatments) follow the shard
+    local_kw = {}
+    for k, val in solver_kw.items():
+        per_case = not isinstance(val, str) and np.ndim(val) == 1 and len(val) == Re.size
+        local_kw[k] = (list(val[lo:hi]) if isinstance(val, (list, tuple)) else np.asarray(val)[lo:hi]) if per_case else val
     n1 = N + 1
     if hi > lo:
-        r: FSGResult = fn(N, Re[lo:hi], tol[lo:hi], max_iter, corner_smoothing=cs[lo:hi], device=device, **solver_kw)
+        r: FSGResult = fn(N, Re[lo:hi], tol[lo:hi], max_iter, corner_smoothing=cs[lo:hi], device=device, **local_kw)
     else:  # more ranks than cavities
         z = np.zeros
         r = FSGResult(z((0, n1, n1)), z((0, n1, n1)), z((0, N - 1, N - 1)), z(0, dtype=np.int64), z(0, dtype=bool),

@@ -30,6 +30,9 @@ def _fake_solver(N, Re, tol, max_iter, *, corner_smoothing, device, **kw):
     v = corner_smoothing[:, None, None] * base
     p = (Re + corner_smoothing)[:, None, None] * np.ones((N - 1, N - 1))
     div = Re > 900
+    if "CFL" in kw:  # per-cavity keyword inputs must arrive sliced like Re
+        assert np.shape(kw["CFL"]) == Re.shape and len(kw["corner_treatment"]) == B
+        p = p + np.asarray(kw["CFL"])[:, None, None]
     return FSGResult(u, v, p, (10 * Re).astype(np.int64), ~div, div, np.where(div, np.nan, 1e-7 * Re), kernel_ms=float(B))
 
 
@@ -43,7 +46,8 @@ def _worker(rank, world, port, B, q):
     try:
         Re = np.linspace(100, 1000, B)
         cs = np.linspace(0.02, 0.35, B)
-        r = solve_sweep(6, Re, cs, 1e-6, 100, fields="rank0", local_solver=_fake_solver)
+        kw = dict(CFL=np.linspace(1.0, 2.0, B), corner_treatment=["smoothing"] * B, n_levels=2) if B == 5 else {}
+        r = solve_sweep(6, Re, cs, 1e-6, 100, fields="rank0", local_solver=_fake_solver, **kw)
         q.put((rank, r.iterations, r.converged, r.diverged, r.rel_residual, None if r.u is None else r.u.copy(),
                None if r.p is None else r.p.copy(), r.kernel_ms, r.bounds))
     finally:
@@ -68,7 +72,8 @@ def test_sweep_sharded_over_two_gloo_ranks_equals_unsharded(B):
         assert p.exitcode == 0
     Re = np.linspace(100, 1000, B)
     cs = np.linspace(0.02, 0.35, B)
-    ref = _fake_solver(6, Re, None, 100, corner_smoothing=cs, device=0)
+    kw = dict(CFL=np.linspace(1.0, 2.0, B), corner_treatment=["smoothing"] * B, n_levels=2) if B == 5 else {}
+    ref = _fake_solver(6, Re, None, 100, corner_smoothing=cs, device=0, **kw)
     for rank, it, conv, div, rel, u, p, kms, bounds in got:
         assert np.array_equal(it, ref.iterations) and np.array_equal(conv, ref.converged) and np.array_equal(div, ref.diverged)
         assert np.array_equal(np.isnan(rel), np.isnan(ref.rel_residual))
