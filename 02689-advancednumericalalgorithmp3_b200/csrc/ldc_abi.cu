@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "peak.cuh"
 #include "resident_eo_main.cuh"
+#include "resident_eo_split.cuh"
 #include "resident_main.cuh"
 #include "stream_eo.cuh"
 #include "tiled.cuh"
@@ -152,18 +153,37 @@ static bool eo_ok(const ldc_handle* h) {
     return eo_smem_bytes(h->HP) <= (size_t)max_optin;
 }
 
+// equation-split variant (resident_eo_split.cuh): small grids only, the base state stays in shared memory too
+static size_t eo_split_smem_bytes(int HP) {
+    switch (HP) {
+        case 8: return EoSplitCfg<8>::smem_doubles() * sizeof(double);
+        case 16: return EoSplitCfg<16>::smem_doubles() * sizeof(double);
+        case 24: return EoSplitCfg<24>::smem_doubles() * sizeof(double);
+    }
+    return 0;
+}
+static bool eo_split_ok(const ldc_handle* h) {
+    if (!eo_ok(h) || h->HP > 24) return false;
+    int max_optin = 0;
+    if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return false;
+    return eo_split_smem_bytes(h->HP) <= (size_t)max_optin;
+}
+
 static bool stream_shape_ok(const ldc_handle* h) {
     const int hh = eo_half(h->mx);
     return h->nx == h->ny && hh > 32 && hh <= ST_HP;
 }
 static bool stream_ok(const ldc_handle* h) { return stream_shape_ok(h) && h->square_ops; }
 
-// 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd
+// 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd, 4 even-odd resident split by equation
 static int pick_kernel(const ldc_handle* h) {
     if (h->path == LDC_PATH_TILED) return 0;
+    if (h->path == LDC_PATH_RESIDENT_EO_SPLIT) return eo_split_ok(h) ? 4 : -1;
     if (h->path == LDC_PATH_RESIDENT) return resident_ok(h) ? 1 : -1;
     if (h->path == LDC_PATH_RESIDENT_EO) return eo_ok(h) ? 2 : -1;
     if (h->path == LDC_PATH_STREAM_EO) return stream_ok(h) ? 3 : -1;
+    // few cavities on a small grid: latency matters, spread each cavity over twice the warps
+    if (eo_split_ok(h) && h->B <= h->num_sms) return 4;
     if (eo_ok(h)) return 2;
     if (resident_ok(h)) return 1;
     return stream_ok(h) ? 3 : 0;
@@ -295,7 +315,9 @@ void ldc_destroy(ldc_t* h) {
 }
 
 int ldc_set_path(ldc_t* h, int path) {
-    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_STREAM_EO) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT_EO_SPLIT) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (path == LDC_PATH_RESIDENT_EO_SPLIT && !(eo_shape_ok(h) && eo_pick_hp(h->mx) <= 24))
+        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the equation-split even-odd path needs nx == ny and nx - 1 <= 48");
     if (path == LDC_PATH_STREAM_EO && !stream_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the streamed even-odd path needs nx == ny and 66 <= nx <= 128");
     if (path == LDC_PATH_RESIDENT_EO && !eo_shape_ok(h))
@@ -318,6 +340,7 @@ const char* ldc_kernel_name(const ldc_t* h) {
         case 1: return "k_resident_rk4";
         case 2: return "k_resident_eo";
         case 3: return "k_stream_stage";
+        case 4: return "k_resident_eo_split";
     }
     return "unsupported";
 }
@@ -554,6 +577,43 @@ static int launch_eo(ldc_handle* h, const ResParams& P) {
     return fail(LDC_ERR_UNSUPPORTED, "even-odd resident path: unsupported padded size");
 }
 
+template <int HP>
+static int eo_split_slots_t(ldc_handle* h) {
+    using C = EoSplitCfg<HP>;
+    const size_t bytes = C::smem_doubles() * sizeof(double);
+    LDC_CUDA(cudaFuncSetAttribute(k_resident_eo_split<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int per_sm = 0;
+    LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resident_eo_split<HP>, C::THREADS, bytes));
+    h->res_slots = std::max(1, per_sm) * h->num_sms;
+    return LDC_OK;
+}
+static int eo_split_slots(ldc_handle* h) {
+    switch (h->HP) {
+        case 8: return eo_split_slots_t<8>(h);
+        case 16: return eo_split_slots_t<16>(h);
+        case 24: return eo_split_slots_t<24>(h);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "equation-split even-odd path: unsupported padded size");
+}
+template <int HP>
+static int launch_eo_split_t(ldc_handle* h, const ResParams& P) {
+    using C = EoSplitCfg<HP>;
+    const size_t bytes = C::smem_doubles() * sizeof(double);
+    k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
+    k_resident_eo_split<HP><<<std::min(h->B, h->res_slots), C::THREADS, bytes, h->stream>>>(P);
+    h->launches += 2;
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+static int launch_eo_split(ldc_handle* h, const ResParams& P) {
+    switch (h->HP) {
+        case 8: return launch_eo_split_t<8>(h, P);
+        case 16: return launch_eo_split_t<16>(h, P);
+        case 24: return launch_eo_split_t<24>(h, P);
+    }
+    return fail(LDC_ERR_UNSUPPORTED, "equation-split even-odd path: unsupported padded size");
+}
+
 static int launch_resident(ldc_handle* h, const ResParams& P) {
     switch (h->MP) {
         case 16: return launch_resident_t<16, 2, 2>(h, P);
@@ -573,7 +633,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     if (kernel < 0)
         return fail(LDC_ERR_UNSUPPORTED, "the requested resident path cannot run this shape (shared memory, or x / y "
                                          "operators differ for the even-odd kernel)");
-    const bool resident = kernel == 1 || kernel == 2, eo = kernel == 2;
+    const bool resident = kernel == 1 || kernel == 2 || kernel == 4, eo = kernel == 2 || kernel == 4, split = kernel == 4;
     if (kernel == 3) {
         if ((rc = ensure_packed(h, 3))) return rc;
         // few CTAs (one per SM): double-buffer the chunk panels inside the CTA; many: two CTAs per SM overlap each other
@@ -620,7 +680,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         k_stream_clear_pad<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
         h->launches += 2;
     } else if (resident) {
-        if ((rc = ensure_packed(h, kernel))) return rc;
+        if ((rc = ensure_packed(h, eo ? 2 : 1))) return rc;
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));  // device time of the stepping kernels only
         ResParams P;
         P.ops = eo ? h->e_ops : h->r_ops; P.square = h->square_ops ? 1 : 0;
@@ -631,7 +691,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         P.status = h->status; P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.freeze = freeze;
         P.max_iter = max_iter;
         P.q_data = h->q_data; P.q_seq = h->q_seq; P.q_ctl = h->q_ctl; P.B = h->B;
-        if ((rc = eo ? eo_slots(h) : resident_slots(h))) return rc;
+        if ((rc = split ? eo_split_slots(h) : (eo ? eo_slots(h) : resident_slots(h)))) return rc;
         // steps per launch (the host looks at the active count between launches)
         const long long chunk = h->mx >= 49 ? 1024 : (h->mx >= 33 ? 2048 : (h->mx >= 17 ? 4096 : 16384));
         h->canon_valid = false;
@@ -645,7 +705,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
                 const long long c = (L * h->B + 64LL * h->res_slots - 1) / (64LL * h->res_slots);
                 P.chunk = std::min(L, std::max(4LL, c));
             }
-            if ((rc = eo ? launch_eo(h, P) : launch_resident(h, P))) return rc;
+            if ((rc = split ? launch_eo_split(h, P) : (eo ? launch_eo(h, P) : launch_resident(h, P)))) return rc;
             if (done + chunk < max_iter) {
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;

@@ -43,8 +43,11 @@ enum {
     LDC_PATH_RESIDENT = 2,    /* state + operators resident in shared memory, FP64 DMMA, many steps per launch */
     LDC_PATH_RESIDENT_EO = 3, /* resident + even-odd (parity) splitting of the operators: half the DMMA work;
                                  needs nx == ny, identical x / y operators and nx - 1 <= 64 */
-    LDC_PATH_STREAM_EO = 4    /* even-odd, one cavity spread over 16 CTAs, operands streamed from L2, one launch per
+    LDC_PATH_STREAM_EO = 4,   /* even-odd, one cavity spread over 16 CTAs, operands streamed from L2, one launch per
                                  RK stage: for 66 <= nx <= 128 (e.g. N = 128); nx == ny, identical x / y operators */
+    LDC_PATH_RESIDENT_EO_SPLIT = 5 /* resident even-odd with the u and v equations of a tile on different warps and the
+                                 base state in shared memory: lower latency per step for few cavities on small grids
+                                 (nx - 1 <= 48); AUTO picks it when batch <= #SM */
 };
 
 /* Library / build information: "ldc_b200 <version> sm_100a". */
@@ -60,7 +63,7 @@ int ldc_set_path(ldc_t* h, int path);
 /* 0 when the resident DMMA path can run this handle's shape, else LDC_ERR_UNSUPPORTED. */
 int ldc_resident_supported(const ldc_t* h);
 /* Name of the stepping kernel ldc_step / ldc_solve launch for this handle with its current path and operators:
- * "k_resident_eo", "k_resident_rk4", "k_stream_stage", "tiled" (or "unsupported" when the forced path cannot run the shape). */
+ * "k_resident_eo", "k_resident_eo_split", "k_resident_rk4", "k_stream_stage", "tiled" (or "unsupported" when the forced path cannot run the shape). */
 const char* ldc_kernel_name(const ldc_t* h);
 
 /* 1-D operators shared by every cavity of the handle (host or device pointers, row-major):

@@ -26,6 +26,10 @@ def fstep(N):
 CASES = [(64, 256, 400), (64, 148, 400), (64, 1024, 200), (48, 512, 400), (32, 1024, 1000), (30, 1, 2000), (16, 2048, 2000)]
 BIG = [(128, 8, 100), (128, 64, 50), (96, 64, 100)]
 RUNS = [(p, c) for c in CASES for p in ("resident", "resident_eo")] + [(p, c) for c in BIG for p in ("tiled", "stream_eo")]
+SMALL = [(30, 1, 4000), (30, 16, 2000), (30, 148, 2000), (30, 296, 2000), (30, 1024, 1000), (15, 1, 4000), (48, 1, 2000), (48, 148, 1000),
+         (16, 2048, 2000), (32, 1024, 1000)]
+if len(sys.argv) > 1 and sys.argv[1] == "small":
+    RUNS = [(p, c) for c in SMALL for p in ("resident_eo", "resident_eo_split")]
 if len(sys.argv) > 1 and sys.argv[1] == "big":
     RUNS = [(p, c) for c in BIG for p in ("tiled", "stream_eo")]
 for path, (N, B, K) in RUNS:
