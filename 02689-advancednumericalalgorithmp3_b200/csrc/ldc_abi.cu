@@ -183,7 +183,7 @@ static int pick_kernel(const ldc_handle* h) {
     if (h->path == LDC_PATH_RESIDENT_EO) return eo_ok(h) ? 2 : -1;
     if (h->path == LDC_PATH_STREAM_EO) return stream_ok(h) ? 3 : -1;
     // few cavities on a small grid: latency matters, spread each cavity over twice the warps
-    if (eo_split_ok(h) && h->B <= h->num_sms) return 4;
+    if (eo_split_ok(h) && h->HP <= 16 && h->B <= h->num_sms) return 4;   // measured: no gain at HP = 24
     if (eo_ok(h)) return 2;
     if (resident_ok(h)) return 1;
     return stream_ok(h) ? 3 : 0;

@@ -47,7 +47,7 @@ enum {
                                  RK stage: for 66 <= nx <= 128 (e.g. N = 128); nx == ny, identical x / y operators */
     LDC_PATH_RESIDENT_EO_SPLIT = 5 /* resident even-odd with the u and v equations of a tile on different warps and the
                                  base state in shared memory: lower latency per step for few cavities on small grids
-                                 (nx - 1 <= 48); AUTO picks it when batch <= #SM */
+                                 (nx - 1 <= 48); AUTO picks it when nx - 1 <= 32 and batch <= #SM */
 };
 
 /* Library / build information: "ldc_b200 <version> sm_100a". */
