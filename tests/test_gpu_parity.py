@@ -342,3 +342,27 @@ def test_fsgsolver_class_is_a_drop_in(ldc, golden):
     assert m.final_residual == pytest.approx(meta[2])  # tol when converged (fsg.py:107-114)
     assert np.allclose([m.u_momentum_residual, m.v_momentum_residual, m.continuity_residual], meta[3:6], rtol=1e-7)
     s.close()
+
+
+def test_full_bench_batch_properties(ldc):
+    """BASELINE config 3 at full size (256 cavities, N=64, Re jitter): size-independent properties of the default path --
+    every cavity's trajectory equals its solo run bit for bit, the batch stays finite, and per-cavity residuals drop."""
+    N, B, K = 64, 256, 30
+    Re = 400.0 * (1 + 0.05 * np.random.default_rng(0).uniform(-1, 1, B))
+    with ldc.BatchedSpectralLDC(N, batch=B) as s:
+        assert s.kernel_name == "k_resident_eo"
+        s.set_cases(Re).init_state()
+        r0 = s.step(K)
+        u, v, p = s.get_state()
+        r1 = s.step(K)
+    assert np.isfinite(u).all() and np.isfinite(v).all() and np.isfinite(p).all()
+    assert np.all(r1.max(axis=1) < r0.max(axis=1))
+    for b in (0, 100, 255):
+        with ldc.BatchedSpectralLDC(N, batch=1, path="resident_eo") as s:
+            s.set_cases(Re[b]).init_state()
+            s.step(K)
+            u1, v1, p1 = s.get_state()
+        assert np.array_equal(u[b], u1[0]) and np.array_equal(v[b], v1[0]) and np.array_equal(p[b], p1[0]), b
+    # lid and wall boundary conditions hold exactly on every cavity
+    assert not u[:, 0, :].any() and not u[:, -1, :].any() and not u[:, :, 0].any() and not v[:, :, -1].any()
+    assert np.allclose(u[:, 10:-10, -1], 1.0)
