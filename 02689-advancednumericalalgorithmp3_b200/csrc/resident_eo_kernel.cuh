@@ -170,19 +170,28 @@ __device__ __forceinline__ void eo_assemble(const double* __restrict__ sVec, con
                     }
                 }
             }
-            // convective term at the four mirror points, back to parity form
+            // Convective term u dF/dx + v dF/dy directly in parity form.  The four parity blocks are the coefficients of
+            // the characters of Z2 x Z2 (mirror in x, mirror in y), so a pointwise product is the group convolution
+            //   (f g)_q = sum_b f_{q xor b} g_b :  32 FMAs per element and no transform to the mirror points and back.
             const int o = i * LD + j;
-            double ur[4], vr[4], fx[4], fy[4], cv[4], cq[4];
-            eo_to_points(sU[o], sU[BLK + o], sU[2 * BLK + o], sU[3 * BLK + o], ur);
-            eo_to_points(sV[o], sV[BLK + o], sV[2 * BLK + o], sV[3 * BLK + o], vr);
-            eo_to_points(dx[0], dx[1], dx[2], dx[3], fx);
-            eo_to_points(dy[0], dy[1], dy[2], dy[3], fy);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) cv[q] = ur[q] * fx[q] + vr[q] * fy[q];
-            eo_from_points4(cv, cq);
+            double uq[4], vq[4], cq[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                aL[q][nt][hh] = fma(-0.25, cq[q], aL[q][nt][hh]);   // R = lin - conv
+                uq[q] = sU[q * BLK + o];
+                vq[q] = sV[q * BLK + o];
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                double c = uq[q] * dx[0];
+#pragma unroll
+                for (int b = 1; b < 4; ++b) c = fma(uq[q ^ b], dx[b], c);
+#pragma unroll
+                for (int b = 0; b < 4; ++b) c = fma(vq[q ^ b], dy[b], c);
+                cq[q] = c;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                aL[q][nt][hh] -= cq[q];                              // R = lin - conv
                 a1[q][nt][hh] = IS_U ? dx[q] : dy[q];                // the divergence part of this field
             }
         }

@@ -204,17 +204,20 @@ __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, con
                     }
                 }
             }
-            double ur[4], vr[4], fx[4], fy[4], cv[4], cq[4];
-            eo_to_points(uo[0][nt][hh], uo[1][nt][hh], uo[2][nt][hh], uo[3][nt][hh], ur);
-            eo_to_points(vo[0][nt][hh], vo[1][nt][hh], vo[2][nt][hh], vo[3][nt][hh], vr);
-            eo_to_points(dx[0], dx[1], dx[2], dx[3], fx);
-            eo_to_points(dy[0], dy[1], dy[2], dy[3], fy);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) cv[q] = ur[q] * fx[q] + vr[q] * fy[q];
-            eo_from_points4(cv, cq);
+            // convective term in parity form: Z2 x Z2 group convolution (see eo_assemble)
+            double cq[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                aL[q][nt][hh] = fma(-0.25, cq[q], aL[q][nt][hh]);
+                double c = uo[q][nt][hh] * dx[0];
+#pragma unroll
+                for (int bb = 1; bb < 4; ++bb) c = fma(uo[q ^ bb][nt][hh], dx[bb], c);
+#pragma unroll
+                for (int bb = 0; bb < 4; ++bb) c = fma(vo[q ^ bb][nt][hh], dy[bb], c);
+                cq[q] = c;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                aL[q][nt][hh] -= cq[q];
                 a1[q][nt][hh] = IS_U ? dx[q] : dy[q];
             }
         }

@@ -365,4 +365,4 @@ def test_full_bench_batch_properties(ldc):
         assert np.array_equal(u[b], u1[0]) and np.array_equal(v[b], v1[0]) and np.array_equal(p[b], p1[0]), b
     # lid and wall boundary conditions hold exactly on every cavity
     assert not u[:, 0, :].any() and not u[:, -1, :].any() and not u[:, :, 0].any() and not v[:, :, -1].any()
-    assert np.allclose(u[:, 10:-10, -1], 1.0)
+    assert np.all(u[:, 20:-20, -1] == 1.0)   # the unsmoothed middle of the lid
