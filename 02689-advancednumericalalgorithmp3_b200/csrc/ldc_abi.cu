@@ -1,6 +1,7 @@
 // C ABI of ldc_b200 (include/ldc_b200.h): handle management, host<->device plumbing and the launch
 // sequences of the tiled and resident kernel paths.  No exception crosses the boundary.
 #include <algorithm>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -653,21 +654,24 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
         P.dt = h->dt; P.n1 = h->n1x; P.m = h->mx; P.K4 = (eo_half(h->mx) + 3) / 4 * 4;
         P.status = h->status; P.partials = h->s_partials; P.freeze = freeze;
+        P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.max_iter = max_iter;
+        P.dx_min = h->dx_min; P.dy_min = h->dy_min;
         k_stream_begin<<<h->B, 256, 0, h->stream>>>(h->s_state, h->e_state_stride, h->mx, h->Re, h->beta2, h->CFL, h->lidvel,
                                                     h->dx_min, h->dy_min, h->dt, h->status);
         h->launches += 1;
         h->canon_valid = false;
         const long long chunk = 256;
         for (long long done = 0; done < max_iter; ++done) {
+            P.first = done == 0 ? 1 : 0;
             for (int stg = 0; stg < 4; ++stg) {
                 P.stage = stg;
                 P.bc_edges = (done == 0 && stg == 0) ? 0 : 1;
                 if (db) k_stream_stage<true><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
                 else k_stream_stage<false><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
             }
-            k_stream_end<<<h->B, 128, 0, h->stream>>>(P, done == 0 ? 1 : 0, tol_dev, warmup, max_iter, nan_exit, h->dx_min,
-                                                       h->dy_min, h->dt);
-            h->launches += 5;
+            h->launches += 4;
+            k_stream_end<<<h->B, ST_THREADS, 0, h->stream>>>(P);
+            h->launches += 1;
             if ((done + 1) % chunk == 0 && done + 1 < max_iter) {
                 LDC_CUDA(cudaGetLastError());
                 int na = 0;

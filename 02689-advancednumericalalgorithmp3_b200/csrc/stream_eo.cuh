@@ -29,11 +29,16 @@ struct StreamParams {
     double* buf[3];               // rotating state buffers (eo packed records)
     size_t stride;                // doubles per cavity record
     const double *Re, *beta2, *CFL, *lidvel, *ulid, *vlid;
-    const double* dt;             // [B]
+    double* dt;                   // [B]
     int n1, m, K4;
     CavityStatus* status;         // status.pad = index of the buffer holding phi^n
     double* partials;             // [B][ST_TILES][8]: s0..s3, max|u|, max|v|
     int stage, freeze, bc_edges;  // bc_edges = 0: boundary lines as stored with phi^n (first stage after a load)
+    // end-of-step bookkeeping (k_stream_end)
+    const double* tol;            // [B] or null
+    int first, warmup, nan_exit;  // first = 1: first step after a load (boundary lines as stored)
+    long long max_iter;
+    double dx_min, dy_min;
 };
 
 __device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc) {
@@ -223,6 +228,78 @@ __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, con
         }
 }
 
+// End of an RK4 step: reduce the tile partials in fixed order, add the boundary lines, convergence bookkeeping,
+// next dt, rotate the buffers and store the boundary-condition lines with the new state.
+// 128 threads per cavity; sh = 32 doubles of reduction scratch, shp = ST_TILES x 6 doubles for the tile partials.
+__device__ __forceinline__ void stream_end_body(const StreamParams& P, int b, double* sh, double* shp) {
+    const int first = P.first, warmup = P.warmup, nan_exit = P.nan_exit;
+    const long long max_iter = P.max_iter;
+    const double dx_min = P.dx_min, dy_min = P.dy_min;
+    const double* tol = P.tol;
+    double* dt = P.dt;
+    CavityStatus st = P.status[b];
+    // the tile partials arrive in parallel (one L2 round trip); thread 0 adds them in fixed order below
+    const double* part = P.partials + (size_t)b * ST_TILES * 8;
+    for (int e = threadIdx.x; e < ST_TILES * 6; e += blockDim.x) shp[e] = __ldcg(part + (e / 6) * 8 + e % 6);
+    const int m = P.m, n1 = P.n1, cur = st.pad, nxt = (cur + 2) % 3;
+    const double* ed = P.buf[cur] + (size_t)b * P.stride + 12 * ST_BLK;   // boundary lines of phi^n
+    double* edn = P.buf[nxt] + (size_t)b * P.stride + 12 * ST_BLK;
+    const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
+    double s[4] = {0, 0, 0, 0}, bm[2] = {0, 0};
+    for (int e = threadIdx.x; e < m; e += blockDim.x) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double lid = (f ? vl : ul)[e + 1];
+            const double* L = ed + f * 4 * ST_ME;
+            const double w = first ? L[e] : 0.0, ea = first ? L[ST_ME + e] : 0.0, so = first ? L[2 * ST_ME + e] : 0.0;
+            const double no = first ? L[3 * ST_ME + e] : lid;
+            const double dn = lid - no;
+            s[2 * f] += w * w + ea * ea + so * so + dn * dn;
+            s[2 * f + 1] += w * w + ea * ea + so * so + no * no;
+            bm[f] = nanmax(bm[f], fabs(lid));
+            double* Ln = edn + f * 4 * ST_ME;
+            Ln[e] = 0.0; Ln[ST_ME + e] = 0.0; Ln[2 * ST_ME + e] = 0.0; Ln[3 * ST_ME + e] = lid;
+        }
+    }
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double* c = ed + 8 * ST_ME + 4 * f;   // c00 c0N cN0 cNN
+            const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
+            const double c0 = first ? c[0] : 0.0, c1 = first ? c[1] : l0, c2 = first ? c[2] : 0.0, c3 = first ? c[3] : lN;
+            const double d1 = l0 - c1, d3 = lN - c3;
+            s[2 * f] += c0 * c0 + d1 * d1 + c2 * c2 + d3 * d3;
+            s[2 * f + 1] += c0 * c0 + c1 * c1 + c2 * c2 + c3 * c3;
+            bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
+            double* cn = edn + 8 * ST_ME + 4 * f;
+            cn[0] = 0.0; cn[1] = l0; cn[2] = 0.0; cn[3] = lN;
+        }
+    }
+    // deterministic CTA reduction of the 4 sums + 2 maxima
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    cta_reduce<4>(s, bm, sh, warp, lane);
+    if (threadIdx.x == 0) {
+        double mx[2] = {0, 0};
+        for (int tl = 0; tl < ST_TILES; ++tl) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s[q] += shp[tl * 6 + q];
+            mx[0] = nanmax(mx[0], shp[tl * 6 + 4]);
+            mx[1] = nanmax(mx[1], shp[tl * 6 + 5]);
+        }
+        const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+        update_status(st, ures, vres, tol ? tol[b] : -1.0, warmup, max_iter, nan_exit);
+        st.umax = nanmax(mx[0], bm[0]);
+        st.vmax = nanmax(mx[1], bm[1]);
+        st.pad = nxt;
+        P.status[b] = st;
+        const double lidv = P.lidvel[b], b2 = P.beta2[b], nu = 1.0 / P.Re[b];
+        const double ua = (lidv > st.umax) ? lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
+        const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu / (dx_min * dx_min);
+        const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu / (dy_min * dy_min);
+        dt[b] = P.CFL[b] / (lam_x + lam_y);
+    }
+}
+
 // One RK stage of every active cavity: grid (ST_TILES, B), 128 threads.  DB = double-buffered chunk panels.
 template <bool DB>
 __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const StreamParams P) {
@@ -247,6 +324,24 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
     double* recO = P.buf[st_out(cur, P.stage)] + (size_t)b * P.stride;            // stage output
     const double* recP = P.freeze ? recN : recI;                                  // pressure operand
     const double nu = 1.0 / P.Re[b], beta2 = P.beta2[b];
+
+    // ---- K loop: the 36 chunk panels arrive by cp.async into two alternating buffers while the previous chunk is
+    // contracted (operators come pre-scaled per cavity from P.opsc: D, nu DD, -G) ----
+    const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
+    const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
+    auto issue = [&](int k0, double* buf) {
+#pragma unroll
+        for (int p = 0; p < 36; ++p) {
+            const double* src;
+            if (p < 6) src = opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;                 // operator rows at the tile rows
+            else if (p < 12) src = opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
+            else if (p < 24) src = (p < 20 ? recI : recP) + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;   // row panels
+            else src = (p < 32 ? recI : recP) + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;               // column panels
+            cp_async16(buf + p * ST_PANEL + lr * ST_LDK + lc, src);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const int nchunks = (P.K4 + ST_KC - 1) / ST_KC;
 
     // ---- boundary-column vectors and boundary lines in parity form ----
     for (int e = tid; e < 8 * ST_HP; e += ST_THREADS) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
@@ -278,23 +373,6 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
 
-    // ---- K loop: the 36 chunk panels arrive by cp.async into two alternating buffers while the previous chunk is
-    // contracted (operators come pre-scaled per cavity from P.opsc: D, nu DD, -G) ----
-    const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
-    const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
-    auto issue = [&](int k0, double* buf) {
-#pragma unroll
-        for (int p = 0; p < 36; ++p) {
-            const double* src;
-            if (p < 6) src = opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;                 // operator rows at the tile rows
-            else if (p < 12) src = opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
-            else if (p < 24) src = (p < 20 ? recI : recP) + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;   // row panels
-            else src = (p < 32 ? recI : recP) + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;               // column panels
-            cp_async16(buf + p * ST_PANEL + lr * ST_LDK + lc, src);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    const int nchunks = (P.K4 + ST_KC - 1) / ST_KC;
     issue(0, sPan);
     for (int c = 0; c < nchunks; ++c) {
         double* cur_buf = sPan + (DB ? (c & 1) * 36 * ST_PANEL : 0);
@@ -305,6 +383,23 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();   // chunk c has landed for every thread (also orders the sVec / sEdgeP writes before their use)
+        if (DB && c + 1 == nchunks) {
+            // Last chunk: the other panel buffer is idle.  The epilogue's operands (this thread's own elements of the
+            // stage input u, v, of phi^n of the warp's field and of p^n) are fetched into it now, behind the DMMAs.
+            double* ep = sPan + ((c + 1) & 1) * 36 * ST_PANEL;
+            const int ei = (r0 + wr + g) * ST_LD + c0 + 2 * t;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt) {
+                    const int sl = q * 2 + nt, e = ei + nt * 8;
+                    cp_async16(ep + ((0 + sl) * ST_THREADS + tid) * 2, recI + (size_t)q * ST_BLK + e);
+                    cp_async16(ep + ((8 + sl) * ST_THREADS + tid) * 2, recI + (size_t)(4 + q) * ST_BLK + e);
+                    cp_async16(ep + ((16 + sl) * ST_THREADS + tid) * 2, recN + (size_t)(4 * fld + q) * ST_BLK + e);
+                    if (fld == 0) cp_async16(ep + ((24 + sl) * ST_THREADS + tid) * 2, recN + (size_t)(8 + q) * ST_BLK + e);
+                }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
         const int ksteps = min(ST_KC, P.K4 - c * ST_KC) / 4;
         if (fld == 0)
             st_chunk<true>(cur_buf, cur_buf + 6 * ST_PANEL, cur_buf + 12 * ST_PANEL, cur_buf + 24 * ST_PANEL,
@@ -318,14 +413,20 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
 
     // ---- epilogue: the thread's own elements of all four blocks ----
     const int i = r0 + wr + g;
+    // prefetched operands (DB): each thread reads back what it copied itself, so wait_group is all the ordering needed
+    const double* ep = sPan + (nchunks & 1) * 36 * ST_PANEL;
+    if (DB) asm volatile("cp.async.wait_group 0;" ::: "memory");
     double uo[4][2][2], vo[4][2][2];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
             const int e = i * ST_LD + c0 + nt * 8 + 2 * t;
-            const double2 a = __ldcg(reinterpret_cast<const double2*>(recI + (size_t)q * ST_BLK + e));
-            const double2 c = __ldcg(reinterpret_cast<const double2*>(recI + (size_t)(4 + q) * ST_BLK + e));
+            const int sl = q * 2 + nt;
+            const double2 a = DB ? *reinterpret_cast<const double2*>(ep + ((0 + sl) * ST_THREADS + tid) * 2)
+                                 : __ldcg(reinterpret_cast<const double2*>(recI + (size_t)q * ST_BLK + e));
+            const double2 c = DB ? *reinterpret_cast<const double2*>(ep + ((8 + sl) * ST_THREADS + tid) * 2)
+                                 : __ldcg(reinterpret_cast<const double2*>(recI + (size_t)(4 + q) * ST_BLK + e));
             uo[q][nt][0] = a.x; uo[q][nt][1] = a.y;
             vo[q][nt][0] = c.x; vo[q][nt][1] = c.y;
         }
@@ -346,7 +447,8 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const size_t off = (size_t)(4 * fld + q) * ST_BLK + e;
-            const double2 f0 = __ldcg(reinterpret_cast<const double2*>(recN + off));
+            const double2 f0 = DB ? *reinterpret_cast<const double2*>(ep + ((16 + q * 2 + nt) * ST_THREADS + tid) * 2)
+                                  : __ldcg(reinterpret_cast<const double2*>(recN + off));
             fn[q][0] = f0.x + adt * aL[q][nt][0];
             fn[q][1] = f0.y + adt * aL[q][nt][1];
             if (last) {
@@ -378,7 +480,8 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const size_t off = (size_t)(8 + q) * ST_BLK + e;
-                const double2 p0 = __ldcg(reinterpret_cast<const double2*>(recN + off));
+                const double2 p0 = DB ? *reinterpret_cast<const double2*>(ep + ((24 + q * 2 + nt) * ST_THREADS + tid) * 2)
+                                      : __ldcg(reinterpret_cast<const double2*>(recN + off));
                 const double dv0 = a1[q][nt][0] + sX[(tw * 16 + (q * 2 + nt) * 2 + 0) * 32 + lane];
                 const double dv1 = a1[q][nt][1] + sX[(tw * 16 + (q * 2 + nt) * 2 + 1) * 32 + lane];
                 __stcg(reinterpret_cast<double2*>(recO + off),
@@ -464,73 +567,13 @@ __global__ void __launch_bounds__(256) k_stream_begin(const double* __restrict__
     }
 }
 
-// End of an RK4 step: reduce the tile partials in fixed order, add the boundary lines, convergence bookkeeping,
-// next dt, rotate the buffers and store the boundary-condition lines with the new state.
-__global__ void __launch_bounds__(128) k_stream_end(StreamParams P, int first, const double* __restrict__ tol, int warmup,
-                                                    long long max_iter, int nan_exit, double dx_min, double dy_min,
-                                                    double* __restrict__ dt) {
-    __shared__ double sh[6 * 32];
+// End of an RK4 step: one CTA per cavity.  (Folding this into the last stage-3 tile of each cavity was tried: the
+// inlined body cost the stage kernel 20 % at every batch size, see profiles/README.md visit 6.)
+__global__ void __launch_bounds__(ST_THREADS) k_stream_end(const StreamParams P) {
+    __shared__ double sh[32], shp[ST_TILES * 6];
     const int b = blockIdx.x;
-    CavityStatus st = P.status[b];
-    if (!st.active) return;
-    const int m = P.m, n1 = P.n1, cur = st.pad, nxt = (cur + 2) % 3;
-    const double* ed = P.buf[cur] + (size_t)b * P.stride + 12 * ST_BLK;   // boundary lines of phi^n
-    double* edn = P.buf[nxt] + (size_t)b * P.stride + 12 * ST_BLK;
-    const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
-    double s[4] = {0, 0, 0, 0}, bm[2] = {0, 0};
-    for (int e = threadIdx.x; e < m; e += blockDim.x) {
-#pragma unroll
-        for (int f = 0; f < 2; ++f) {
-            const double lid = (f ? vl : ul)[e + 1];
-            const double* L = ed + f * 4 * ST_ME;
-            const double w = first ? L[e] : 0.0, ea = first ? L[ST_ME + e] : 0.0, so = first ? L[2 * ST_ME + e] : 0.0;
-            const double no = first ? L[3 * ST_ME + e] : lid;
-            const double dn = lid - no;
-            s[2 * f] += w * w + ea * ea + so * so + dn * dn;
-            s[2 * f + 1] += w * w + ea * ea + so * so + no * no;
-            bm[f] = nanmax(bm[f], fabs(lid));
-            double* Ln = edn + f * 4 * ST_ME;
-            Ln[e] = 0.0; Ln[ST_ME + e] = 0.0; Ln[2 * ST_ME + e] = 0.0; Ln[3 * ST_ME + e] = lid;
-        }
-    }
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int f = 0; f < 2; ++f) {
-            const double* c = ed + 8 * ST_ME + 4 * f;   // c00 c0N cN0 cNN
-            const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
-            const double c0 = first ? c[0] : 0.0, c1 = first ? c[1] : l0, c2 = first ? c[2] : 0.0, c3 = first ? c[3] : lN;
-            const double d1 = l0 - c1, d3 = lN - c3;
-            s[2 * f] += c0 * c0 + d1 * d1 + c2 * c2 + d3 * d3;
-            s[2 * f + 1] += c0 * c0 + c1 * c1 + c2 * c2 + c3 * c3;
-            bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
-            double* cn = edn + 8 * ST_ME + 4 * f;
-            cn[0] = 0.0; cn[1] = l0; cn[2] = 0.0; cn[3] = lN;
-        }
-    }
-    // deterministic CTA reduction of the 4 sums + 2 maxima
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    cta_reduce<4>(s, bm, sh, warp, lane);
-    if (threadIdx.x == 0) {
-        double mx[2] = {0, 0};
-        const double* part = P.partials + (size_t)b * ST_TILES * 8;
-        for (int tl = 0; tl < ST_TILES; ++tl) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) s[q] += part[tl * 8 + q];
-            mx[0] = nanmax(mx[0], part[tl * 8 + 4]);
-            mx[1] = nanmax(mx[1], part[tl * 8 + 5]);
-        }
-        const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
-        update_status(st, ures, vres, tol ? tol[b] : -1.0, warmup, max_iter, nan_exit);
-        st.umax = nanmax(mx[0], bm[0]);
-        st.vmax = nanmax(mx[1], bm[1]);
-        st.pad = nxt;
-        P.status[b] = st;
-        const double lidv = P.lidvel[b], b2 = P.beta2[b], nu = 1.0 / P.Re[b];
-        const double ua = (lidv > st.umax) ? lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
-        const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu / (dx_min * dx_min);
-        const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu / (dy_min * dy_min);
-        dt[b] = P.CFL[b] / (lam_x + lam_y);
-    }
+    if (!P.status[b].active) return;
+    stream_end_body(P, b, sh, shp);
 }
 
 // After a run: move every cavity's record into buffer 0 so that the next run (or an unpack) finds it there.
