@@ -638,7 +638,9 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     if (kernel == 3) {
         if ((rc = ensure_packed(h, 3))) return rc;
         // few CTAs (one per SM): double-buffer the chunk panels inside the CTA; many: two CTAs per SM overlap each other
-        const bool db = (long long)h->B * ST_TILES <= h->num_sms;
+        // one CTA per SM, double-buffered panels + split-K warps: for few CTAs, and (measured, N = 128 B = 64: 153 k ->
+        // 171 k steps/s; N = 96: 355 k -> 341 k) whenever all 16 tiles of the padded blocks are in use
+        const bool db = (long long)h->B * ST_TILES <= h->num_sms || eo_half(h->mx) > 48;
         const size_t smem = st_smem_doubles(db) * sizeof(double);
         if (db) LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         else LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -666,7 +668,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
             for (int stg = 0; stg < 4; ++stg) {
                 P.stage = stg;
                 P.bc_edges = (done == 0 && stg == 0) ? 0 : 1;
-                if (db) k_stream_stage<true><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
+                if (db) k_stream_stage<true><<<dim3(ST_TILES, h->B), 2 * ST_THREADS, smem, h->stream>>>(P);
                 else k_stream_stage<false><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
             }
             h->launches += 4;

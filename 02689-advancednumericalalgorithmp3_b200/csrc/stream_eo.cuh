@@ -67,7 +67,7 @@ __device__ __forceinline__ int st_out(int cur, int stage) { return (stage & 1) ?
 template <bool P_LEFT>
 __device__ __forceinline__ void st_chunk(const double* __restrict__ sOa, const double* __restrict__ sOb,
                                          const double* __restrict__ sFa, const double* __restrict__ sFb,
-                                         const double* __restrict__ sPa, const double* __restrict__ sPb, int ksteps,
+                                         const double* __restrict__ sPa, const double* __restrict__ sPb, int ks0, int ks1,
                                          int wr, int g, int t, double (&a1)[4][2][2], double (&a2)[4][2][2],
                                          double (&aL)[4][2][2]) {
     constexpr int NT = 2;
@@ -75,7 +75,7 @@ __device__ __forceinline__ void st_chunk(const double* __restrict__ sOa, const d
     const int brow = g * ST_LDK + t;          // operator rows at the tile columns: Op[8 nt + g][k + t]
     const int bfld = t * ST_LDK + g;          // column-type panel: F[k + t][8 nt + g]
 #pragma unroll 1
-    for (int ks = 0; ks < ksteps; ++ks) {
+    for (int ks = ks0; ks < ks1; ++ks) {
         const int k0 = 4 * ks;
         double FA[4], FB[4][NT];
 #pragma unroll
@@ -300,9 +300,15 @@ __device__ __forceinline__ void stream_end_body(const StreamParams& P, int b, do
     }
 }
 
-// One RK stage of every active cavity: grid (ST_TILES, B), 128 threads.  DB = double-buffered chunk panels.
+// One RK stage of every active cavity: grid (ST_TILES, B).
+// DB = false (many CTAs, two per SM): 128 threads, single panel buffer, the two CTAs of an SM overlap each other.
+// DB = true (few CTAs, one per SM): double-buffered panels and 256 threads -- a second group of four warps takes the
+// upper half of the k-steps of every chunk (split-K), so that each SM sub-partition has two warps issuing DMMAs (one warp
+// alone is latency-bound: 25 instead of 16 cycles per DMMA, profiles/README.md visit 6); its accumulators are added to
+// the first group's through shared memory, in fixed order, and the first group runs the epilogue.
 template <bool DB>
-__global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const StreamParams P) {
+__global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) k_stream_stage(const StreamParams P) {
+    constexpr int NTHR = DB ? 2 * ST_THREADS : ST_THREADS;
     extern __shared__ __align__(16) double smem[];
     double* sPan = smem;
     double* sVec = sPan + (DB ? 2 : 1) * 36 * ST_PANEL;
@@ -314,8 +320,10 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
     const CavityStatus st = P.status[b];
     if (!st.active) return;
     const int tile = blockIdx.x, r0 = (tile / (ST_HP / ST_T)) * ST_T, c0 = (tile % (ST_HP / ST_T)) * ST_T;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    const int tw = warp & 1, fld = warp >> 1, wr = 8 * tw;
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int kgrp = DB ? (threadIdx.x >> 7) : 0;          // split-K group (DB only)
+    const int tid = threadIdx.x & (ST_THREADS - 1);         // thread index inside the group
+    const int warp = tid >> 5, tw = warp & 1, fld = warp >> 1, wr = 8 * tw;
     const int m = P.m, h = eo_half(m), centre = (m & 1) ? h - 1 : -1;
     if (r0 >= h || c0 >= h) return;   // tile lies in the zero padding of the blocks
     const int cur = st.pad;
@@ -332,6 +340,7 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
     auto issue = [&](int k0, double* buf) {
 #pragma unroll
         for (int p = 0; p < 36; ++p) {
+            if (DB && (p & 1) != kgrp) continue;   // each group fetches every other panel
             const double* src;
             if (p < 6) src = opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;                 // operator rows at the tile rows
             else if (p < 12) src = opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
@@ -344,8 +353,8 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
     const int nchunks = (P.K4 + ST_KC - 1) / ST_KC;
 
     // ---- boundary-column vectors and boundary lines in parity form ----
-    for (int e = tid; e < 8 * ST_HP; e += ST_THREADS) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
-    for (int e = tid; e < 8 * ST_HP; e += ST_THREADS) {
+    for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) {
         const int line = e / ST_HP, k = e % ST_HP;   // uW uE uS uN vW vE vS vN
         double x = 0.0, y = 0.0;
         if (k < h) {
@@ -383,7 +392,7 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();   // chunk c has landed for every thread (also orders the sVec / sEdgeP writes before their use)
-        if (DB && c + 1 == nchunks) {
+        if (DB && c + 1 == nchunks && kgrp == 0) {
             // Last chunk: the other panel buffer is idle.  The epilogue's operands (this thread's own elements of the
             // stage input u, v, of phi^n of the warp's field and of p^n) are fetched into it now, behind the DMMAs.
             double* ep = sPan + ((c + 1) & 1) * 36 * ST_PANEL;
@@ -401,15 +410,54 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
         const int ksteps = min(ST_KC, P.K4 - c * ST_KC) / 4;
+        const int ksplit = DB ? (ksteps + 1) / 2 : ksteps;          // group 0: [0, ksplit), group 1: [ksplit, ksteps)
+        const int ks0 = kgrp ? ksplit : 0, ks1 = kgrp ? ksteps : ksplit;
         if (fld == 0)
             st_chunk<true>(cur_buf, cur_buf + 6 * ST_PANEL, cur_buf + 12 * ST_PANEL, cur_buf + 24 * ST_PANEL,
-                           cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+                           cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ks0, ks1, wr, g, t, a1, a2, aL);
         else
             st_chunk<false>(cur_buf, cur_buf + 6 * ST_PANEL, cur_buf + 16 * ST_PANEL, cur_buf + 28 * ST_PANEL,
-                            cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ksteps, wr, g, t, a1, a2, aL);
+                            cur_buf + 20 * ST_PANEL, cur_buf + 32 * ST_PANEL, ks0, ks1, wr, g, t, a1, a2, aL);
         __syncthreads();   // chunk c consumed: its buffer may be refilled by the next issue
         if (!DB && c + 1 < nchunks) issue((c + 1) * ST_KC, sPan);
     }
+
+    if (DB) {
+        // split-K hand-off: group 1 parks its accumulators in the panel buffer of the last chunk (free since the barrier
+        // above; the prefetched epilogue operands sit in the other one) and leaves; group 0 adds them, always in this order
+        double* sAcc = sPan + ((nchunks - 1) & 1) * 36 * ST_PANEL;
+        if (kgrp == 1) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int idx = (q * 2 + nt) * 2 + hh;
+                        sAcc[(0 + idx) * ST_THREADS + tid] = a1[q][nt][hh];
+                        sAcc[(16 + idx) * ST_THREADS + tid] = a2[q][nt][hh];
+                        sAcc[(32 + idx) * ST_THREADS + tid] = aL[q][nt][hh];
+                    }
+        }
+        __syncthreads();
+        if (kgrp == 1) return;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int idx = (q * 2 + nt) * 2 + hh;
+                    a1[q][nt][hh] += sAcc[(0 + idx) * ST_THREADS + tid];
+                    a2[q][nt][hh] += sAcc[(16 + idx) * ST_THREADS + tid];
+                    aL[q][nt][hh] += sAcc[(32 + idx) * ST_THREADS + tid];
+                }
+    }
+    // the epilogue's barriers: group 0 only in DB mode (named barrier 1, 128 threads), the whole CTA otherwise
+    auto epi_barrier = [&]() {
+        if (DB) asm volatile("bar.sync 1, 128;" ::: "memory");
+        else __syncthreads();
+    };
 
     // ---- epilogue: the thread's own elements of all four blocks ----
     const int i = r0 + wr + g;
@@ -472,7 +520,7 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
             }
         }
     }
-    __syncthreads();
+    epi_barrier();
     if (fld == 0) {
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
@@ -501,7 +549,7 @@ __global__ void __launch_bounds__(ST_THREADS, DB ? 1 : 2) k_stream_stage(const S
             sRed[warp * 4 + 1] = s1;
             sRed[warp * 4 + 2] = mx;
         }
-        __syncthreads();
+        epi_barrier();
         if (tid == 0) {
             double* out = P.partials + ((size_t)b * ST_TILES + tile) * 8;
             out[0] = sRed[0] + sRed[4];                 // u: sum d^2   (warps 0, 1)
