@@ -208,6 +208,9 @@ def gpu_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION/INFO) out of it
+    if "LDC_KEEP_NCCL_DEBUG" not in os.environ:
+        os.environ["NCCL_DEBUG"] = "WARN"
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; ldc_b200 has no CPU fallback (use --impl reference for the CPU arm)")
 
