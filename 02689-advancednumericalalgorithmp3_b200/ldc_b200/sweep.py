@@ -242,15 +242,24 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
         r = solve(N, per["Re"], per["corner_smoothing"], per["tolerance"], int(k0["max_iterations"]), kind=kind,
                   fields="all", device=device, **shared)
         wall = time.time() - t0
-        verrs = _group_validation_errors(N, k0, per, r, root, device)
+        # post-processing of this rank's shard only (validation-error kernel, streamfunction solves), then one
+        # all-gather of the small per-trial records
+        lo, hi = _my_block(r.bounds, len(idx))
+        verr_loc = _group_validation_errors(N, k0, {k: v[lo:hi] for k, v in per.items()}, r.u[lo:hi], r.v[lo:hi], r.p[lo:hi],
+                                            root, device) if hi > lo else []
         lv = ops.build_level(N, N, k0["Lx"], k0["Ly"], str(k0["basis_type"]).lower())
-        for j, i in enumerate(idx):
+        vm_loc = []
+        for j in range(lo, hi):
             vm = {}
             if vortex_metrics and not r.diverged[j]:
                 try:
                     vm = streamfunction_vortex_metrics(lv, r.u[j], r.v[j])
                 except Exception:   # base.py:156-160 swallows these too
                     vm = {}
+            vm_loc.append({k: float(v) for k, v in vm.items()})
+        verrs, vms = _gather_records(verr_loc, vm_loc, r.bounds, len(idx))
+        for j, i in enumerate(idx):
+            vm = vms[j]
             m = Metrics(iterations=int(r.iterations[j]), converged=bool(r.converged[j]),
                         final_residual=float(r.rel_residual[j]), wall_time_seconds=wall / len(idx),
                         **{k: float(v) for k, v in vm.items() if k in Metrics.__dataclass_fields__})
@@ -261,8 +270,34 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
     return results
 
 
-def _group_validation_errors(N, k0, per, r, root, device):
-    """Batched L2 errors of one group: one `ldc_validation_errors` call per distinct integer Re and stored solution."""
+def _my_block(bounds, n):
+    """[lo, hi) of the cavities this rank post-processes: its shard of the solve, or everything without a process group."""
+    from .sharded import _dist
+
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1 or len(bounds) != dist.get_world_size():
+        return 0, n
+    return bounds[dist.get_rank()]
+
+
+def _gather_records(verr_loc, vm_loc, bounds, n):
+    """Per-trial dicts of every rank's block, concatenated in trial order on every rank."""
+    from .sharded import _dist
+
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1 or len(bounds) != dist.get_world_size():
+        return verr_loc, vm_loc
+    parts = [None] * dist.get_world_size()
+    dist.all_gather_object(parts, (verr_loc, vm_loc))
+    verrs = [d for part in parts for d in part[0]]
+    vms = [d for part in parts for d in part[1]]
+    assert len(verrs) == n and len(vms) == n
+    return verrs, vms
+
+
+def _group_validation_errors(N, k0, per, u, v, p, root, device):
+    """Batched L2 errors of one block of cavities: one `ldc_validation_errors` call per distinct integer Re and stored
+    solution."""
     from .batched import BatchedSpectralLDC
     from .validation import REF_DIRS, StoredSolution, batched_validation_errors
 
@@ -280,7 +315,7 @@ def _group_validation_errors(N, k0, per, r, root, device):
     dev = device if device is not None else (torch.cuda.current_device() if torch.cuda.is_available() else 0)
     with BatchedSpectralLDC(N, N, per["Re"].size, k0["Lx"], k0["Ly"], str(k0["basis_type"]).lower(), dev) as b:
         b.set_cases(per["Re"])
-        b.set_state(r.u, r.v, r.p)
+        b.set_state(np.ascontiguousarray(u), np.ascontiguousarray(v), np.ascontiguousarray(p))
         for Re, suffix, path in todo:
             e = batched_validation_errors(b, StoredSolution.from_vts(path))
             for j in np.nonzero(per["Re"].astype(int) == Re)[0]:

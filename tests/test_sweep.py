@@ -112,3 +112,48 @@ def test_small_real_sweep_matches_the_solver_class(built_lib, golden, tmp_path):
             s.close()
     finally:
         os.chdir(cwd)
+
+
+def _fake_sweep_sharded(N, Re, cs, tol, max_iter, *, kind, fields, device, **kw):
+    import torch.distributed as dist
+
+    from ldc_b200.sharded import shard_bounds
+
+    r = _fake_sweep(N, Re, cs, tol, max_iter, kind=kind, fields=fields, device=device, **kw)
+    r.bounds = shard_bounds(Re.size, dist.get_world_size())
+    return r
+
+
+def _sweep_worker(rank, world, port, root, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        trials = sweep.expand_overrides(["N=8", "Re=100,400,1000", "solver.corner_smoothing=0.1,0.2,0.3"])
+        res = sweep.run_trials(trials, "fv_l2_error", root=root, vortex_metrics=False, solve=_fake_sweep_sharded)
+        q.put((rank, [(r.index, r.metrics["iterations"], r.objective, r.validation_errors) for r in res]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_post_processing_is_sharded_and_gathered_over_two_gloo_ranks(tmp_path):
+    """Each rank post-processes its own block of the batch; the per-trial records are all-gathered in trial order."""
+    import socket
+
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sweep_worker, args=(r, 2, port, str(tmp_path), q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted((q.get(timeout=120) for _ in procs), key=lambda t: t[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert got[0][1] == got[1][1] and [x[0] for x in got[0][1]] == list(range(9))
+    assert [x[1] for x in got[0][1]] == [1000, 1000, 1000, 4000, 4000, 4000, 10000, 10000, 10000]
