@@ -366,3 +366,33 @@ def test_full_bench_batch_properties(ldc):
     # lid and wall boundary conditions hold exactly on every cavity
     assert not u[:, 0, :].any() and not u[:, -1, :].any() and not u[:, :, 0].any() and not v[:, :, -1].any()
     assert np.all(u[:, 20:-20, -1] == 1.0)   # the unsmoothed middle of the lid
+
+
+@pytest.mark.parametrize("N,B", [(128, 3), (80, 12)])
+def test_streamed_kernel_is_deterministic_and_batch_independent(ldc, N, B):
+    """Both shapes of the streamed stage kernel (one CTA per SM with the split-K warp group; two CTAs per SM): repeated
+    runs agree bit for bit (no shared-memory race shows up as run-to-run noise) and a cavity does not see its batch-mates."""
+    Re = np.linspace(300.0, 900.0, B)
+    runs = []
+    for _ in range(2):
+        with ldc.BatchedSpectralLDC(N, batch=B, path="stream_eo") as s:
+            s.set_cases(Re).init_state()
+            r = s.step(6)
+            runs.append((*s.get_state(), r))
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+    # same kernel shape for the solo run: (128, 1) and (80, 12 -> 1) both keep their template (h > 48 resp. B x 16 <= #SM
+    # would switch the N = 80 case, so compare it inside one batch instead: duplicate cavities must agree)
+    if N == 128:
+        with ldc.BatchedSpectralLDC(N, batch=1, path="stream_eo") as s:
+            s.set_cases(Re[1]).init_state()
+            s.step(6)
+            u1, v1, p1 = s.get_state()
+        assert np.array_equal(runs[0][0][1], u1[0]) and np.array_equal(runs[0][2][1], p1[0])
+    else:
+        with ldc.BatchedSpectralLDC(N, batch=B, path="stream_eo") as s:
+            s.set_cases(np.full(B, Re[3])).init_state()
+            s.step(6)
+            u, v, p = s.get_state()
+        assert all(np.array_equal(u[0], u[k]) and np.array_equal(p[0], p[k]) for k in range(1, B))
+        assert np.array_equal(u[0], runs[0][0][3])
