@@ -13,6 +13,7 @@
 #include "stream_eo.cuh"
 #include "tiled.cuh"
 #include "validate.cuh"
+#include "history_fused.cuh"
 
 namespace ldc {
 thread_local std::string g_last_error;
@@ -824,7 +825,27 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
     LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
     const long long end = std::min<long long>(max_iter, start_iter + hist_cap);
     const int nfull = (int)nf, ninner = h->mx * h->my;
-    for (long long it = start_iter; it < end; ++it) {
+    // small grids: the whole chunk of iterations in ONE launch, everything in shared memory (history_fused.cuh)
+    const size_t fused_bytes = hist_fused_smem_doubles(h->n1x, h->n1y) * sizeof(double);
+    int max_optin = 0;
+    LDC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    const char* env_fused = getenv("LDC_HISTORY_FUSED");
+    const bool fused = fused_bytes <= (size_t)max_optin && !(env_fused && atoi(env_fused) == 0) && h->path != LDC_PATH_TILED;
+    if (fused) {
+        LDC_CUDA(cudaFuncSetAttribute(k_history_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fused_bytes));
+        HistFusedParams F;
+        F.u = h->u; F.v = h->v; F.p = h->p;
+        F.Dx = h->Dx; F.Dxx = h->Dxx; F.DyT = h->DyT; F.DyyT = h->DyyT; F.Ix = h->Ix; F.IyT = h->IyT;
+        F.Re = h->Re; F.beta2 = h->beta2; F.CFL = h->CFL; F.lidvel = h->lidvel; F.ulid = h->ulid; F.vlid = h->vlid;
+        F.W = h->Wq; F.tol = h->tol; F.status = h->status; F.hist = h->hist; F.cap = h->hist_cap;
+        F.start_iter = start_iter; F.end_iter = end; F.max_iter = max_iter;
+        F.warmup = warmup; F.nan_exit = nan_exit ? 1 : 0; F.freeze = freeze_pressure ? 1 : 0;
+        F.n1x = h->n1x; F.n1y = h->n1y; F.dx_min = h->dx_min; F.dy_min = h->dy_min;
+        k_history_fused<<<h->B, HF_THREADS, fused_bytes, h->stream>>>(F);
+        h->launches += 1;
+        LDC_CUDA(cudaGetLastError());
+    }
+    for (long long it = start_iter; it < end && !fused; ++it) {
         launch_tiled_step(h, freeze_pressure ? 1 : 0, warmup, max_iter, nan_exit ? 1 : 0, h->tol);
         const long long slot = it - start_iter;
         // h->Ru, Rv, Rp still hold the last stage's residual (what the reference's arrays.R_* hold after step())

@@ -110,7 +110,9 @@ int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int fre
  * enstrophy, palinstrophy of the new state with quadrature weights W[(nx+1)][(ny+1)] (spectral/sg.py:495-550) }.
  * The call takes at most hist_cap iterations: the caller streams a long solve in chunks, start_iter = 0 starts a solve
  * (status reset), start_iter > 0 continues the previous call of this handle (iters keeps counting; max_iter is absolute).
- * Rows of iterations a cavity did not take stay zero; the reference keeps rows i >= 10 only (base.py:262-276). */
+ * Rows of iterations a cavity did not take stay zero; the reference keeps rows i >= 10 only (base.py:262-276).
+ * Grids whose operators, state and work arrays fit one SM's shared memory (N <= 36) run a whole call in ONE launch
+ * (k_history_fused); larger grids, and handles forced to LDC_PATH_TILED, take one launch per RK stage. */
 int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t max_iter, int warmup, int freeze_pressure,
                       int nan_exit, const double* W, double* hist, int64_t hist_cap, int64_t* iters, int32_t* converged,
                       int32_t* diverged, double* rel_res);

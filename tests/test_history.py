@@ -85,3 +85,25 @@ def test_history_off_uses_the_resident_kernel(built_lib, golden):
     assert s.metrics.iterations == int(golden.history["full_meta"][0])
     assert len(s.time_series.rel_iter_residual) == 1
     s.close()
+
+
+@pytest.mark.gpu
+def test_fused_history_kernel_matches_the_launch_per_stage_path(built_lib):
+    """k_history_fused (one launch per chunk, everything in shared memory) against the launch-per-stage history path
+    (forced with path='tiled'): same per-node arithmetic, so records agree to rounding of the reductions."""
+    out = {}
+    for path in ("auto", "tiled"):
+        with built_lib.BatchedSpectralLDC(20, 14, batch=3, path=path) as b:   # non-square grid, three cavities
+            b.set_cases([100.0, 400.0, 50.0], corner_smoothing=[0.15, 0.1, 0.2]).init_state()
+            launches0 = b.launches
+            r, h = b.solve_history(2e-3, 600, warmup=10, freeze_pressure=(path == "auto") or True, chunk=128)
+            out[path] = (r, h, b.launches - launches0, b.get_state())
+    ra, ha, la, sa = out["auto"]
+    rt, ht, lt, st = out["tiled"]
+    assert la < lt / 50                      # a handful of launches against ~22 per iteration
+    assert np.array_equal(ra.iterations, rt.iterations) and np.array_equal(ra.converged, rt.converged)
+    assert len(set(ra.iterations)) > 1       # the cavities stop at different iterations inside a chunk
+    for a, c in zip(ha, ht):
+        assert a.shape == c.shape and relcols(a, c).max() < 1e-11
+    for a, c in zip(sa, st):
+        assert np.max(np.abs(a - c)) < 1e-13
