@@ -150,11 +150,29 @@ def reference_arm(args):
 # clocks
 # ----------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock, power and throttle reasons of one GPU, sampled every 10 ms through NVML (nvidia-ml-py) while the timed
+    region runs; falls back to `nvidia-smi -lms 100` when NVML cannot be loaded."""
+
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, device_index: int):
-        self.rows, self.proc = [], None
+    def __init__(self, device_index: int, uuid: str | None = None):
+        self.rows, self.proc, self.nvml, self.stop_flag = [], None, None, False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            try:
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid) if uuid else pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nvml = pynvml
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                           "-i", str(device_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -163,36 +181,65 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        bits = [(getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8), "hw_slowdown"),
+                (getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40), "hw_thermal_slowdown"),
+                (getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), "sw_thermal_slowdown"),
+                (getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4), "sw_power_cap")]
+        reasons_fn = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(
+            n, "nvmlDeviceGetCurrentClocksThrottleReasons", None)
+        try:
+            mx = float(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM))
+        except Exception:
+            mx = None
+        while not self.stop_flag:
+            try:
+                sm = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                pw = n.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
+                mask = int(reasons_fn(self.handle)) if reasons_fn else 0
+                self.rows.append((time.perf_counter(), (sm, mx, pw, [nm for bit, nm in bits if mask & bit])))
+            except Exception:
+                pass
+            time.sleep(0.01)
+
     def _pump(self):
         for ln in self.proc.stdout:
-            self.rows.append((time.perf_counter(), ln.strip()))
-
-    def stop(self, t0=None, t1=None):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        sm, mx, pw, reasons = [], [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ts, ln in self.rows:
-            if t0 is not None and not (t0 <= ts <= t1 + 0.2):
-                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+                row = (float(f[0]), float(f[1]), float(f[2]),
+                       [nm for nm, val in zip(self.NAMES, f[3:7]) if val.lower().startswith("active")])
             except ValueError:
                 continue
-            for nm, val in zip(names, f[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(nm)
+            self.rows.append((time.perf_counter(), row))
+
+    def stop(self, t0=None, t1=None):
+        if self.nvml is None and self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml and nvidia-smi unavailable"]}
+        self.stop_flag = True
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        else:
+            self.th.join(timeout=1)
+        sm, mx, pw, reasons = [], [], [], set()
+        for ts, (a, b, c, rs) in self.rows:
+            if t0 is not None and not (t0 <= ts <= t1 + (0.2 if self.proc is not None else 0.0)):
+                continue
+            sm.append(a)
+            if b is not None:
+                mx.append(b)
+            pw.append(c)
+            reasons.update(rs)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvml, 10 ms" if self.nvml is not None else "nvidia-smi, 100 ms"}
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -250,7 +297,11 @@ def gpu_arm(args):
     for _ in range(args.warmup):
         s.step(P, want_rel=False)
     barrier()
-    clocks = ClockSampler(local)
+    try:
+        _uuid = "GPU-" + str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        _uuid = None
+    clocks = ClockSampler(local, _uuid)
     time.sleep(0.3)
     l0 = s.launches
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
