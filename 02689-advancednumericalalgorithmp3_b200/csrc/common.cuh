@@ -109,6 +109,7 @@ struct ldc_handle {
     double* hist = nullptr;
     size_t hist_cap = 0;
     double* Wq = nullptr;
+    double* fork = nullptr;       // ldc_solve_sampled: the status (and, on the launch-per-stage path, the state) kept across a record step
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_ms = 0.0;

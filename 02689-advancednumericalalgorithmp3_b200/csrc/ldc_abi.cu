@@ -303,7 +303,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->hist, h->Wq};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->hist, h->Wq, h->fork};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -626,10 +626,15 @@ static int launch_resident(ldc_handle* h, const ResParams& P) {
     return fail(LDC_ERR_UNSUPPORTED, "resident path: unsupported padded size");
 }
 
-// Shared driver of ldc_step / ldc_solve: iterate until every cavity is inactive.
-static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, int warmup, int freeze, int nan_exit) {
-    k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
-    h->launches += 1;
+// Shared driver of ldc_step / ldc_solve / ldc_solve_sampled: iterations [start, stop) of a solve whose limit is max_iter,
+// until every cavity is inactive.  start = 0 starts a solve (status reset); start > 0 continues from the status the
+// previous call left (every active cavity has taken exactly `start` iterations).
+static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long long stop, long long max_iter, int warmup,
+                     int freeze, int nan_exit) {
+    if (start == 0) {
+        k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 1;
+    }
     int rc;
     const int kernel = pick_kernel(h);
     if (kernel < 0)
@@ -664,7 +669,9 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         h->launches += 1;
         h->canon_valid = false;
         const long long chunk = 256;
-        for (long long done = 0; done < max_iter; ++done) {
+        // a continued solve (start > 0) finds the boundary lines as its own last step left them: no "first step after a
+        // load" there, so that a solve cut into segments takes bitwise the steps of an uncut one
+        for (long long done = start; done < stop; ++done) {
             P.first = done == 0 ? 1 : 0;
             for (int stg = 0; stg < 4; ++stg) {
                 P.stage = stg;
@@ -675,7 +682,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
             h->launches += 4;
             k_stream_end<<<h->B, ST_THREADS, 0, h->stream>>>(P);
             h->launches += 1;
-            if ((done + 1) % chunk == 0 && done + 1 < max_iter) {
+            if ((done + 1 - start) % chunk == 0 && done + 1 < stop) {
                 LDC_CUDA(cudaGetLastError());
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
@@ -702,8 +709,8 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         // steps per launch (the host looks at the active count between launches)
         const long long chunk = h->mx >= 49 ? 1024 : (h->mx >= 33 ? 2048 : (h->mx >= 17 ? 4096 : 16384));
         h->canon_valid = false;
-        for (long long done = 0; done < max_iter; done += chunk) {
-            const long long L = std::min(chunk, max_iter - done);
+        for (long long done = start; done < stop; done += chunk) {
+            const long long L = std::min(chunk, stop - done);
             P.launch_end = done + L;
             // steps per queue visit: the whole launch when every cavity has its own CTA slot, else ~64 visits per slot so
             // that the tail of the launch (slots idling while the last visits finish) stays near 1.5 %
@@ -713,7 +720,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
                 P.chunk = std::min(L, std::max(4LL, c));
             }
             if ((rc = split ? launch_eo_split(h, P) : (eo ? launch_eo(h, P) : launch_resident(h, P)))) return rc;
-            if (done + chunk < max_iter) {
+            if (done + chunk < stop) {
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
                 if (na == 0) break;
@@ -724,11 +731,11 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
         h->packed_valid = 0;
         const long long chunk = 64;
-        for (long long done = 0; done < max_iter; done += chunk) {
-            const long long n = std::min(chunk, max_iter - done);
+        for (long long done = start; done < stop; done += chunk) {
+            const long long n = std::min(chunk, stop - done);
             for (long long s = 0; s < n; ++s) launch_tiled_step(h, freeze, warmup, max_iter, nan_exit, tol_dev);
             LDC_CUDA(cudaGetLastError());
-            if (done + chunk < max_iter) {
+            if (done + chunk < stop) {
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
                 if (na == 0) break;
@@ -741,6 +748,53 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long max_iter, i
     LDC_CUDA(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_ms = ms;
     LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}
+
+// Iterations [start_iter, end) on the canonical state with their records into h->hist rows slot0, slot0 + 1, ...:
+// one launch for the lot where the grid fits one SM's shared memory (history_fused.cuh), else a launch per RK stage.
+static int hist_iterations(ldc_handle* h, long long start_iter, long long end, long long max_iter, int warmup, int freeze,
+                           int nan_exit, long long slot0) {
+    int rc;
+    const int nfull = h->n1x * h->n1y, ninner = h->mx * h->my;
+    const size_t fused_bytes = hist_fused_smem_doubles(h->n1x, h->n1y) * sizeof(double);
+    int max_optin = 0;
+    LDC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    const char* env_fused = getenv("LDC_HISTORY_FUSED");
+    const bool fused = fused_bytes <= (size_t)max_optin && !(env_fused && atoi(env_fused) == 0) && h->path != LDC_PATH_TILED;
+    if (fused) {
+        LDC_CUDA(cudaFuncSetAttribute(k_history_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fused_bytes));
+        HistFusedParams F;
+        F.u = h->u; F.v = h->v; F.p = h->p;
+        F.Dx = h->Dx; F.Dxx = h->Dxx; F.DyT = h->DyT; F.DyyT = h->DyyT; F.Ix = h->Ix; F.IyT = h->IyT;
+        F.Re = h->Re; F.beta2 = h->beta2; F.CFL = h->CFL; F.lidvel = h->lidvel; F.ulid = h->ulid; F.vlid = h->vlid;
+        F.W = h->Wq; F.tol = h->tol; F.status = h->status; F.hist = h->hist + (size_t)slot0 * HIST_W; F.cap = h->hist_cap;
+        F.start_iter = start_iter; F.end_iter = end; F.max_iter = max_iter;
+        F.warmup = warmup; F.nan_exit = nan_exit; F.freeze = freeze;
+        F.n1x = h->n1x; F.n1y = h->n1y; F.dx_min = h->dx_min; F.dy_min = h->dy_min;
+        k_history_fused<<<h->B, HF_THREADS, fused_bytes, h->stream>>>(F);
+        h->launches += 1;
+        LDC_CUDA(cudaGetLastError());
+        return LDC_OK;
+    }
+    for (long long it = start_iter; it < end; ++it) {
+        launch_tiled_step(h, freeze, warmup, max_iter, nan_exit, h->tol);
+        const long long slot = slot0 + it - start_iter;
+        // h->Ru, Rv, Rp still hold the last stage's residual (what the reference's arrays.R_* hold after step())
+        k_hist_norms<<<h->B, RED_THREADS, 0, h->stream>>>(h->Ru, h->Rv, h->Rp, nfull, ninner, h->status, it, slot, h->hist_cap,
+                                                         h->hist);
+        k_vorticity<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(h->u, h->v, h->Dx, h->DyT, h->pfull, h->n1x,
+                                                                              h->n1y);
+        k_hist_diag<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->pfull, h->Dx, h->DyT, h->Wq, h->n1x, h->n1y, h->status,
+                                                        it, slot, h->hist_cap, h->hist);
+        h->launches += 3;
+        if ((it + 1 - start_iter) % 256 == 0 && it + 1 < end) {
+            LDC_CUDA(cudaGetLastError());
+            int na = 0;
+            if ((rc = count_active(h, &na))) return rc;
+            if (na == 0) break;
+        }
+    }
     return LDC_OK;
 }
 
@@ -775,7 +829,7 @@ int ldc_step(ldc_t* h, int64_t n_steps, int freeze_pressure, double* rel) {
     if (n_steps < 0) return fail(LDC_ERR_INVALID, "ldc_step: n_steps must be >= 0");
     LDC_CUDA(cudaSetDevice(h->device));
     if (n_steps == 0) return LDC_OK;
-    if ((rc = run_steps(h, nullptr, n_steps, 0, freeze_pressure ? 1 : 0, 0))) return rc;
+    if ((rc = run_steps(h, nullptr, 0, n_steps, n_steps, 0, freeze_pressure ? 1 : 0, 0))) return rc;
     if (rel) return export_status(h, nullptr, nullptr, nullptr, nullptr, rel);
     return LDC_OK;
 }
@@ -788,7 +842,7 @@ int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int fre
     LDC_CUDA(cudaSetDevice(h->device));
     if ((rc = copy_in(h, h->tol, tol, h->B))) return rc;
     if (max_iter > 0) {
-        if ((rc = run_steps(h, h->tol, max_iter, warmup, freeze_pressure ? 1 : 0, nan_exit ? 1 : 0))) return rc;
+        if ((rc = run_steps(h, h->tol, 0, max_iter, max_iter, warmup, freeze_pressure ? 1 : 0, nan_exit ? 1 : 0))) return rc;
     } else {
         k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
         h->launches += 1;
@@ -824,45 +878,7 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
     }
     LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
     const long long end = std::min<long long>(max_iter, start_iter + hist_cap);
-    const int nfull = (int)nf, ninner = h->mx * h->my;
-    // small grids: the whole chunk of iterations in ONE launch, everything in shared memory (history_fused.cuh)
-    const size_t fused_bytes = hist_fused_smem_doubles(h->n1x, h->n1y) * sizeof(double);
-    int max_optin = 0;
-    LDC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-    const char* env_fused = getenv("LDC_HISTORY_FUSED");
-    const bool fused = fused_bytes <= (size_t)max_optin && !(env_fused && atoi(env_fused) == 0) && h->path != LDC_PATH_TILED;
-    if (fused) {
-        LDC_CUDA(cudaFuncSetAttribute(k_history_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fused_bytes));
-        HistFusedParams F;
-        F.u = h->u; F.v = h->v; F.p = h->p;
-        F.Dx = h->Dx; F.Dxx = h->Dxx; F.DyT = h->DyT; F.DyyT = h->DyyT; F.Ix = h->Ix; F.IyT = h->IyT;
-        F.Re = h->Re; F.beta2 = h->beta2; F.CFL = h->CFL; F.lidvel = h->lidvel; F.ulid = h->ulid; F.vlid = h->vlid;
-        F.W = h->Wq; F.tol = h->tol; F.status = h->status; F.hist = h->hist; F.cap = h->hist_cap;
-        F.start_iter = start_iter; F.end_iter = end; F.max_iter = max_iter;
-        F.warmup = warmup; F.nan_exit = nan_exit ? 1 : 0; F.freeze = freeze_pressure ? 1 : 0;
-        F.n1x = h->n1x; F.n1y = h->n1y; F.dx_min = h->dx_min; F.dy_min = h->dy_min;
-        k_history_fused<<<h->B, HF_THREADS, fused_bytes, h->stream>>>(F);
-        h->launches += 1;
-        LDC_CUDA(cudaGetLastError());
-    }
-    for (long long it = start_iter; it < end && !fused; ++it) {
-        launch_tiled_step(h, freeze_pressure ? 1 : 0, warmup, max_iter, nan_exit ? 1 : 0, h->tol);
-        const long long slot = it - start_iter;
-        // h->Ru, Rv, Rp still hold the last stage's residual (what the reference's arrays.R_* hold after step())
-        k_hist_norms<<<h->B, RED_THREADS, 0, h->stream>>>(h->Ru, h->Rv, h->Rp, nfull, ninner, h->status, it, slot, h->hist_cap,
-                                                         h->hist);
-        k_vorticity<<<grid2d(h->n1x, h->n1y, h->B), kBlock2d, 0, h->stream>>>(h->u, h->v, h->Dx, h->DyT, h->pfull, h->n1x,
-                                                                              h->n1y);
-        k_hist_diag<<<h->B, RED_THREADS, 0, h->stream>>>(h->u, h->v, h->pfull, h->Dx, h->DyT, h->Wq, h->n1x, h->n1y, h->status,
-                                                        it, slot, h->hist_cap, h->hist);
-        h->launches += 3;
-        if ((slot + 1) % 256 == 0 && it + 1 < end) {
-            LDC_CUDA(cudaGetLastError());
-            int na = 0;
-            if ((rc = count_active(h, &na))) return rc;
-            if (na == 0) break;
-        }
-    }
+    if ((rc = hist_iterations(h, start_iter, end, max_iter, warmup, freeze_pressure ? 1 : 0, nan_exit ? 1 : 0, 0))) return rc;
     LDC_CUDA(cudaEventRecord(h->ev1, h->stream));
     LDC_CUDA(cudaEventSynchronize(h->ev1));
     float ms = 0;
@@ -877,6 +893,95 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
                                (size_t)hist_cap * HIST_W * sizeof(double))))
                 return rc;
     }
+    return export_status(h, iters, converged, diverged, rel_res, nullptr);
+}
+
+int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit,
+                      const double* W, int64_t n_rec, const int64_t* rec_iter, double* hist, int64_t* iters, int32_t* converged,
+                      int32_t* diverged, double* rel_res) {
+    int rc = check_ready(h, "ldc_solve_sampled");
+    if (rc) return rc;
+    if (!tol || !W || !hist || !rec_iter || n_rec < 1 || max_iter < 1 || warmup < 0)
+        return fail(LDC_ERR_INVALID, "ldc_solve_sampled: bad argument");
+    for (int64_t k = 0; k < n_rec; ++k)
+        if (rec_iter[k] < 0 || rec_iter[k] >= max_iter || (k && rec_iter[k] <= rec_iter[k - 1]))
+            return fail(LDC_ERR_INVALID, "ldc_solve_sampled: rec_iter must be strictly increasing inside [0, max_iter)");
+    LDC_CUDA(cudaSetDevice(h->device));
+    const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my, B = h->B;
+    const size_t st_doubles = (B * sizeof(CavityStatus) + 7) / 8;
+    if (!h->Wq && (rc = dalloc(&h->Wq, nf))) return rc;
+    if (!h->fork && (rc = dalloc(&h->fork, st_doubles + B * (2 * nf + ni)))) return rc;
+    if (h->hist_cap < (size_t)n_rec) {
+        if (h->hist) cudaFree(h->hist);
+        h->hist = nullptr;
+        h->hist_cap = 0;
+        if ((rc = dalloc(&h->hist, B * (size_t)n_rec * HIST_W))) return rc;
+        h->hist_cap = (size_t)n_rec;
+    }
+    if ((rc = copy_in(h, h->tol, tol, B))) return rc;
+    if ((rc = copy_in(h, h->Wq, W, nf))) return rc;
+    LDC_CUDA(cudaMemsetAsync(h->hist, 0, B * h->hist_cap * HIST_W * sizeof(double), h->stream));
+    cudaEvent_t t0, t1;
+    LDC_CUDA(cudaEventCreate(&t0));
+    LDC_CUDA(cudaEventCreate(&t1));
+    LDC_CUDA(cudaEventRecord(t0, h->stream));
+    const int fz = freeze_pressure ? 1 : 0, ne = nan_exit ? 1 : 0;
+    double *fu = h->fork + st_doubles, *fv = fu + B * nf, *fp = fv + B * nf;
+    long long cur = 0;
+    bool started = false;
+    for (int64_t k = 0; k < n_rec; ++k) {
+        const long long K = rec_iter[k];
+        if (K > cur) {
+            if ((rc = run_steps(h, h->tol, cur, K, max_iter, warmup, fz, ne))) return rc;
+            cur = K;
+            started = true;
+        } else if (!started) {   // a record of iteration 0: the solve starts here
+            k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+            h->launches += 1;
+            started = true;
+        }
+        if (k % 16 == 15) {   // everything converged already: the remaining records stay zero
+            int na = 0;
+            if ((rc = count_active(h, &na))) return rc;
+            if (na == 0) break;
+        }
+        // the record step runs on the canonical copy of the state; the stepping kernels' own record (packed_valid != 0)
+        // is not touched, so the trajectory is the one ldc_solve takes
+        if ((rc = ensure_canonical(h))) return rc;
+        const bool canon_is_master = h->packed_valid == 0;
+        LDC_CUDA(cudaMemcpyAsync(h->fork, h->status, B * sizeof(CavityStatus), cudaMemcpyDeviceToDevice, h->stream));
+        if (canon_is_master) {
+            LDC_CUDA(cudaMemcpyAsync(fu, h->u, B * nf * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(fv, h->v, B * nf * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(fp, h->p, B * ni * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        }
+        if ((rc = hist_iterations(h, K, K + 1, max_iter, warmup, fz, ne, k))) return rc;
+        LDC_CUDA(cudaMemcpyAsync(h->status, h->fork, B * sizeof(CavityStatus), cudaMemcpyDeviceToDevice, h->stream));
+        if (canon_is_master) {
+            LDC_CUDA(cudaMemcpyAsync(h->u, fu, B * nf * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(h->v, fv, B * nf * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(h->p, fp, B * ni * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        } else {
+            h->canon_valid = false;
+        }
+    }
+    if (cur < max_iter) {
+        int na = 1;
+        if (started && (rc = count_active(h, &na))) return rc;
+        if (na > 0 && (rc = run_steps(h, h->tol, cur, max_iter, max_iter, warmup, fz, ne))) return rc;
+    }
+    LDC_CUDA(cudaEventRecord(t1, h->stream));
+    LDC_CUDA(cudaEventSynchronize(t1));
+    float ms = 0;
+    LDC_CUDA(cudaEventElapsedTime(&ms, t0, t1));
+    h->last_ms = ms;   // the whole call: stepping kernels and record steps
+    cudaEventDestroy(t0);
+    cudaEventDestroy(t1);
+    LDC_CUDA(cudaGetLastError());
+    for (size_t b = 0; b < B; ++b)   // the device rows are h->hist_cap apart (a buffer of an earlier, longer call is reused)
+        if ((rc = copy_out(h, hist + b * (size_t)n_rec * HIST_W, h->hist + b * h->hist_cap * HIST_W,
+                           (size_t)n_rec * HIST_W * sizeof(double))))
+            return rc;
     return export_status(h, iters, converged, diverged, rel_res, nullptr);
 }
 

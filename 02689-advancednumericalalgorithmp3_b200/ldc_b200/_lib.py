@@ -36,6 +36,8 @@ SIGNATURES = {
     "ldc_solve": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]),
     "ldc_solve_history": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int64, _vp, _vp,
                                     _vp, _vp]),
+    "ldc_solve_sampled": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, C.c_int64, _vp, _vp, _vp, _vp, _vp,
+                                    _vp]),
     "ldc_diagnostics": (C.c_int, [_vp, _vp, _vp]),
     "ldc_validation_errors": (C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ldc_prolongate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),

@@ -225,6 +225,55 @@ class BatchedSpectralLDC:
         hist = [np.concatenate(r) if r else np.zeros((0, 7)) for r in rows]
         return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, ms), hist
 
+    @staticmethod
+    def sample_iterations(n_iter: int, skip: int = 10, max_points: int = 1000):
+        """The iterations whose records the reference's TimeSeries holds: records of iterations >= skip are kept
+        (base.py:262-276) and thinned to max_points by np.linspace(0, L-1, max_points, dtype=int) (base.py:137-141).
+        The last entry is always the final iteration (Metrics are read from it)."""
+        kept = int(n_iter) - skip
+        if kept <= 0:
+            return np.zeros(0, dtype=np.int64)
+        if kept <= max_points:
+            return skip + np.arange(kept, dtype=np.int64)
+        return skip + np.linspace(0, kept - 1, max_points, dtype=int).astype(np.int64)
+
+    def solve_history_sampled(self, tolerance, max_iter: int, warmup: int = 10, freeze_pressure: bool = True,
+                              nan_exit: bool = False, skip: int = 10, max_points: int = 1000):
+        """The down-sampled history the reference ends up with, without a record per iteration.
+
+        Two passes over the same start state, both on the stepping kernels of `solve` (bitwise reproducible): the first
+        finds every cavity's iteration count, hence which iterations survive the reference's thinning
+        (`sample_iterations`); the second repeats the solve and forms those records only (`ldc_solve_sampled`: one
+        iteration of the history path on a copy of the state, the trajectory is not touched).  Returns
+        (SolveResult, history, iterations): history[b] is (n_b, 7) in the layout of `solve_history`, iterations[b] the
+        0-based iteration of each row.
+        """
+        state0 = self.get_state()
+        first = self.solve(tolerance, max_iter, warmup=warmup, freeze_pressure=freeze_pressure, nan_exit=nan_exit)
+        idx = [self.sample_iterations(n, skip, max_points) for n in first.iterations]
+        rec = np.unique(np.concatenate(idx)) if self.B > 1 else idx[0]
+        if rec.size == 0:
+            return first, [np.zeros((0, 7)) for _ in range(self.B)], idx
+        self.set_state(*state0)
+        tol = _per_case(tolerance, self.B, "tolerance")
+        iters = np.zeros(self.B, dtype=np.int64)
+        conv = np.zeros(self.B, dtype=np.int32)
+        divg = np.zeros(self.B, dtype=np.int32)
+        rel = np.zeros(self.B)
+        W = np.ascontiguousarray(self.level.W)
+        rec = np.ascontiguousarray(rec, dtype=np.int64)
+        buf = np.zeros((self.B, rec.size, 7))
+        _lib.check(self.lib.ldc_solve_sampled(self._h, _lib.ptr(tol), int(max_iter), int(warmup),
+                                              int(bool(freeze_pressure)), int(bool(nan_exit)), _lib.ptr(W), rec.size,
+                                              _lib.ptr(rec), _lib.ptr(buf), _lib.ptr(iters), _lib.ptr(conv),
+                                              _lib.ptr(divg), _lib.ptr(rel)), "ldc_solve_sampled")
+        res = SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, first.kernel_ms + self.last_kernel_ms)
+        if not np.array_equal(iters, first.iterations):
+            raise RuntimeError("solve_history_sampled: the second pass took a different number of iterations "
+                               f"({iters.tolist()} vs {first.iterations.tolist()}); use solve_history")
+        hist = [buf[b, np.searchsorted(rec, idx[b])] for b in range(self.B)]
+        return res, hist, idx
+
     def diagnostics(self):
         """[B,3] = (energy, enstrophy, palinstrophy)."""
         out = np.empty((self.B, 3))

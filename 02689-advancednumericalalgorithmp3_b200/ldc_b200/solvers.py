@@ -7,9 +7,10 @@ main.py:75-120) can instantiate them through Hydra's `_target_` unchanged.  The 
 the CUDA library through the C ABI (one cavity = a batch of one); nothing here falls back to the CPU.
 
 Beyond the reference surface, both classes accept `device=` (CUDA device index, default 0) and `history=`
-(default True: `SGSolver.solve` records the reference's per-iteration TimeSeries, base.py:243-313, on the
-launch-per-stage path; False: the resident DMMA kernel runs the whole solve and the TimeSeries holds the final
-record only) -- both optional, so the reference's YAML files stay valid.
+(default True: `SGSolver.solve` returns the reference's TimeSeries, base.py:243-313 thinned to 1000 points as base.py:137-141
+does, forming only the records that survive the thinning -- two passes of the resident DMMA kernel, one history-path
+iteration per kept record; "full": a record after every iteration, then thinned; False: the resident kernel runs the
+solve once and the TimeSeries holds the final record only) -- both optional, so the reference's YAML files stay valid.
 """
 from __future__ import annotations
 
@@ -36,8 +37,10 @@ class SGSolver:
 
     MAX_TIMESERIES_POINTS = 1000  # base.py:100 (_store_results default)
 
-    def __init__(self, params=None, device: int = 0, history: bool = True, **kwargs):
-        self.history = bool(history)
+    def __init__(self, params=None, device: int = 0, history=True, **kwargs):
+        if isinstance(history, str) and history.lower() not in ("full", "sampled"):
+            raise ValueError("history must be True, False, 'sampled' or 'full'")
+        self.history = "full" if isinstance(history, str) and history.lower() == "full" else bool(history)
         if params is None:
             params = self.Parameters(**kwargs)  # unknown key -> TypeError, as in the reference (base.py:47-52)
         self.params = params
@@ -168,9 +171,14 @@ class SGSolver:
         t0 = time.time()
         self._push_state()
         hist = None
-        if self.history:
+        if self.history == "full":
             r, hists = g.solve_history(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
             hist = hists[0][10:]  # base.py:262: records are kept for i >= 10 only
+        elif self.history:
+            # only the records that survive the reference's thinning to MAX_TIMESERIES_POINTS are formed
+            r, hists, _ = g.solve_history_sampled(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True,
+                                                  skip=10, max_points=self.MAX_TIMESERIES_POINTS)
+            hist = hists[0]
         else:
             r = g.solve(tol, int(max_iter), warmup=10, freeze_pressure=True, nan_exit=True)
         diverged = bool(r.diverged[0])

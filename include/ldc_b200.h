@@ -117,6 +117,18 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
                       int nan_exit, const double* W, double* hist, int64_t hist_cap, int64_t* iters, int32_t* converged,
                       int32_t* diverged, double* rel_res);
 
+/* base.solve's records at chosen iterations only: the reference keeps every record and then thins the series to 1000 points
+ * (_store_results base.py:136-141, indices np.linspace(0, L-1, 1000, dtype=int)), so a caller
+ * that knows the iteration count L of the solve (from a first ldc_solve on the same start state: the stepping kernels are
+ * deterministic) needs the records of those iterations alone.  The call is ldc_solve -- same stepping kernels, same
+ * trajectory, same iters / flags / final state -- and, for each k < n_rec, hist[b][k][7] = the record (layout of
+ * ldc_solve_history) of iteration rec_iter[k] (0-based, strictly increasing, < max_iter), formed by one iteration of the
+ * history path on a copy of the state the cavity has after rec_iter[k] iterations.  Rows of iterations a cavity did not take
+ * stay zero. */
+int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit,
+                      const double* W, int64_t n_rec, const int64_t* rec_iter, double* hist, int64_t* iters,
+                      int32_t* converged, int32_t* diverged, double* rel_res);
+
 /* Energy, enstrophy, palinstrophy with quadrature weights W[(nx+1)][(ny+1)]
  * (spectral/sg.py:495-550); out is [batch][3]. */
 int ldc_diagnostics(ldc_t* h, const double* W, double* out);

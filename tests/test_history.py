@@ -50,9 +50,10 @@ def test_short_history_matches_reference(built_lib, golden):
 
 
 @pytest.mark.gpu
-def test_full_history_and_metrics_match_reference(built_lib, golden):
+@pytest.mark.parametrize("mode", [True, "full"])   # True: only the records that survive the thinning are formed
+def test_full_history_and_metrics_match_reference(built_lib, golden, mode):
     g = golden.history
-    s = built_lib.SGSolver(**KW)
+    s = built_lib.SGSolver(history=mode, **KW)
     s.solve()
     meta = g["full_meta"]
     assert s.metrics.iterations == int(meta[0]) and s.metrics.converged
@@ -107,3 +108,43 @@ def test_fused_history_kernel_matches_the_launch_per_stage_path(built_lib):
         assert a.shape == c.shape and relcols(a, c).max() < 1e-11
     for a, c in zip(sa, st):
         assert np.max(np.abs(a - c)) < 1e-13
+
+
+def test_sample_iterations_rule():
+    from ldc_b200.batched import BatchedSpectralLDC as B
+
+    assert B.sample_iterations(7).size == 0 and B.sample_iterations(10).size == 0
+    assert B.sample_iterations(13).tolist() == [10, 11, 12]
+    assert B.sample_iterations(1010).tolist() == list(range(10, 1010))
+    idx = B.sample_iterations(14155)
+    assert idx.size == 1000 and idx[0] == 10 and idx[-1] == 14154
+    assert idx.tolist() == [10 + int(i) for i in np.linspace(0, 14144, 1000, dtype=int)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,path", [(16, "auto"), (16, "tiled"), (40, "auto"), (72, "auto")])
+def test_sampled_history_is_the_full_history_at_the_sampled_iterations(built_lib, n, path):
+    """ldc_solve_sampled: same iteration counts and final state as a plain solve (bitwise: the record steps run on a copy),
+    records equal to the every-iteration history at the kept iterations (two trajectories that differ by rounding)."""
+    Re, tol, cap, pts = [100.0, 150.0, 70.0], 2e-3 if n < 72 else 2e-2, 4000, 37
+    with built_lib.BatchedSpectralLDC(n, batch=3, path=path) as b:
+        b.set_cases(Re).init_state()
+        plain = b.solve(tol, cap, warmup=10, freeze_pressure=True)
+        s_plain = b.get_state()
+        b.init_state()
+        rs, hs, idx = b.solve_history_sampled(tol, cap, max_points=pts)
+        s_samp = b.get_state()
+        b.init_state()
+        rf, hf = b.solve_history(tol, cap)
+    assert np.array_equal(rs.iterations, plain.iterations) and np.array_equal(rs.converged, plain.converged)
+    assert plain.converged.all() and len(set(plain.iterations.tolist())) == 3
+    for a, c in zip(s_plain, s_samp):
+        assert np.array_equal(a, c)
+    assert np.all(np.abs(rf.iterations - rs.iterations) <= 1)
+    for b_ in range(3):
+        want = built_lib.BatchedSpectralLDC.sample_iterations(plain.iterations[b_], 10, pts)
+        assert np.array_equal(idx[b_], want) and hs[b_].shape == (pts, 7)
+        ok = idx[b_] < rf.iterations[b_]
+        assert ok.sum() >= pts - 1
+        assert relcols(hs[b_][ok], hf[b_][idx[b_][ok]]).max() < 1e-8
+        assert np.all(hs[b_][:, 4] > 0)      # every kept record was formed (no zero rows)
