@@ -626,6 +626,24 @@ static int launch_resident(ldc_handle* h, const ResParams& P) {
     return fail(LDC_ERR_UNSUPPORTED, "resident path: unsupported padded size");
 }
 
+// A launch of the streamed path's kernel chain: with pdl, the kernel may start while its predecessor in the stream drains
+// (programmatic dependent launch; the kernels order themselves with griddepcontrol.wait, stream_eo.cuh).
+template <typename K>
+static cudaError_t launch_chain(bool pdl, K kernel, dim3 grid, int threads, size_t smem, cudaStream_t stream,
+                                const StreamParams& P) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, P);
+}
+
 // Shared driver of ldc_step / ldc_solve / ldc_solve_sampled: iterations [start, stop) of a solve whose limit is max_iter,
 // until every cavity is inactive.  start = 0 starts a solve (status reset); start > 0 continues from the status the
 // previous call left (every active cavity has taken exactly `start` iterations).
@@ -669,6 +687,8 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         h->launches += 1;
         h->canon_valid = false;
         const long long chunk = 256;
+        const char* env_pdl = getenv("LDC_STREAM_PDL");   // 0: plain stream-ordered launches (A / B measurements)
+        const bool pdl = !(env_pdl && atoi(env_pdl) == 0);
         // a continued solve (start > 0) finds the boundary lines as its own last step left them: no "first step after a
         // load" there, so that a solve cut into segments takes bitwise the steps of an uncut one
         for (long long done = start; done < stop; ++done) {
@@ -676,11 +696,11 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             for (int stg = 0; stg < 4; ++stg) {
                 P.stage = stg;
                 P.bc_edges = (done == 0 && stg == 0) ? 0 : 1;
-                if (db) k_stream_stage<true><<<dim3(ST_TILES, h->B), 2 * ST_THREADS, smem, h->stream>>>(P);
-                else k_stream_stage<false><<<dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream>>>(P);
+                if (db) LDC_CUDA(launch_chain(pdl, k_stream_stage<true>, dim3(ST_TILES, h->B), 2 * ST_THREADS, smem, h->stream, P));
+                else LDC_CUDA(launch_chain(pdl, k_stream_stage<false>, dim3(ST_TILES, h->B), ST_THREADS, smem, h->stream, P));
             }
             h->launches += 4;
-            k_stream_end<<<h->B, ST_THREADS, 0, h->stream>>>(P);
+            LDC_CUDA(launch_chain(pdl, k_stream_end, dim3(h->B), ST_THREADS, 0, h->stream, P));
             h->launches += 1;
             if ((done + 1 - start) % chunk == 0 && done + 1 < stop) {
                 LDC_CUDA(cudaGetLastError());

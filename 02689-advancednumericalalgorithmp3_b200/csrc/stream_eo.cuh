@@ -23,6 +23,12 @@ constexpr int ST_ME = 2 * ST_HP;
 // + divergence exchange (2 x 16 x 32) + reduction scratch
 constexpr size_t st_smem_doubles(bool db) { return (size_t)(db ? 2 : 1) * 36 * ST_PANEL + 8 * ST_HP + 16 * ST_HP + 2 * 16 * 32 + 32; }
 
+// Programmatic dependent launch (sm_90+): launch_dependents lets the next kernel of the stream start once every CTA of this
+// grid has issued it (or exited); wait blocks until the preceding grid has completed and its writes are visible.  Both are
+// no-ops for a kernel launched without the programmatic-serialization attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 struct StreamParams {
     const double* ops;            // eo packed operators, HP = 64
     const double* opsc;           // [B][6 blocks] per-cavity copies: D, nu DD, -G (cp.async sources)
@@ -317,8 +323,6 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     double* sRed = sX + 2 * 16 * 32;
 
     const int b = blockIdx.y;
-    const CavityStatus st = P.status[b];
-    if (!st.active) return;
     const int tile = blockIdx.x, r0 = (tile / (ST_HP / ST_T)) * ST_T, c0 = (tile % (ST_HP / ST_T)) * ST_T;
     const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     const int kgrp = DB ? (threadIdx.x >> 7) : 0;          // split-K group (DB only)
@@ -326,6 +330,47 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     const int warp = tid >> 5, tw = warp & 1, fld = warp >> 1, wr = 8 * tw;
     const int m = P.m, h = eo_half(m), centre = (m & 1) ? h - 1 : -1;
     if (r0 >= h || c0 >= h) return;   // tile lies in the zero padding of the blocks
+
+    // Programmatic dependent launch: the stage kernels and k_stream_end of a run form a chain in which each launch may
+    // start while its predecessor drains.  Everything up to pdl_wait() touches only data no kernel of the chain writes
+    // (operators, lid profiles): the boundary vectors and the operator panels of the first chunk are on their way while
+    // the predecessor's last tiles finish.
+    pdl_launch_dependents();
+    const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
+    const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
+    // operators come pre-scaled per cavity from P.opsc: D, nu DD, -G
+    auto issue_ops = [&](int k0, double* buf) {
+#pragma unroll
+        for (int p = 0; p < 12; ++p) {
+            if (DB && (p & 1) != kgrp) continue;   // each group fetches every other panel
+            const double* src = p < 6 ? opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc            // rows at the tile rows
+                                      : opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
+            cp_async16(buf + p * ST_PANEL + lr * ST_LDK + lc, src);
+        }
+    };
+    issue_ops(0, sPan);
+    for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    // ---- boundary lines in parity form: uW uE uS uN vW vE vS vN ----
+    if (P.bc_edges) {   // W, E, S are zero and the lid line is the prescribed profile (every stage but the first after a load)
+        for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) {
+            const int line = e / ST_HP, k = e % ST_HP;
+            double x = 0.0, y = 0.0;
+            if (k < h && (line & 3) == 3) {
+                const double* lid = (line < 4 ? P.ulid : P.vlid) + (size_t)b * P.n1 + 1;
+                x = lid[k];
+                y = lid[m - 1 - k];
+            }
+            sEdgeP[2 * line * ST_HP + k] = 0.5 * (x + y);
+            sEdgeP[(2 * line + 1) * ST_HP + k] = 0.5 * (x - y);
+        }
+    }
+    pdl_wait();   // the predecessor's state, status and dt are complete and visible from here on
+
+    const CavityStatus st = P.status[b];
+    if (!st.active) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        return;
+    }
     const int cur = st.pad;
     const double* recN = P.buf[cur] + (size_t)b * P.stride;                       // phi^n
     const double* recI = P.buf[st_in(cur, P.stage)] + (size_t)b * P.stride;       // stage input
@@ -334,44 +379,37 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     const double nu = 1.0 / P.Re[b], beta2 = P.beta2[b];
 
     // ---- K loop: the 36 chunk panels arrive by cp.async into two alternating buffers while the previous chunk is
-    // contracted (operators come pre-scaled per cavity from P.opsc: D, nu DD, -G) ----
-    const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
-    const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
-    auto issue = [&](int k0, double* buf) {
+    // contracted ----
+    auto issue_state = [&](int k0, double* buf) {
 #pragma unroll
-        for (int p = 0; p < 36; ++p) {
-            if (DB && (p & 1) != kgrp) continue;   // each group fetches every other panel
+        for (int p = 12; p < 36; ++p) {
+            if (DB && (p & 1) != kgrp) continue;
             const double* src;
-            if (p < 6) src = opsc + (size_t)p * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;                 // operator rows at the tile rows
-            else if (p < 12) src = opsc + (size_t)(p - 6) * ST_BLK + (c0 + lr) * ST_LD + k0 + lc;     // ... at the tile columns
-            else if (p < 24) src = (p < 20 ? recI : recP) + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;   // row panels
-            else src = (p < 32 ? recI : recP) + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;               // column panels
+            if (p < 24) src = (p < 20 ? recI : recP) + (size_t)(p - 12) * ST_BLK + (r0 + lr) * ST_LD + k0 + lc;   // row panels
+            else src = (p < 32 ? recI : recP) + (size_t)(p - 24) * ST_BLK + (k0 + lr) * ST_LD + c0 + lc;          // column panels
             cp_async16(buf + p * ST_PANEL + lr * ST_LDK + lc, src);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    auto issue = [&](int k0, double* buf) {
+        issue_ops(k0, buf);
+        issue_state(k0, buf);
+    };
     const int nchunks = (P.K4 + ST_KC - 1) / ST_KC;
+    issue_state(0, sPan);
 
-    // ---- boundary-column vectors and boundary lines in parity form ----
-    for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) sVec[e] = __ldg(P.ops + 6 * ST_BLK + e);
-    for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) {
-        const int line = e / ST_HP, k = e % ST_HP;   // uW uE uS uN vW vE vS vN
-        double x = 0.0, y = 0.0;
-        if (k < h) {
-            if (P.bc_edges) {
-                if ((line & 3) == 3) {
-                    const double* lid = (line < 4 ? P.ulid : P.vlid) + (size_t)b * P.n1 + 1;
-                    x = lid[k];
-                    y = lid[m - 1 - k];
-                }
-            } else {
+    if (!P.bc_edges) {   // first stage after a load: the lines as stored with phi^n
+        for (int e = threadIdx.x; e < 8 * ST_HP; e += NTHR) {
+            const int line = e / ST_HP, k = e % ST_HP;
+            double x = 0.0, y = 0.0;
+            if (k < h) {
                 const double* src = recN + 12 * ST_BLK + line * ST_ME;
                 x = __ldcg(src + k);
                 y = __ldcg(src + m - 1 - k);
             }
+            sEdgeP[2 * line * ST_HP + k] = 0.5 * (x + y);
+            sEdgeP[(2 * line + 1) * ST_HP + k] = 0.5 * (x - y);
         }
-        sEdgeP[2 * line * ST_HP + k] = 0.5 * (x + y);
-        sEdgeP[(2 * line + 1) * ST_HP + k] = 0.5 * (x - y);
     }
 
     double a1[4][2][2], a2[4][2][2], aL[4][2][2];
@@ -382,7 +420,6 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
 
-    issue(0, sPan);
     for (int c = 0; c < nchunks; ++c) {
         double* cur_buf = sPan + (DB ? (c & 1) * 36 * ST_PANEL : 0);
         if (DB && c + 1 < nchunks) {
@@ -620,6 +657,8 @@ __global__ void __launch_bounds__(256) k_stream_begin(const double* __restrict__
 __global__ void __launch_bounds__(ST_THREADS) k_stream_end(const StreamParams P) {
     __shared__ double sh[32], shp[ST_TILES * 6];
     const int b = blockIdx.x;
+    pdl_launch_dependents();
+    pdl_wait();
     if (!P.status[b].active) return;
     stream_end_body(P, b, sh, shp);
 }
