@@ -105,6 +105,10 @@ struct ldc_handle {
     int num_sms = 0;
     int res_slots = 0;            // CTAs of the resident kernel the chip holds at once
 
+    // streamed path: its own operator pack and record stride (ST_HP blocks), so that a grid the resident even-odd kernel
+    // also takes (half size <= 32) can use either
+    double* s_ops = nullptr;
+    size_t s_stride = 0;
     // per-iteration history of ldc_solve_history: [B][hist_cap][7] records + the quadrature weights
     double* hist = nullptr;
     size_t hist_cap = 0;

@@ -173,7 +173,7 @@ static bool eo_split_ok(const ldc_handle* h) {
 
 static bool stream_shape_ok(const ldc_handle* h) {
     const int hh = eo_half(h->mx);
-    return h->nx == h->ny && hh > 32 && hh <= ST_HP;
+    return h->nx == h->ny && hh > 16 && hh <= ST_HP;   // below: one 16 x 16 tile per block, nothing to spread
 }
 static bool stream_ok(const ldc_handle* h) { return stream_shape_ok(h) && h->square_ops; }
 
@@ -186,6 +186,9 @@ static int pick_kernel(const ldc_handle* h) {
     if (h->path == LDC_PATH_STREAM_EO) return stream_ok(h) ? 3 : -1;
     // few cavities on a small grid: latency matters, spread each cavity over twice the warps
     if (eo_split_ok(h) && h->HP <= 16 && h->B <= h->num_sms) return 4;   // measured: no gain at HP = 24
+    // few cavities on the largest resident grids (50 <= N <= 65): four SMs per cavity on the streamed path beat one
+    // (N = 64: 28.0 k against 16.7 k steps/s for one cavity, 822 k against 614 k for 37; 74 cavities: 1.02 M against 1.23 M)
+    if (stream_ok(h) && eo_half(h->mx) > 24 && eo_half(h->mx) <= 32 && 4LL * h->B <= h->num_sms) return 3;
     if (eo_ok(h)) return 2;
     if (resident_ok(h)) return 1;
     return stream_ok(h) ? 3 : 0;
@@ -197,7 +200,7 @@ static int ensure_canonical(ldc_handle* h) {
     const int n1 = h->n1x;
     const dim3 grid((n1 * n1 + 255) / 256, h->B);
     if (h->packed_valid == 3)
-        k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->s_state, h->e_state_stride, n1, ST_HP);
+        k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->s_state, h->s_stride, n1, ST_HP);
     else if (h->packed_valid == 2)
         k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->e_state, h->e_state_stride, n1, h->HP);
     else
@@ -213,9 +216,9 @@ static int ensure_packed(ldc_handle* h, int kind) {
     int rc = ensure_canonical(h);
     if (rc) return rc;
     if (kind == 2 || kind == 3) {
-        const int HP = h->HP, LD = eo_ld(HP);
+        const int HP = kind == 3 ? ST_HP : h->HP, LD = eo_ld(HP);
         k_pack_state_eo<<<dim3((std::max(HP * LD, 2 * HP) + 255) / 256, h->B), 256, 0, h->stream>>>(
-            h->u, h->v, h->p, kind == 3 ? h->s_state : h->e_state, h->e_state_stride, h->n1x, HP);
+            h->u, h->v, h->p, kind == 3 ? h->s_state : h->e_state, kind == 3 ? h->s_stride : h->e_state_stride, h->n1x, HP);
     } else {
         const int MP = h->MP, LD = res_ld(MP);
         k_pack_state<<<dim3((MP * LD + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->r_state, h->r_state_stride,
@@ -273,13 +276,11 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
         h->e_state_stride = eo_state_stride(h->HP);
         A_(e_ops, eo_ops_size(h->HP));
         A_(e_state, B * h->e_state_stride);
-    } else if (rc == LDC_OK && stream_shape_ok(h)) {
-        h->HP = ST_HP;
-        h->e_state_stride = eo_state_stride(ST_HP);
-        A_(e_ops, eo_ops_size(ST_HP));
-        A_(s_state, 3 * B * h->e_state_stride);
-        A_(s_partials, B * ST_TILES * 8);
-        A_(s_opsc, B * 6 * ST_BLK);
+    }
+    if (rc == LDC_OK && stream_shape_ok(h)) {   // the state buffers of the streamed path come with its first run
+        if (!eo_shape_ok(h)) h->HP = ST_HP;
+        h->s_stride = eo_state_stride(ST_HP);
+        A_(s_ops, eo_ops_size(ST_HP));
     }
     if (rc == LDC_OK && cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
         rc = fail(LDC_ERR_CUDA, "ldc_create: cannot query the SM count");
@@ -303,7 +304,7 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->hist, h->Wq, h->fork};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->s_ops, h->hist, h->Wq, h->fork};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -402,6 +403,13 @@ int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const doubl
         double* DI = h->pfull;  // scratch: D I (n1 x m)
         k_left_mul<<<grid2d(n1, m, 1), kBlock2d, 0, h->stream>>>(h->Dx, h->Ix, DI, n1, n1, m, nullptr);
         k_pack_ops_eo<<<(HP * eo_ld(HP) + T - 1) / T, T, 0, h->stream>>>(h->Dx, h->Dxx, DI, h->e_ops, n1, HP);
+        h->launches += 2;
+    }
+    if (h->s_ops && h->square_ops) {
+        const int n1 = h->n1x, m = h->mx;
+        double* DI = h->pfull;
+        k_left_mul<<<grid2d(n1, m, 1), kBlock2d, 0, h->stream>>>(h->Dx, h->Ix, DI, n1, n1, m, nullptr);
+        k_pack_ops_eo<<<(ST_HP * eo_ld(ST_HP) + T - 1) / T, T, 0, h->stream>>>(h->Dx, h->Dxx, DI, h->s_ops, n1, ST_HP);
         h->launches += 2;
     }
     LDC_CUDA(cudaGetLastError());
@@ -660,29 +668,35 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
                                          "operators differ for the even-odd kernel)");
     const bool resident = kernel == 1 || kernel == 2 || kernel == 4, eo = kernel == 2 || kernel == 4, split = kernel == 4;
     if (kernel == 3) {
+        if (!h->s_state) {
+            if ((rc = dalloc(&h->s_state, 3 * (size_t)h->B * h->s_stride))) return rc;
+            if ((rc = dalloc(&h->s_partials, (size_t)h->B * ST_TILES * 8))) return rc;
+            if ((rc = dalloc(&h->s_opsc, (size_t)h->B * 6 * ST_BLK))) return rc;
+        }
         if ((rc = ensure_packed(h, 3))) return rc;
         // few CTAs (one per SM): double-buffer the chunk panels inside the CTA; many: two CTAs per SM overlap each other
         // one CTA per SM, double-buffered panels + split-K warps: for few CTAs, and (measured, N = 128 B = 64: 153 k ->
         // 171 k steps/s; N = 96: 355 k -> 341 k) whenever all 16 tiles of the padded blocks are in use
-        const bool db = (long long)h->B * ST_TILES <= h->num_sms || eo_half(h->mx) > 48;
+        const int trow = (eo_half(h->mx) + ST_T - 1) / ST_T;   // tiles of a block row that hold data
+        const bool db = (long long)h->B * trow * trow <= h->num_sms || eo_half(h->mx) > 48;
         const size_t smem = st_smem_doubles(db) * sizeof(double);
         if (db) LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         else LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
         StreamParams P;
-        P.ops = h->e_ops;
+        P.ops = h->s_ops;
         P.opsc = h->s_opsc;
-        k_stream_scale_ops<<<dim3(32, h->B), 256, 0, h->stream>>>(h->e_ops, h->Re, h->s_opsc);
+        k_stream_scale_ops<<<dim3(32, h->B), 256, 0, h->stream>>>(h->s_ops, h->Re, h->s_opsc);
         h->launches += 1;
-        const size_t bs = (size_t)h->B * h->e_state_stride;
+        const size_t bs = (size_t)h->B * h->s_stride;
         P.buf[0] = h->s_state; P.buf[1] = h->s_state + bs; P.buf[2] = h->s_state + 2 * bs;
-        P.stride = h->e_state_stride;
+        P.stride = h->s_stride;
         P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
         P.dt = h->dt; P.n1 = h->n1x; P.m = h->mx; P.K4 = (eo_half(h->mx) + 3) / 4 * 4;
         P.status = h->status; P.partials = h->s_partials; P.freeze = freeze;
         P.tol = tol_dev; P.warmup = warmup; P.nan_exit = nan_exit; P.max_iter = max_iter;
         P.dx_min = h->dx_min; P.dy_min = h->dy_min;
-        k_stream_begin<<<h->B, 256, 0, h->stream>>>(h->s_state, h->e_state_stride, h->mx, h->Re, h->beta2, h->CFL, h->lidvel,
+        k_stream_begin<<<h->B, 256, 0, h->stream>>>(h->s_state, h->s_stride, h->mx, h->Re, h->beta2, h->CFL, h->lidvel,
                                                     h->dx_min, h->dy_min, h->dt, h->status);
         h->launches += 1;
         h->canon_valid = false;
@@ -710,7 +724,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             }
         }
         // every cavity's record back into buffer 0
-        k_stream_normalise<<<dim3(32, h->B), 256, 0, h->stream>>>(h->s_state, bs, h->e_state_stride, h->status);
+        k_stream_normalise<<<dim3(32, h->B), 256, 0, h->stream>>>(h->s_state, bs, h->s_stride, h->status);
         k_stream_clear_pad<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
         h->launches += 2;
     } else if (resident) {

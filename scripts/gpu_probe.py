@@ -30,6 +30,10 @@ SMALL = [(30, 1, 4000), (30, 16, 2000), (30, 148, 2000), (30, 296, 2000), (30, 1
          (16, 2048, 2000), (32, 1024, 1000)]
 if len(sys.argv) > 1 and sys.argv[1] == "small":
     RUNS = [(p, c) for c in SMALL for p in ("resident_eo", "resident_eo_split")]
+MID = [(64, 1, 1000), (64, 8, 1000), (64, 16, 1000), (64, 37, 1000), (64, 74, 500), (64, 148, 500), (48, 8, 1000), (48, 37, 1000),
+       (40, 8, 1000), (34, 8, 1000)]
+if len(sys.argv) > 1 and sys.argv[1] == "mid":
+    RUNS = [(p, c) for c in MID for p in ("resident_eo", "stream_eo")]
 if len(sys.argv) > 1 and sys.argv[1] == "big":
     RUNS = [(p, c) for c in BIG for p in ("tiled", "stream_eo")]
 for path, (N, B, K) in RUNS:
