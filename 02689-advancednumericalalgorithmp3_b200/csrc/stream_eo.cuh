@@ -336,6 +336,7 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     // (operators, lid profiles): the boundary vectors and the operator panels of the first chunk are on their way while
     // the predecessor's last tiles finish.
     pdl_launch_dependents();
+    const double nu = 1.0 / __ldg(P.Re + b), beta2 = __ldg(P.beta2 + b);   // per-cavity constants: not written by the chain
     const int lr = tid >> 3, lc = 2 * (tid & 7);   // this thread's (row, column pair) inside a 16 x 16 chunk panel
     const double* opsc = P.opsc + (size_t)b * 6 * ST_BLK;
     // operators come pre-scaled per cavity from P.opsc: D, nu DD, -G
@@ -367,6 +368,7 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     pdl_wait();   // the predecessor's state, status and dt are complete and visible from here on
 
     const CavityStatus st = P.status[b];
+    const double dt_b = __ldcg(P.dt + b);   // on its way with the status (used by the epilogue only)
     if (!st.active) {
         asm volatile("cp.async.wait_all;" ::: "memory");
         return;
@@ -376,7 +378,6 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     const double* recI = P.buf[st_in(cur, P.stage)] + (size_t)b * P.stride;       // stage input
     double* recO = P.buf[st_out(cur, P.stage)] + (size_t)b * P.stride;            // stage output
     const double* recP = P.freeze ? recN : recI;                                  // pressure operand
-    const double nu = 1.0 / P.Re[b], beta2 = P.beta2[b];
 
     // ---- K loop: the 36 chunk panels arrive by cp.async into two alternating buffers while the previous chunk is
     // contracted ----
@@ -518,7 +519,7 @@ __global__ void __launch_bounds__(DB ? 2 * ST_THREADS : ST_THREADS, DB ? 1 : 2) 
     if (fld == 0) st_assemble<true>(sVec, sEdgeP, nu, P.bc_edges != 0, i, c0, t, uo, vo, a1, a2, aL);
     else st_assemble<false>(sVec, sEdgeP + 8 * ST_HP, nu, P.bc_edges != 0, i, c0, t, uo, vo, a1, a2, aL);
 
-    const double adt = rk_alpha(P.stage) * P.dt[b];
+    const double adt = rk_alpha(P.stage) * dt_b;
     const bool last = (P.stage == 3);
     double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
     const double wi = (i == centre) ? 0.5 : 1.0;
