@@ -116,6 +116,7 @@ struct ldc_handle {
     double* fork = nullptr;       // ldc_solve_sampled: the status (and, on the launch-per-stage path, the state) kept across a record step
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev2 = nullptr, ev3 = nullptr;   // ldc_solve_sampled: the whole call (its segments use ev0 / ev1)
     double last_ms = 0.0;
     int64_t launches = 0;
 };

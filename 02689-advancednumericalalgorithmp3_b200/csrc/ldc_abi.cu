@@ -314,6 +314,8 @@ void ldc_destroy(ldc_t* h) {
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev2) cudaEventDestroy(h->ev2);
+    if (h->ev3) cudaEventDestroy(h->ev3);
     delete h;
 }
 
@@ -955,10 +957,9 @@ int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup,
     if ((rc = copy_in(h, h->tol, tol, B))) return rc;
     if ((rc = copy_in(h, h->Wq, W, nf))) return rc;
     LDC_CUDA(cudaMemsetAsync(h->hist, 0, B * h->hist_cap * HIST_W * sizeof(double), h->stream));
-    cudaEvent_t t0, t1;
-    LDC_CUDA(cudaEventCreate(&t0));
-    LDC_CUDA(cudaEventCreate(&t1));
-    LDC_CUDA(cudaEventRecord(t0, h->stream));
+    if (!h->ev2) LDC_CUDA(cudaEventCreate(&h->ev2));
+    if (!h->ev3) LDC_CUDA(cudaEventCreate(&h->ev3));
+    LDC_CUDA(cudaEventRecord(h->ev2, h->stream));
     const int fz = freeze_pressure ? 1 : 0, ne = nan_exit ? 1 : 0;
     double *fu = h->fork + st_doubles, *fv = fu + B * nf, *fp = fv + B * nf;
     long long cur = 0;
@@ -1004,13 +1005,11 @@ int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup,
         if (started && (rc = count_active(h, &na))) return rc;
         if (na > 0 && (rc = run_steps(h, h->tol, cur, max_iter, max_iter, warmup, fz, ne))) return rc;
     }
-    LDC_CUDA(cudaEventRecord(t1, h->stream));
-    LDC_CUDA(cudaEventSynchronize(t1));
+    LDC_CUDA(cudaEventRecord(h->ev3, h->stream));
+    LDC_CUDA(cudaEventSynchronize(h->ev3));
     float ms = 0;
-    LDC_CUDA(cudaEventElapsedTime(&ms, t0, t1));
+    LDC_CUDA(cudaEventElapsedTime(&ms, h->ev2, h->ev3));
     h->last_ms = ms;   // the whole call: stepping kernels and record steps
-    cudaEventDestroy(t0);
-    cudaEventDestroy(t1);
     LDC_CUDA(cudaGetLastError());
     for (size_t b = 0; b < B; ++b)   // the device rows are h->hist_cap apart (a buffer of an earlier, longer call is reused)
         if ((rc = copy_out(h, hist + b * (size_t)n_rec * HIST_W, h->hist + b * h->hist_cap * HIST_W,
