@@ -162,6 +162,98 @@ class SGSolver:
         self._push_state()
         return compute_validation_errors(self._batch(), self.params.Re)
 
+    def validation_table(self, reference_csv: str = None):
+        """The rows of the vortex-metrics comparison table of base.py:890-964 (computed value, Botella & Peyret value,
+        error in per cent; primary, BL and BR vortices), or None when the reference file is missing.  As in the
+        reference the file is data/validation/botella/botella_Re<int(Re)>_vortex.csv relative to the working directory,
+        read with `comment="#"`, first data row; a column the file does not have gives a "-" row."""
+        import os
+
+        import pandas as pd
+
+        if reference_csv is None:
+            reference_csv = f"data/validation/botella/botella_Re{int(self.params.Re)}_vortex.csv"
+        if not os.path.exists(reference_csv):
+            log.warning(f"Reference file not found: {reference_csv}")
+            return None
+        ref = pd.read_csv(reference_csv, comment="#").iloc[0].to_dict()
+        rows = []
+
+        def add_row(vortex, metric, computed, reference, fmt=".6f"):
+            if reference and reference != 0:
+                error_pct = abs(abs(computed) - abs(reference)) / abs(reference) * 100
+                ref_str = f"{reference:{fmt}}" if abs(reference) >= 1e-3 else f"{reference:.4e}"
+            else:
+                error_pct, ref_str = None, "-"
+            comp_str = f"{computed:{fmt}}" if abs(computed) >= 1e-3 else f"{computed:.4e}"
+            rows.append({"Vortex": vortex, "Metric": metric, "Computed": comp_str, "Botella": ref_str,
+                         "Error (%)": f"{error_pct:.2f}" if error_pct is not None else "-"})
+
+        m = self.metrics
+        add_row("Primary", "|\u03c8|", abs(m.psi_min), ref.get("psi_primary"))
+        add_row("Primary", "|\u03c9|", abs(m.omega_center), ref.get("omega_primary"))
+        add_row("Primary", "x", m.psi_min_x, ref.get("x_primary"))
+        add_row("Primary", "y", m.psi_min_y, ref.get("y_primary"))
+        for tag in ("BL", "BR"):
+            add_row(tag, "|\u03c8|", abs(getattr(m, f"psi_{tag}")), ref.get(f"psi_{tag}"))
+            add_row(tag, "|\u03c9|", abs(getattr(m, f"omega_{tag}", 0.0)), ref.get(f"omega_{tag}"))
+            add_row(tag, "x", getattr(m, f"psi_{tag}_x"), ref.get(f"x_{tag}"))
+            add_row(tag, "y", getattr(m, f"psi_{tag}_y"), ref.get(f"y_{tag}"))
+        return rows
+
+    def mlflow_log_validation_table(self, reference_csv: str = None):
+        """base.py:890-964: `validation_table` logged as validation_metrics.json into the active MLflow run; a warning
+        and nothing else when MLflow is not installed or no run is active."""
+        try:
+            import mlflow
+        except ImportError:
+            log.warning("MLflow is not installed - skipping validation table")
+            return
+        if not mlflow.active_run():
+            log.warning("No active MLflow run - skipping validation table")
+            return
+        rows = self.validation_table(reference_csv)
+        if rows is None:
+            return
+        import pandas as pd
+
+        mlflow.log_table(pd.DataFrame(rows), artifact_file="validation_metrics.json")
+        log.info("Logged validation metrics table to MLflow")
+
+    def to_vtk(self):
+        """base.py:464-522 without PyVista: the solution as a structured grid with u, v, pressure, velocity_magnitude,
+        vorticity (the base-class default base.py:524-549, which the spectral solvers do not override: cubic splines built
+        as Spline(y, x, F) and evaluated with dx=1 for "dvdx" and dy=1 for "dudy" -- the first spline variable being y,
+        the array written as "vorticity" is dv/dy - du/dx; kept, the stored FV files carry exactly that), the velocity vector and the Re / N / solver field data; `to_vtk().save(path)` (main.py:116) writes
+        the .vts flavour VTK writes (`ldc_b200.vts.write_vts`).  Point order and dimensions are PyVista's for
+        `StructuredGrid(X, Y, Z)` with `X, Y = meshgrid(x, y)`: y runs fastest, dimensions (ny, nx, 1)."""
+        from scipy.interpolate import RectBivariateSpline
+
+        from .vts import StructuredGrid
+
+        x_unique = np.sort(np.unique(self.fields.x))
+        y_unique = np.sort(np.unique(self.fields.y))
+        nx, ny = len(x_unique), len(y_unique)
+        order = np.lexsort((self.fields.x, self.fields.y))
+        U = self.fields.u[order].reshape(ny, nx)
+        V = self.fields.v[order].reshape(ny, nx)
+        Pr = self.fields.p[order].reshape(ny, nx)
+        X, Y = np.meshgrid(x_unique, y_unique)
+        pts = np.column_stack([X.ravel("F"), Y.ravel("F"), np.zeros(nx * ny)])
+        dvdx = RectBivariateSpline(y_unique, x_unique, V)(y_unique, x_unique, dx=1)   # sic (base.py:546)
+        dudy = RectBivariateSpline(y_unique, x_unique, U)(y_unique, x_unique, dy=1)   # sic (base.py:547)
+        grid = StructuredGrid(points=pts, dimensions=(ny, nx, 1))
+        grid["u"] = U.ravel("F")
+        grid["v"] = V.ravel("F")
+        grid["pressure"] = Pr.ravel("F")
+        grid["velocity_magnitude"] = np.sqrt(U**2 + V**2).ravel("F")
+        grid["vorticity"] = (dvdx - dudy).ravel("F")
+        grid["velocity"] = np.column_stack([U.ravel("F"), V.ravel("F"), np.zeros(nx * ny)])
+        grid.field_data["Re"] = np.array([self.params.Re])
+        grid.field_data["N"] = np.array([self.params.nx])
+        grid.field_data["solver"] = str(self.params.name)
+        return grid
+
     def solve(self, tolerance: float = None, max_iter: int = None):
         """base.solve (base.py:202-330) for the spectral single grid: iterate SGSolver.step until
         max(||du||/(||u||+1e-12), same for v) < tolerance after a 10-iteration warm-up."""

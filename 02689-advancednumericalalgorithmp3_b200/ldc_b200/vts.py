@@ -22,11 +22,26 @@ _DTYPES = {"Float64": "f8", "Float32": "f4", "Int64": "i8", "Int32": "i4", "UInt
 
 @dataclass
 class StructuredGrid:
-    """What the reference reads from a `pv.StructuredGrid`: points (n, 3), point_data by name, the point extent."""
+    """What the reference reads from / writes through a `pv.StructuredGrid`: points (n, 3), point_data by name, the point
+    extent, field_data (numeric arrays and strings), `grid["name"]` access and `save(path)` (main.py:116)."""
 
     points: np.ndarray
     point_data: Dict[str, np.ndarray] = field(default_factory=dict)
     dimensions: tuple = (0, 0, 0)
+    field_data: Dict[str, object] = field(default_factory=dict)
+
+    def __getitem__(self, name):
+        return self.point_data[name]
+
+    def __setitem__(self, name, values):
+        self.point_data[name] = np.asarray(values)
+
+    @property
+    def n_points(self) -> int:
+        return int(self.points.shape[0])
+
+    def save(self, path: str) -> None:
+        write_vts(path, self.points, self.dimensions, self.point_data, self.field_data)
 
 
 def _b64_chunk_len(nbytes: int) -> int:
@@ -92,6 +107,17 @@ def read_vts(path: str) -> StructuredGrid:
     if pts.shape != (npts, 3):
         raise ValueError(f"{path}: {pts.shape} points for extent {dims}")
     out = StructuredGrid(points=pts, dimensions=dims)
+    fd = grid.find("FieldData")
+    if fd is not None:
+        for el in list(fd):
+            if el.get("type") == "String":   # <Array type="String">: the bytes of the string(s), NUL-terminated
+                if el.get("format", "ascii") == "binary":
+                    raw = _decode_binary(el.text, np.dtype("u1"), header_dtype, comp is not None, order).tobytes()
+                else:
+                    raw = bytes(int(x) for x in el.text.split())
+                out.field_data[el.get("Name")] = raw.rstrip(b"\0").decode()
+            else:
+                out.field_data[el.get("Name")] = array(el)
     pd = piece.find("PointData")
     if pd is not None:
         for el in pd.findall("DataArray"):
@@ -111,23 +137,47 @@ def _encode_binary(a: np.ndarray, block: int = 32768) -> str:
     return base64.b64encode(head).decode() + base64.b64encode(b"".join(comp)).decode()
 
 
-def write_vts(path: str, points: np.ndarray, dims, point_data: Dict[str, np.ndarray]) -> None:
-    """Write the same flavour of .vts (zlib, UInt32 headers, inline binary).  Used by the tests and by sweeps that want
-    to hand a field to ParaView; the reference's own writer is `pv.StructuredGrid.save` (main.py:116)."""
+def _range_attrs(a: np.ndarray) -> str:
+    """RangeMin / RangeMax as VTK writes them: of the values, or of the tuple norms for multi-component arrays."""
+    if a.size == 0:
+        return ""
+    m = np.linalg.norm(a, axis=1) if a.ndim == 2 else a
+    return f' RangeMin="{m.min()!r}" RangeMax="{m.max()!r}"'.replace("np.float64(", "").replace("np.int64(", "").replace(")", "")
+
+
+def write_vts(path: str, points: np.ndarray, dims, point_data: Dict[str, np.ndarray], field_data: Dict[str, object] = None) -> None:
+    """Write the flavour of .vts `pv.StructuredGrid.save` produces (main.py:116; zlib, UInt32 headers, inline binary,
+    FieldData in front of the piece, RangeMin / RangeMax attributes), so that ParaView, PyVista and `read_vts` read it."""
     ext = f"0 {dims[0] - 1} 0 {dims[1] - 1} 0 {dims[2] - 1}"
     names = {np.dtype("f8"): "Float64", np.dtype("f4"): "Float32", np.dtype("i8"): "Int64", np.dtype("i4"): "Int32"}
     lines = ['<?xml version="1.0"?>',
              '<VTKFile type="StructuredGrid" version="0.1" byte_order="LittleEndian" header_type="UInt32" '
              'compressor="vtkZLibDataCompressor">',
-             f'  <StructuredGrid WholeExtent="{ext}">', f'  <Piece Extent="{ext}">', "    <PointData>"]
+             f'  <StructuredGrid WholeExtent="{ext}">']
+    if field_data:
+        lines.append("    <FieldData>")
+        for name, val in field_data.items():
+            if isinstance(val, str):
+                raw = np.frombuffer(val.encode() + b"\0", dtype="u1")
+                lines += [f'      <Array type="String" Name="{name}" NumberOfTuples="1" format="binary">',
+                          "        " + _encode_binary(raw), "      </Array>"]
+            else:
+                a = np.atleast_1d(np.asarray(val))
+                if a.dtype not in names:
+                    a = a.astype(np.int64 if np.issubdtype(a.dtype, np.integer) else np.float64)
+                lines += [f'      <DataArray type="{names[a.dtype]}" Name="{name}" NumberOfTuples="{a.shape[0]}" '
+                          f'format="binary"{_range_attrs(a)}>', "        " + _encode_binary(a), "      </DataArray>"]
+        lines.append("    </FieldData>")
+    scal = next((k for k, a in point_data.items() if np.ndim(a) == 1), None)
+    lines += [f'  <Piece Extent="{ext}">', f'    <PointData Scalars="{scal}">' if scal else "    <PointData>"]
     for name, a in point_data.items():
         a = np.asarray(a)
         nc = "" if a.ndim == 1 else f' NumberOfComponents="{a.shape[1]}"'
-        lines += [f'      <DataArray type="{names[a.dtype]}" Name="{name}"{nc} format="binary">',
+        lines += [f'      <DataArray type="{names[a.dtype]}" Name="{name}"{nc} format="binary"{_range_attrs(a)}>',
                   "        " + _encode_binary(a), "      </DataArray>"]
     pts = np.asarray(points, dtype=np.float64)
     lines += ["    </PointData>", "    <CellData>", "    </CellData>", "    <Points>",
-              '      <DataArray type="Float64" Name="Points" NumberOfComponents="3" format="binary">',
+              f'      <DataArray type="Float64" Name="Points" NumberOfComponents="3" format="binary"{_range_attrs(pts)}>',
               "        " + _encode_binary(pts), "      </DataArray>", "    </Points>", "  </Piece>", "  </StructuredGrid>",
               "</VTKFile>"]
     with open(path, "w") as f:
