@@ -148,3 +148,37 @@ def test_sampled_history_is_the_full_history_at_the_sampled_iterations(built_lib
         assert ok.sum() >= pts - 1
         assert relcols(hs[b_][ok], hf[b_][idx[b_][ok]]).max() < 1e-8
         assert np.all(hs[b_][:, 4] > 0)      # every kept record was formed (no zero rows)
+
+
+@pytest.mark.gpu
+def test_sampled_history_edge_cases(built_lib):
+    """ldc_solve_sampled at the ends of its domain: a record of iteration 0 and of the last iteration of a solve that
+    stops at max_iter, a cavity that goes non-finite (its later rows stay zero), argument checks."""
+    from ldc_b200 import _lib
+
+    with built_lib.BatchedSpectralLDC(16, batch=2) as b:
+        b.set_cases([100.0, 1000.0], corner_smoothing=[0.15, 0.01], CFL=[1.5, 50.0]).init_state()   # second one blows up
+        full, hf = b.solve_history(1e-12, 300, nan_exit=True)
+        assert full.diverged[1] and not full.diverged[0] and full.iterations[0] == 300 and full.iterations[1] < 300
+        b.init_state()
+        tol = np.full(2, 1e-12)
+        rec = np.array([0, 1, 7, int(full.iterations[1]) - 1, int(full.iterations[1]) + 5, 299], dtype=np.int64)
+        buf = np.zeros((2, rec.size, 7))
+        iters, conv, divg, rel = np.zeros(2, np.int64), np.zeros(2, np.int32), np.zeros(2, np.int32), np.zeros(2)
+        W = np.ascontiguousarray(b.level.W)
+
+        def call(r, max_iter=300):
+            return b.lib.ldc_solve_sampled(b._h, _lib.ptr(tol), max_iter, 10, 1, 1, _lib.ptr(W), r.size, _lib.ptr(r), _lib.ptr(buf),
+                                           _lib.ptr(iters), _lib.ptr(conv), _lib.ptr(divg), _lib.ptr(rel))
+
+        assert call(rec) == 0
+        assert np.array_equal(iters, full.iterations) and divg[1] == 1 and divg[0] == 0
+        for k, it in enumerate(rec):
+            assert relcols(buf[0, k][None], hf[0][it][None]).max() < 1e-9
+            if it < full.iterations[1] - 1:
+                assert relcols(buf[1, k][None], hf[1][it][None]).max() < 1e-7      # a trajectory about to blow up
+            elif it >= full.iterations[1]:
+                assert not buf[1, k].any()                                          # iteration not taken: zero row
+        for bad in (np.array([5, 5], dtype=np.int64), np.array([7, 3], dtype=np.int64), np.array([300], dtype=np.int64),
+                    np.array([-1], dtype=np.int64)):
+            assert call(bad) != 0 and "rec_iter" in b.lib.ldc_last_error().decode()
