@@ -680,7 +680,8 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         // one CTA per SM, double-buffered panels + split-K warps: for few CTAs, and (measured, N = 128 B = 64: 153 k ->
         // 171 k steps/s; N = 96: 355 k -> 341 k) whenever all 16 tiles of the padded blocks are in use
         const int trow = (eo_half(h->mx) + ST_T - 1) / ST_T;   // tiles of a block row that hold data
-        const bool db = (long long)h->B * trow * trow <= h->num_sms || eo_half(h->mx) > 48;
+        bool db = (long long)h->B * trow * trow <= h->num_sms || eo_half(h->mx) > 48;
+        if (const char* e = getenv("LDC_STREAM_DB")) db = atoi(e) != 0;   // A / B measurements of the two shapes
         const size_t smem = st_smem_doubles(db) * sizeof(double);
         if (db) LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         else LDC_CUDA(cudaFuncSetAttribute(k_stream_stage<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
