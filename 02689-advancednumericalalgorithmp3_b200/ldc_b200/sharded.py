@@ -74,14 +74,23 @@ def _allgather_blocks(local: np.ndarray, counts, dtype):
     return np.concatenate([out[r, :counts[r]] for r in range(world)], axis=0)
 
 
+def interleave_permutation(n_cases: int, world: int) -> np.ndarray:
+    """Order in which the cavities are laid out before the contiguous split so that rank r gets cavities r, r + world,
+    r + 2 world, ...: a sweep ordered by Re or corner_smoothing then hands every rank the same mix of short and long solves
+    (the block sizes are those of `shard_bounds`)."""
+    return np.concatenate([np.arange(r, n_cases, world) for r in range(world)]) if n_cases else np.zeros(0, dtype=np.int64)
+
+
 def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fsg", fields: str = "rank0",
-                local_solver=None, device=None, **solver_kw) -> SweepResult:
+                local_solver=None, device=None, balance: str = "block", **solver_kw) -> SweepResult:
     """Solve B = len(Re) cavities (per-cavity Re and corner_smoothing; everything in solver_kw is shared),
     sharded over the ranks of the initialised process group (or on this process alone if there is none).
 
     kind   : "fsg" (solve_fsg_batched) or "sg" (solve_sg_batched)
     fields : "rank0" gathers u, v, p on rank 0 only, "all" on every rank, "none" skips the field gather
     local_solver : override of the per-rank solver (tests); signature of solve_fsg_batched
+    balance : "block" -- rank r solves the contiguous block `shard_bounds` gives it; "interleave" -- rank r solves
+              cavities r, r + world, ... (`interleave_permutation`); results come back in the caller's order either way
     """
     import torch
 
@@ -91,6 +100,15 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
     dist = _dist()
     rank = dist.get_rank() if dist else 0
     world = dist.get_world_size() if dist else 1
+    if balance not in ("block", "interleave"):
+        raise ValueError("balance must be 'block' or 'interleave'")
+    n_all = Re.size
+    perm = interleave_permutation(n_all, world) if balance == "interleave" and world > 1 else None
+    if perm is not None:
+        Re, cs, tol = Re[perm], cs[perm], tol[perm]
+        solver_kw = {k: (([val[i] for i in perm] if isinstance(val, (list, tuple)) else np.asarray(val)[perm])
+                         if not isinstance(val, str) and np.ndim(val) == 1 and len(val) == n_all else val)
+                     for k, val in solver_kw.items()}
     bounds = shard_bounds(Re.size, world)
     lo, hi = bounds[rank]
     counts = [b - a for a, b in bounds]
@@ -122,5 +140,9 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
         gp = _allgather_blocks(r.p, counts, torch.float64)
         if fields == "all" or rank == 0:
             u, v, p = gu, gv, gp
+    if perm is not None:   # back to the caller's order
+        inv = np.argsort(perm)
+        scal = scal[inv]
+        u, v, p = (None if a is None else a[inv] for a in (u, v, p))
     return SweepResult(np.rint(scal[:, 0]).astype(np.int64), scal[:, 1] > 0.5, scal[:, 2] > 0.5, scal[:, 3], u, v, p,
                        float(kms), bounds)

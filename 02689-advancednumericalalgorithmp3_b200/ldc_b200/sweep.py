@@ -240,7 +240,7 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
                           prolongation=k0["prolongation_method"])
         t0 = time.time()
         r = solve(N, per["Re"], per["corner_smoothing"], per["tolerance"], int(k0["max_iterations"]), kind=kind,
-                  fields="all", device=device, **shared)
+                  fields="all", device=device, balance="interleave", **shared)   # sweeps arrive ordered by Re / smoothing
         wall = time.time() - t0
         # post-processing of this rank's shard only (validation-error kernel, streamfunction solves), then one
         # all-gather of the small per-trial records

@@ -22,6 +22,7 @@ ap.add_argument("--N", type=int, default=32)
 ap.add_argument("--grid", type=int, default=8)
 ap.add_argument("--max-iter", type=int, default=2_000_000)
 ap.add_argument("--tol", type=float, default=1e-6)
+ap.add_argument("--balance", default="block", choices=["block", "interleave"])
 ap.add_argument("--out", default="gpurun_out/sweep_demo.json")
 args = ap.parse_args()
 
@@ -43,21 +44,24 @@ cs, Re = np.meshgrid(np.linspace(0.02, 0.35, args.grid), np.linspace(100, 1000, 
 cs, Re = cs.ravel(), Re.ravel()
 torch.cuda.synchronize()
 t0 = time.perf_counter()
-r = solve_sweep(args.N, Re, cs, args.tol, args.max_iter, kind="fsg", n_levels=2, coarse_tolerance_factor=1.0)
+r = solve_sweep(args.N, Re, cs, args.tol, args.max_iter, kind="fsg", n_levels=2, coarse_tolerance_factor=1.0, balance=args.balance)
 torch.cuda.synchronize()
 wall = time.perf_counter() - t0
 if rank == 0:
-    # spot check: three cavities solved alone must reproduce the sharded result bit for bit
+    # spot check: three cavities solved alone (AUTO may pick another kernel for a batch of one: same iteration count,
+    # fields equal to rounding) must reproduce the sharded result
     pick = [0, Re.size // 2, Re.size - 1]
-    ok = True
+    ok, worst = True, 0.0
     for k in pick:
         one = ldc_b200.solve_fsg_batched(args.N, Re[k:k + 1], args.tol, args.max_iter, corner_smoothing=cs[k:k + 1],
                                          n_levels=2, coarse_tolerance_factor=1.0, device=local)
-        ok &= int(one.iterations[0]) == int(r.iterations[k]) and np.array_equal(one.u[0], r.u[k])
-    out = dict(N=args.N, cavities=int(Re.size), world=world, wall_s=wall, kernel_ms_max=r.kernel_ms,
+        ok &= int(one.iterations[0]) == int(r.iterations[k])
+        worst = max(worst, float(np.linalg.norm(one.u[0] - r.u[k]) / np.linalg.norm(r.u[k])))
+    ok &= worst < 1e-10
+    out = dict(N=args.N, cavities=int(Re.size), world=world, balance=args.balance, wall_s=wall, kernel_ms_max=r.kernel_ms,
                converged=int(r.converged.sum()), diverged=int(r.diverged.sum()),
                total_iterations=int(r.iterations.sum()), iters_min=int(r.iterations.min()), iters_max=int(r.iterations.max()),
-               cavity_steps_per_s=float(r.iterations.sum() / wall), spot_check_bitwise=bool(ok), bounds=r.bounds)
+               cavity_steps_per_s=float(r.iterations.sum() / wall), spot_check=bool(ok), spot_check_rel_l2=worst, bounds=r.bounds)
     print(json.dumps(out))
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, "w"), indent=1)

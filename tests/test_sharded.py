@@ -36,7 +36,7 @@ def _fake_solver(N, Re, tol, max_iter, *, corner_smoothing, device, **kw):
     return FSGResult(u, v, p, (10 * Re).astype(np.int64), ~div, div, np.where(div, np.nan, 1e-7 * Re), kernel_ms=float(B))
 
 
-def _worker(rank, world, port, B, q):
+def _worker(rank, world, port, B, q, balance="block"):
     import torch.distributed as dist
 
     from ldc_b200.sharded import solve_sweep
@@ -47,15 +47,27 @@ def _worker(rank, world, port, B, q):
         Re = np.linspace(100, 1000, B)
         cs = np.linspace(0.02, 0.35, B)
         kw = dict(CFL=np.linspace(1.0, 2.0, B), corner_treatment=["smoothing"] * B, n_levels=2) if B == 5 else {}
-        r = solve_sweep(6, Re, cs, 1e-6, 100, fields="rank0", local_solver=_fake_solver, **kw)
+        r = solve_sweep(6, Re, cs, 1e-6, 100, fields="rank0", local_solver=_fake_solver, balance=balance, **kw)
         q.put((rank, r.iterations, r.converged, r.diverged, r.rel_residual, None if r.u is None else r.u.copy(),
                None if r.p is None else r.p.copy(), r.kernel_ms, r.bounds))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("B", [5, 8, 1])
-def test_sweep_sharded_over_two_gloo_ranks_equals_unsharded(B):
+def test_interleave_permutation():
+    from ldc_b200.sharded import interleave_permutation
+
+    assert interleave_permutation(7, 3).tolist() == [0, 3, 6, 1, 4, 2, 5]
+    assert interleave_permutation(4, 1).tolist() == [0, 1, 2, 3] and interleave_permutation(0, 2).size == 0
+    for B, W in ((1024, 8), (5, 2), (1, 4), (13, 5)):
+        perm, lo = interleave_permutation(B, W), 0
+        assert sorted(perm.tolist()) == list(range(B))
+        for r, (a, b) in enumerate(shard_bounds(B, W)):   # the block sizes are those of the contiguous split
+            assert perm[a:b].tolist() == list(range(r, B, W))
+
+
+@pytest.mark.parametrize("B,balance", [(5, "block"), (8, "block"), (1, "block"), (5, "interleave"), (8, "interleave")])
+def test_sweep_sharded_over_two_gloo_ranks_equals_unsharded(B, balance):
     import torch.multiprocessing as mp
 
     with socket.socket() as s:
@@ -63,7 +75,7 @@ def test_sweep_sharded_over_two_gloo_ranks_equals_unsharded(B):
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, B, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, B, q, balance)) for r in range(2)]
     for p in procs:
         p.start()
     got = sorted((q.get(timeout=120) for _ in procs), key=lambda t: t[0])
