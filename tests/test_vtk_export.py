@@ -99,3 +99,31 @@ def test_validation_table_matches_the_reference(tmp_path, monkeypatch):
     logged.clear()
     s.mlflow_log_validation_table()
     assert not logged
+
+
+import pytest
+
+
+@pytest.mark.gpu
+def test_solve_then_export_matches_the_reference_file_content(built_lib, golden, tmp_path):
+    """The whole tail of main.py's run flow on the device path: FSGSolver.solve() (Re=100, N=24), then to_vtk().save();
+    the arrays in the file against those the reference's own solve + to_vtk produced (fixture vtk.npz)."""
+    from ldc_b200 import vts
+
+    g = golden.vtk
+    s = built_lib.FSGSolver(**KW)
+    s.solve()
+    path = os.path.join(tmp_path, "solution.vts")
+    s.to_vtk().save(path)
+    s.close()
+    back = vts.read_vts(path)
+
+    def rel(a, b):
+        return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+    assert rel(back["u"], g["grid_u"]) < 1e-10 and rel(back["v"], g["grid_v"]) < 1e-10
+    assert rel(back["pressure"], g["grid_pressure"]) < 1e-9
+    assert rel(back["velocity_magnitude"], g["grid_velocity_magnitude"]) < 1e-10
+    assert rel(back["vorticity"], g["grid_vorticity"]) < 1e-9
+    assert rel(back["velocity"], g["grid_velocity"]) < 1e-10
+    assert back.field_data["solver"] == "spectral_fsg" and back.field_data["N"][0] == 24
