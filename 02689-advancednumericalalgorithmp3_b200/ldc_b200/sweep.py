@@ -384,6 +384,10 @@ def main(argv=None):
     if "RANK" in os.environ and not dist.is_initialized():
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo")
     rank = dist.get_rank() if dist.is_initialized() else 0
+    t0 = time.time()
+    if dist.is_initialized():
+        dist.barrier()   # brings the communicator up (seconds for NCCL on 8 GPUs) outside the sweep's own clock
+    comm_setup = time.time() - t0
     objective = "fv_l2_error"
     overrides = []
     for ov in args.overrides:
@@ -397,7 +401,7 @@ def main(argv=None):
     wall = time.time() - t0
     if rank == 0:
         best = min(res, key=lambda r: r.objective) if res else None
-        summary = dict(trials=len(res), groups=len({r.group for r in res}), wall_s=wall, objective=objective,
+        summary = dict(trials=len(res), groups=len({r.group for r in res}), wall_s=wall, comm_setup_s=comm_setup, objective=objective,
                        converged=sum(r.metrics["converged"] for r in res),
                        best=dict(index=best.index, overrides=best.overrides, objective=best.objective) if best else None)
         print(json.dumps(summary))
