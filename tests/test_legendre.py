@@ -1,0 +1,65 @@
+"""`basis_type: legendre` (conf/solver/spectral/sg.yaml:19; LegendreLobattoBasis spectral/basis/spectral.py:326-408): the
+operators on the host and the device path against tests/golden/legendre.npz, minted by make_golden_legendre.py from the
+unmodified reference.  Legendre-Gauss-Lobatto nodes are symmetric about the mid-point like the Chebyshev ones, so the
+even-odd kernels apply unchanged; these tests are what says so."""
+import numpy as np
+import pytest
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.mark.parametrize("N", [16, 21])
+def test_legendre_operators_match_reference(golden, N):
+    from ldc_b200 import operators as ops
+
+    g = golden.legendre
+    lv = ops.build_level(N, N, 1.0, 1.0, "legendre")
+    assert np.max(np.abs(lv.x - g[f"x_{N}"])) < 1e-15
+    assert rel(lv.Dx, g[f"Dx_{N}"]) < 1e-13 and rel(lv.Dxx, g[f"Dxx_{N}"]) < 1e-12
+    assert rel(lv.Ix, g[f"Ix_{N}"]) < 1e-12 and rel(lv.W, g[f"W_{N}"]) < 1e-13
+    assert abs(lv.dx_min - float(g[f"dxmin_{N}"])) < 1e-16
+    # the symmetry the parity kernels rest on: D is centro-antisymmetric, D^2 and the quadrature centro-symmetric
+    # (to rounding, relative to the largest entry -- as for the reference's own matrices)
+    assert np.max(np.abs(lv.Dx + lv.Dx[::-1, ::-1])) < 1e-12 * np.max(np.abs(lv.Dx))
+    assert np.max(np.abs(lv.Dxx - lv.Dxx[::-1, ::-1])) < 1e-11 * np.max(np.abs(lv.Dxx))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", ["auto", "resident", "tiled"])
+def test_legendre_trajectory_matches_reference(built_lib, golden, path):
+    g = golden.legendre["traj_21"]
+    with built_lib.BatchedSpectralLDC(21, batch=1, basis="legendre", path=path) as b:
+        b.set_cases(400.0).init_state()
+        done = 0
+        for row, k in zip(g, (1, 5, 10)):
+            b.step(k - done, freeze_pressure=True, want_rel=False)   # SGSolver.step: frozen pressure gradient
+            done = k
+            u, v, p = b.get_state()
+            got = np.concatenate([u.ravel(), v.ravel(), p.ravel()])
+            assert rel(got, row) < 1e-12, (path, k)
+
+
+@pytest.mark.gpu
+def test_legendre_solves_match_reference(built_lib, golden):
+    g = golden.legendre
+    kw = dict(name="spectral", Re=100.0, lid_velocity=1.0, Lx=1.0, Ly=1.0, nx=16, ny=16, tolerance=1e-6,
+              max_iterations=10_000_000, basis_type="legendre", CFL=1.5, beta_squared=5.0, corner_treatment="smoothing",
+              corner_smoothing=0.15, multigrid="none")
+    s = built_lib.SGSolver(**kw)
+    s.solve()
+    meta = g["sg_meta"]
+    assert abs(s.metrics.iterations - int(meta[0])) <= 1 and s.metrics.converged == bool(meta[1])
+    assert rel(s.arrays.u.reshape(17, 17), g["sg_u"]) < 1e-10 and rel(s.arrays.v.reshape(17, 17), g["sg_v"]) < 1e-10
+    assert rel(s.arrays.p.reshape(15, 15), g["sg_p"]) < 1e-10
+    got = np.array([s.metrics.final_energy, s.metrics.final_enstrophy, s.metrics.final_palinstrophy])
+    assert np.max(np.abs(got - meta[3:6]) / np.abs(meta[3:6])) < 1e-9
+    s.close()
+    f = built_lib.FSGSolver(**{**kw, "name": "spectral_fsg", "nx": 24, "ny": 24, "multigrid": "fsg", "n_levels": 2,
+                               "coarse_tolerance_factor": 1.0, "prolongation_method": "fft", "restriction_method": "fft"})
+    f.solve()
+    assert abs(f.metrics.iterations - int(g["fsg_meta"][0])) <= 1 and f.metrics.converged
+    assert rel(f.arrays.u.reshape(25, 25), g["fsg_u"]) < 1e-10 and rel(f.arrays.v.reshape(25, 25), g["fsg_v"]) < 1e-10
+    assert rel(f.arrays.p.reshape(23, 23), g["fsg_p"]) < 1e-10
+    f.close()
