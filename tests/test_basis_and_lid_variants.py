@@ -63,3 +63,21 @@ def test_legendre_solves_match_reference(built_lib, golden):
     assert rel(f.arrays.u.reshape(25, 25), g["fsg_u"]) < 1e-10 and rel(f.arrays.v.reshape(25, 25), g["fsg_v"]) < 1e-10
     assert rel(f.arrays.p.reshape(23, 23), g["fsg_p"]) < 1e-10
     f.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N", [16, 24])
+def test_saad_regularised_lid_matches_reference(built_lib, golden, N):
+    """`corner_treatment: saad` (conf/experiment/validation/saad-regu/spectral.yaml): FSG at Re=1000 with the polynomial lid
+    u = 16 x^2 (1-x)^2, against tests/golden/saad.npz (make_golden_saad.py, unmodified reference)."""
+    g = golden.saad
+    f = built_lib.FSGSolver(name="spectral_fsg", Re=1000.0, lid_velocity=1.0, Lx=1.0, Ly=1.0, nx=N, ny=N, tolerance=1e-6,
+                            max_iterations=10_000_000, basis_type="chebyshev", CFL=1.5, beta_squared=5.0,
+                            corner_treatment="saad", corner_smoothing=0.15, multigrid="fsg", n_levels=2,
+                            coarse_tolerance_factor=1.0, prolongation_method="fft", restriction_method="fft")
+    f.solve()
+    n = N + 1
+    assert abs(f.metrics.iterations - int(g[f"meta_{N}"][0])) <= 1 and f.metrics.converged
+    assert rel(f.arrays.u.reshape(n, n), g[f"u_{N}"]) < 1e-10 and rel(f.arrays.v.reshape(n, n), g[f"v_{N}"]) < 1e-10
+    assert rel(f.arrays.p.reshape(n - 2, n - 2), g[f"p_{N}"]) < 1e-10
+    f.close()
