@@ -81,3 +81,49 @@ def test_saad_regularised_lid_matches_reference(built_lib, golden, N):
     assert rel(f.arrays.u.reshape(n, n), g[f"u_{N}"]) < 1e-10 and rel(f.arrays.v.reshape(n, n), g[f"v_{N}"]) < 1e-10
     assert rel(f.arrays.p.reshape(n - 2, n - 2), g[f"p_{N}"]) < 1e-10
     f.close()
+
+
+RECT_SG = dict(name="spectral", Re=100.0, lid_velocity=1.0, Lx=2.0, Ly=0.5, nx=20, ny=14, tolerance=1e-6,
+               max_iterations=10_000_000, basis_type="chebyshev", CFL=1.5, beta_squared=5.0, corner_treatment="smoothing",
+               corner_smoothing=0.15, multigrid="none")
+
+
+@pytest.mark.gpu
+def test_rectangular_cavity_trajectory_and_solve_match_reference(built_lib, golden):
+    """Lx != Ly and nx != ny (tests/golden/rect.npz, make_golden_rect.py, unmodified reference): SG on a 20 x 14 grid over
+    [0,2] x [0,0.5] -- operators of different size, the launch-per-stage path -- step by step and to tolerance."""
+    g = golden.rect
+    with built_lib.BatchedSpectralLDC(20, 14, batch=1, Lx=2.0, Ly=0.5) as b:
+        assert b.kernel_name == "tiled"
+        b.set_cases(100.0).init_state()
+        done = 0
+        for row, k in zip(g["sg_traj"], (1, 5, 10)):
+            b.step(k - done, freeze_pressure=True, want_rel=False)
+            done = k
+            u, v, p = b.get_state()
+            assert rel(np.concatenate([u.ravel(), v.ravel(), p.ravel()]), row) < 1e-12, k
+    s = built_lib.SGSolver(**RECT_SG)
+    s.solve()
+    meta = g["sg_meta"]
+    assert abs(s.metrics.iterations - int(meta[0])) <= 1 and s.metrics.converged
+    assert rel(s.arrays.u.reshape(21, 15), g["sg_u"]) < 1e-10 and rel(s.arrays.v.reshape(21, 15), g["sg_v"]) < 1e-10
+    assert rel(s.arrays.p.reshape(19, 13), g["sg_p"]) < 1e-10
+    got = np.array([s.metrics.final_energy, s.metrics.final_enstrophy, s.metrics.final_palinstrophy])
+    assert np.max(np.abs(got - meta[2:5]) / np.abs(meta[2:5])) < 1e-9
+    s.close()
+
+
+@pytest.mark.gpu
+def test_stretched_square_grid_fsg_matches_reference(built_lib, golden):
+    """nx == ny on [0,2] x [0,1]: x and y operators of the same size but different scaling -- the plain resident DMMA
+    kernel with separate x / y operators (the even-odd kernel needs them identical); FSG [12, 24] to tolerance."""
+    g = golden.rect
+    f = built_lib.FSGSolver(**{**RECT_SG, "name": "spectral_fsg", "Lx": 2.0, "Ly": 1.0, "nx": 24, "ny": 24, "multigrid": "fsg",
+                               "n_levels": 2, "coarse_tolerance_factor": 1.0, "prolongation_method": "fft",
+                               "restriction_method": "fft"})
+    f.solve()
+    assert f._batch().kernel_name == "k_resident_rk4"
+    assert abs(f.metrics.iterations - int(g["fsg_meta"][0])) <= 1 and f.metrics.converged
+    assert rel(f.arrays.u.reshape(25, 25), g["fsg_u"]) < 1e-10 and rel(f.arrays.v.reshape(25, 25), g["fsg_v"]) < 1e-10
+    assert rel(f.arrays.p.reshape(23, 23), g["fsg_p"]) < 1e-10
+    f.close()
