@@ -127,3 +127,28 @@ def test_stretched_square_grid_fsg_matches_reference(built_lib, golden):
     assert rel(f.arrays.u.reshape(25, 25), g["fsg_u"]) < 1e-10 and rel(f.arrays.v.reshape(25, 25), g["fsg_v"]) < 1e-10
     assert rel(f.arrays.p.reshape(23, 23), g["fsg_p"]) < 1e-10
     f.close()
+
+
+@pytest.mark.gpu
+def test_fsg_knobs_match_reference(built_lib, golden):
+    """The knobs of conf/solver/spectral/fsg.yaml beyond the defaults (tests/golden/fsg_variants.npz,
+    make_golden_fsg_variants.py): three levels [12, 24, 48] with coarse_tolerance_factor=10 and polynomial prolongation;
+    and an iteration cap that every level hits (the cap is per level, the result unconverged, the one-entry TimeSeries
+    carries 10 x tolerance -- fsg.py:76-114)."""
+    g = golden.fsg_variants
+    base = dict(name="spectral_fsg", Re=100.0, lid_velocity=1.0, Lx=1.0, Ly=1.0, tolerance=1e-6, max_iterations=10_000_000,
+                basis_type="chebyshev", CFL=1.5, beta_squared=5.0, corner_treatment="smoothing", corner_smoothing=0.15,
+                multigrid="fsg", n_levels=2, coarse_tolerance_factor=1.0, prolongation_method="fft", restriction_method="fft")
+    for tag, over in (("three", dict(nx=48, ny=48, n_levels=3, coarse_tolerance_factor=10.0, prolongation_method="polynomial")),
+                      ("capped", dict(nx=24, ny=24, max_iterations=300))):
+        f = built_lib.FSGSolver(**{**base, **over})
+        f.solve()
+        meta, n = g[f"{tag}_meta"], over["nx"] + 1
+        assert abs(f.metrics.iterations - int(meta[0])) <= (1 if tag == "three" else 0)
+        assert f.metrics.converged == bool(meta[1])
+        assert f.metrics.final_residual == pytest.approx(meta[2], rel=1e-12)
+        assert len(f.time_series.rel_iter_residual) == int(meta[3])
+        assert f.time_series.rel_iter_residual[-1] == pytest.approx(meta[4], rel=1e-12)
+        assert rel(f.arrays.u.reshape(n, n), g[f"{tag}_u"]) < 1e-10 and rel(f.arrays.v.reshape(n, n), g[f"{tag}_v"]) < 1e-10
+        assert rel(f.arrays.p.reshape(n - 2, n - 2), g[f"{tag}_p"]) < 1e-10
+        f.close()
