@@ -152,3 +152,32 @@ def test_fsg_knobs_match_reference(built_lib, golden):
         assert rel(f.arrays.u.reshape(n, n), g[f"{tag}_u"]) < 1e-10 and rel(f.arrays.v.reshape(n, n), g[f"{tag}_v"]) < 1e-10
         assert rel(f.arrays.p.reshape(n - 2, n - 2), g[f"{tag}_p"]) < 1e-10
         f.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", ["auto", "resident_eo", "resident", "tiled"])
+def test_non_default_lid_velocity_beta_cfl_match_reference(built_lib, golden, path):
+    """lid_velocity=2, beta_squared=2.5, CFL=1, corner_smoothing=0.08 at Re=200 (tests/golden/params.npz,
+    make_golden_params.py): they enter the lid profile, the continuity residual and the adaptive step."""
+    g = golden.params
+    kw = dict(lid_velocity=2.0, beta_squared=2.5, CFL=1.0, corner_smoothing=0.08)
+    with built_lib.BatchedSpectralLDC(16, batch=1, path=path) as b:
+        b.set_cases(200.0, **kw).init_state()
+        done = 0
+        for row, k in zip(g["traj"], (1, 5, 10)):
+            b.step(k - done, freeze_pressure=True, want_rel=False)
+            done = k
+            u, v, p = b.get_state()
+            assert rel(np.concatenate([u.ravel(), v.ravel(), p.ravel()]), row) < 1e-12, (path, k)
+    if path != "auto":
+        return
+    s = built_lib.SGSolver(name="spectral", Re=200.0, Lx=1.0, Ly=1.0, nx=16, ny=16, tolerance=1e-6, max_iterations=10_000_000,
+                           basis_type="chebyshev", corner_treatment="smoothing", multigrid="none", **kw)
+    s.solve()
+    meta = g["meta"]
+    assert abs(s.metrics.iterations - int(meta[0])) <= 1 and s.metrics.converged == bool(meta[1])
+    assert rel(s.arrays.u.reshape(17, 17), g["u"]) < 1e-10 and rel(s.arrays.v.reshape(17, 17), g["v"]) < 1e-10
+    assert rel(s.arrays.p.reshape(15, 15), g["p"]) < 1e-10
+    got = np.array([s.metrics.final_energy, s.metrics.final_enstrophy, s.metrics.final_palinstrophy])
+    assert np.max(np.abs(got - meta[2:5]) / np.abs(meta[2:5])) < 1e-9
+    s.close()
