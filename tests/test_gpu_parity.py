@@ -398,3 +398,46 @@ def test_streamed_kernel_is_deterministic_and_batch_independent(ldc, N, B):
             u, v, p = s.get_state()
         assert all(np.array_equal(u[0], u[k]) and np.array_equal(p[0], p[k]) for k in range(1, B))
         assert np.array_equal(u[0], runs[0][0][3])
+
+
+@pytest.mark.parametrize("N", [2, 3, 4, 5, 7])
+def test_smallest_grids_against_the_oracle(ldc, N):
+    """The smallest orders the reference accepts (N = 2: one interior node, a 1 x 1 pressure grid): every path that takes
+    the shape against the CPU oracle, from the cold start, both pressure semantics."""
+    from oracle import ldc_oracle as orc
+
+    lv = orc.build_level(N)
+    case = orc.Case(Re=50.0, corner_smoothing=0.3)
+    ul, vl = orc.lid_profile(lv.x, "smoothing", 0.3, 1.0, 1.0)
+    for freeze in (False, True):
+        uo, vo, po = orc.initial_state(lv, ul, vl)
+        for _ in range(6):
+            orc.rk4_step(lv, uo, vo, po, case, ul, vl, freeze_pressure=freeze)
+        for path in SMALL_PATHS + ["auto"]:
+            with ldc.BatchedSpectralLDC(N, batch=2, path=path) as s:
+                s.set_cases([50.0, 50.0], corner_smoothing=0.3).init_state()
+                s.step(6, freeze_pressure=freeze, want_rel=False)
+                u, v, p = s.get_state()
+            for b in range(2):
+                assert rel(u[b], uo) < 1e-12 and rel(v[b], vo) < 1e-12, (N, path, freeze)
+                assert np.linalg.norm(p[b] - po) <= 1e-12 * max(np.linalg.norm(po), 1.0), (N, path, freeze)
+
+
+@pytest.mark.parametrize("N", [129, 130, 160])
+def test_largest_streamed_grid_and_beyond_against_the_oracle(ldc, N):
+    """N = 129 is the last order the streamed DMMA kernel takes (half of the interior = 64 = its block size); past it AUTO
+    falls back to the launch-per-stage path.  Two steps against the oracle."""
+    from oracle import ldc_oracle as orc
+
+    lv = orc.build_level(N)
+    case = orc.Case(Re=400.0, corner_smoothing=0.15)
+    ul, vl = orc.lid_profile(lv.x, "smoothing", 0.15, 1.0, 1.0)
+    uo, vo, po = orc.initial_state(lv, ul, vl)
+    for _ in range(2):
+        orc.rk4_step(lv, uo, vo, po, case, ul, vl, freeze_pressure=False)
+    with ldc.BatchedSpectralLDC(N, batch=1) as s:
+        assert s.kernel_name == ("k_stream_stage" if N <= 129 else "tiled")
+        s.set_cases(400.0).init_state()
+        s.step(2, want_rel=False)
+        u, v, p = s.get_state()
+    assert rel(u[0], uo) < 1e-11 and rel(v[0], vo) < 1e-11 and rel(p[0], po) < 1e-10
