@@ -237,11 +237,12 @@ __device__ __forceinline__ void st_assemble(const double* __restrict__ sVec, con
 // End of an RK4 step: reduce the tile partials in fixed order, add the boundary lines, convergence bookkeeping,
 // next dt, rotate the buffers and store the boundary-condition lines with the new state.
 // 128 threads per cavity; sh = 32 doubles of reduction scratch, shp = ST_TILES x 6 doubles for the tile partials.
-__device__ __forceinline__ void stream_end_body(const StreamParams& P, int b, double* sh, double* shp) {
+// lidv, b2, nu, cfl, tolb: the cavity's constants, fetched by the caller before it waits for the stage kernels.
+__device__ __forceinline__ void stream_end_body(const StreamParams& P, int b, double* sh, double* shp, double lidv, double b2,
+                                                double nu, double cfl, double tolb) {
     const int first = P.first, warmup = P.warmup, nan_exit = P.nan_exit;
     const long long max_iter = P.max_iter;
     const double dx_min = P.dx_min, dy_min = P.dy_min;
-    const double* tol = P.tol;
     double* dt = P.dt;
     CavityStatus st = P.status[b];
     // the tile partials arrive in parallel (one L2 round trip); thread 0 adds them in fixed order below
@@ -293,16 +294,15 @@ __device__ __forceinline__ void stream_end_body(const StreamParams& P, int b, do
             mx[1] = nanmax(mx[1], shp[tl * 6 + 5]);
         }
         const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
-        update_status(st, ures, vres, tol ? tol[b] : -1.0, warmup, max_iter, nan_exit);
+        update_status(st, ures, vres, tolb, warmup, max_iter, nan_exit);
         st.umax = nanmax(mx[0], bm[0]);
         st.vmax = nanmax(mx[1], bm[1]);
         st.pad = nxt;
         P.status[b] = st;
-        const double lidv = P.lidvel[b], b2 = P.beta2[b], nu = 1.0 / P.Re[b];
         const double ua = (lidv > st.umax) ? lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
         const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu / (dx_min * dx_min);
         const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu / (dy_min * dy_min);
-        dt[b] = P.CFL[b] / (lam_x + lam_y);
+        dt[b] = cfl / (lam_x + lam_y);
     }
 }
 
@@ -659,9 +659,12 @@ __global__ void __launch_bounds__(ST_THREADS) k_stream_end(const StreamParams P)
     __shared__ double sh[32], shp[ST_TILES * 6];
     const int b = blockIdx.x;
     pdl_launch_dependents();
+    // per-cavity constants (nothing in the chain writes them): on their way before the wait
+    const double lidv = __ldg(P.lidvel + b), b2 = __ldg(P.beta2 + b), nu = 1.0 / __ldg(P.Re + b), cfl = __ldg(P.CFL + b);
+    const double tolb = P.tol ? __ldg(P.tol + b) : -1.0;
     pdl_wait();
     if (!P.status[b].active) return;
-    stream_end_body(P, b, sh, shp);
+    stream_end_body(P, b, sh, shp, lidv, b2, nu, cfl, tolb);
 }
 
 // After a run: move every cavity's record into buffer 0 so that the next run (or an unpack) finds it there.
