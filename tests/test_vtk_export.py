@@ -127,3 +127,44 @@ def test_solve_then_export_matches_the_reference_file_content(built_lib, golden,
     assert rel(back["vorticity"], g["grid_vorticity"]) < 1e-9
     assert rel(back["velocity"], g["grid_velocity"]) < 1e-10
     assert back.field_data["solver"] == "spectral_fsg" and back.field_data["N"][0] == 24
+
+
+def test_reader_takes_ascii_and_uncompressed_binary(tmp_path):
+    """The two other inline encodings VTK writes (`format="ascii"`, `format="binary"` without a compressor): same grid
+    as the compressed flavour."""
+    import base64
+
+    from ldc_b200 import vts
+
+    pts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 1, 0], [0, 2, 0], [1, 2, 0]], dtype=np.float64)
+    u = np.array([0.5, -1.25, 2.0, 3.5, -4.0, 6.25])
+
+    def raw(a):
+        b = a.tobytes()
+        return base64.b64encode(np.array([len(b)], dtype="<u4").tobytes() + b).decode()
+
+    ascii_file = f"""<?xml version="1.0"?>
+<VTKFile type="StructuredGrid" version="0.1" byte_order="LittleEndian">
+  <StructuredGrid WholeExtent="0 1 0 2 0 0"><Piece Extent="0 1 0 2 0 0">
+    <PointData><DataArray type="Float64" Name="u" format="ascii">{' '.join(repr(float(x)) for x in u)}</DataArray></PointData>
+    <Points><DataArray type="Float64" NumberOfComponents="3" format="ascii">{' '.join(repr(float(x)) for x in pts.ravel())}</DataArray></Points>
+  </Piece></StructuredGrid>
+</VTKFile>"""
+    binary_file = f"""<?xml version="1.0"?>
+<VTKFile type="StructuredGrid" version="0.1" byte_order="LittleEndian" header_type="UInt32">
+  <StructuredGrid WholeExtent="0 1 0 2 0 0"><Piece Extent="0 1 0 2 0 0">
+    <PointData><DataArray type="Float64" Name="u" format="binary">{raw(u)}</DataArray></PointData>
+    <Points><DataArray type="Float64" NumberOfComponents="3" format="binary">{raw(pts)}</DataArray></Points>
+  </Piece></StructuredGrid>
+</VTKFile>"""
+    for name, text in (("a.vts", ascii_file), ("b.vts", binary_file)):
+        path = os.path.join(tmp_path, name)
+        with open(path, "w") as f:
+            f.write(text)
+        g = vts.read_vts(path)
+        assert g.dimensions == (2, 3, 1) and np.array_equal(g.points, pts) and np.array_equal(g["u"], u)
+    bad = os.path.join(tmp_path, "c.vts")
+    with open(bad, "w") as f:
+        f.write(binary_file.replace('format="binary"', 'format="appended"', 1))
+    with pytest.raises(ValueError, match="appended"):
+        vts.read_vts(bad)
