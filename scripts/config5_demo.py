@@ -43,6 +43,8 @@ from ldc_b200 import operators as ops
 from ldc_b200 import postprocess
 from ldc_b200.sharded import solve_sweep
 
+if world > 1:
+    torch.distributed.barrier()   # NCCL's communicator comes up here, not inside the timed solve
 Re = args.Re * (1.0 + 0.02 * np.random.default_rng(1).uniform(-1, 1, args.batch))   # seed 1, 2 % jitter
 torch.cuda.synchronize()
 t0 = time.time()
