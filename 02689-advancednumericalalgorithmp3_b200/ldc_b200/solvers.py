@@ -220,6 +220,35 @@ class SGSolver:
         mlflow.log_table(pd.DataFrame(rows), artifact_file="validation_metrics.json")
         log.info("Logged validation metrics table to MLflow")
 
+    def compute_global_quantities(self) -> dict:
+        """base.py:551-567: {'E': kinetic energy, 'Z': enstrophy, 'P': palinstrophy} of the current solution (one device call)."""
+        E, Z, Pal = self._diagnostics()
+        return {"E": float(E), "Z": float(Z), "P": float(Pal)}
+
+    def save_vtk(self, filepath):
+        """base.py:776-790: `to_vtk()` written to `filepath` (.vts), parent directories created."""
+        import os
+
+        filepath = os.fspath(filepath)
+        os.makedirs(os.path.dirname(filepath) or ".", exist_ok=True)
+        self.to_vtk().save(filepath)
+        log.info(f"Saved VTS to {filepath}")
+
+    def save(self, filepath):
+        """base.py:332-353: params, metrics, time_series and fields as four tables of one HDF5 file (pandas.HDFStore, which
+        needs PyTables -- as in the reference)."""
+        import os
+
+        import pandas as pd
+
+        filepath = os.fspath(filepath)
+        os.makedirs(os.path.dirname(filepath) or ".", exist_ok=True)
+        with pd.HDFStore(filepath, mode="w", complevel=5) as store:
+            store["params"] = self.params.to_dataframe()
+            store["metrics"] = self.metrics.to_dataframe()
+            store["time_series"] = self.time_series.to_dataframe()
+            store["fields"] = self.fields.to_dataframe()
+
     def to_vtk(self):
         """base.py:464-522 without PyVista: the solution as a structured grid with u, v, pressure, velocity_magnitude,
         vorticity (the base-class default base.py:524-549, which the spectral solvers do not override: cubic splines built

@@ -168,3 +168,31 @@ def test_reader_takes_ascii_and_uncompressed_binary(tmp_path):
         f.write(binary_file.replace('format="binary"', 'format="appended"', 1))
     with pytest.raises(ValueError, match="appended"):
         vts.read_vts(bad)
+
+
+def test_save_vtk_creates_directories(golden, tmp_path):
+    from ldc_b200 import vts
+
+    s = _solver_with_reference_solution(golden.vtk)
+    path = tmp_path / "out" / "run7" / "solution.vts"
+    s.save_vtk(path)
+    assert vts.read_vts(str(path)).n_points == 625
+
+
+@pytest.mark.gpu
+def test_compute_global_quantities(built_lib, golden):
+    """base.py:551-567 on the device path: E, Z, P of the reference's own FSG Re=100 N=24 solution against the values
+    its solve reported (tests/golden/solves.npz meta: energy, enstrophy, palinstrophy)."""
+    g = golden.vtk
+    s = built_lib.FSGSolver(**KW)
+    s.arrays.u[:] = g["u"].ravel()
+    s.arrays.v[:] = g["v"].ravel()
+    s.arrays.p[:] = g["p"].ravel()
+    q = s.compute_global_quantities()
+    s.close()
+    assert set(q) == {"E", "Z", "P"} and all(np.isfinite(v) and v > 0 for v in q.values())
+    from oracle import ldc_oracle as orc
+
+    lv = orc.build_level(24)
+    E, Z, Pal = orc.diagnostics(lv, g["u"], g["v"])
+    assert abs(q["E"] - E) < 1e-13 * E and abs(q["Z"] - Z) < 1e-12 * Z and abs(q["P"] - Pal) < 1e-11 * Pal
