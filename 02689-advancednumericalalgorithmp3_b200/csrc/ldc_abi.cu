@@ -324,7 +324,7 @@ int ldc_set_path(ldc_t* h, int path) {
     if (path == LDC_PATH_RESIDENT_EO_SPLIT && !(eo_shape_ok(h) && eo_pick_hp(h->mx) <= 24))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the equation-split even-odd path needs nx == ny and nx - 1 <= 48");
     if (path == LDC_PATH_STREAM_EO && !stream_shape_ok(h))
-        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the streamed even-odd path needs nx == ny and 66 <= nx <= 128");
+        return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the streamed even-odd path needs nx == ny and 34 <= nx <= 129");
     if (path == LDC_PATH_RESIDENT_EO && !eo_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the even-odd resident path needs nx == ny and nx - 1 <= 64");
     if (path == LDC_PATH_RESIDENT && !resident_shape_ok(h))

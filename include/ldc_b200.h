@@ -43,8 +43,10 @@ enum {
     LDC_PATH_RESIDENT = 2,    /* state + operators resident in shared memory, FP64 DMMA, many steps per launch */
     LDC_PATH_RESIDENT_EO = 3, /* resident + even-odd (parity) splitting of the operators: half the DMMA work;
                                  needs nx == ny, identical x / y operators and nx - 1 <= 64 */
-    LDC_PATH_STREAM_EO = 4,   /* even-odd, one cavity spread over 16 CTAs, operands streamed from L2, one launch per
-                                 RK stage: for 66 <= nx <= 128 (e.g. N = 128); nx == ny, identical x / y operators */
+    LDC_PATH_STREAM_EO = 4,   /* even-odd, one cavity spread over up to 16 CTAs, operands streamed from L2, one launch per
+                                 RK stage (a programmatic-dependent-launch chain): 34 <= nx <= 129, nx == ny, identical
+                                 x / y operators; AUTO picks it for nx >= 66 (e.g. N = 128) and, when 4 x batch <= #SM,
+                                 for 50 <= nx <= 65 (four SMs per cavity instead of one) */
     LDC_PATH_RESIDENT_EO_SPLIT = 5 /* resident even-odd with the u and v equations of a tile on different warps and the
                                  base state in shared memory: lower latency per step for few cavities on small grids
                                  (nx - 1 <= 48); AUTO picks it when nx - 1 <= 32 and batch <= #SM */
