@@ -887,6 +887,25 @@ int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int fre
     return export_status(h, iters, converged, diverged, rel_res, nullptr);
 }
 
+int ldc_solve_segment(ldc_t* h, const double* tol, int64_t start_iter, int64_t stop_iter, int64_t max_iter, int warmup,
+                      int freeze_pressure, int nan_exit, int64_t* iters, int32_t* converged, int32_t* diverged,
+                      double* rel_res) {
+    int rc = check_ready(h, "ldc_solve_segment");
+    if (rc) return rc;
+    if (!tol || start_iter < 0 || stop_iter < start_iter || max_iter < stop_iter || warmup < 0)
+        return fail(LDC_ERR_INVALID, "ldc_solve_segment: need tol and 0 <= start_iter <= stop_iter <= max_iter");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = copy_in(h, h->tol, tol, h->B))) return rc;
+    if (stop_iter > start_iter) {
+        if ((rc = run_steps(h, h->tol, start_iter, stop_iter, max_iter, warmup, freeze_pressure ? 1 : 0, nan_exit ? 1 : 0)))
+            return rc;
+    } else if (start_iter == 0) {
+        k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 1;
+    }
+    return export_status(h, iters, converged, diverged, rel_res, nullptr);
+}
+
 int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t max_iter, int warmup, int freeze_pressure,
                       int nan_exit, const double* W, double* hist, int64_t hist_cap, int64_t* iters, int32_t* converged,
                       int32_t* diverged, double* rel_res) {

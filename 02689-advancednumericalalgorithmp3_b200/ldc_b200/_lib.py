@@ -34,6 +34,8 @@ SIGNATURES = {
     "ldc_residual": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "ldc_step": (C.c_int, [_vp, C.c_int64, C.c_int, _vp]),
     "ldc_solve": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp]),
+    "ldc_solve_segment": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp,
+                                    _vp]),
     "ldc_solve_history": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, _vp, C.c_int64, _vp, _vp,
                                     _vp, _vp]),
     "ldc_solve_sampled": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, C.c_int64, _vp, _vp, _vp, _vp, _vp,

@@ -237,25 +237,31 @@ class BatchedSpectralLDC:
             return skip + np.arange(kept, dtype=np.int64)
         return skip + np.linspace(0, kept - 1, max_points, dtype=int).astype(np.int64)
 
-    def solve_history_sampled(self, tolerance, max_iter: int, warmup: int = 10, freeze_pressure: bool = True,
-                              nan_exit: bool = False, skip: int = 10, max_points: int = 1000):
-        """The down-sampled history the reference ends up with, without a record per iteration.
+    # replay route of solve_history_sampled: at most this many snapshot segments (= cavities of the replay batch) ...
+    REPLAY_MAX_SEGMENTS = 512
+    # ... first snapshot spacing (doubled whenever the segment count would pass the limit) ...
+    REPLAY_SEGMENT = 512
+    # ... and only for batches up to this size (larger ones take the two-pass route)
+    REPLAY_MAX_BATCH = 16
+    # ... whose replay needs no more than this for its records (else: two passes on this handle)
+    REPLAY_MAX_BYTES = 128 << 20
 
-        Two passes over the same start state, both on the stepping kernels of `solve` (bitwise reproducible): the first
-        finds every cavity's iteration count, hence which iterations survive the reference's thinning
-        (`sample_iterations`); the second repeats the solve and forms those records only (`ldc_solve_sampled`: one
-        iteration of the history path on a copy of the state, the trajectory is not touched).  Returns
-        (SolveResult, history, iterations): history[b] is (n_b, 7) in the layout of `solve_history`, iterations[b] the
-        0-based iteration of each row.
-        """
-        state0 = self.get_state()
-        first = self.solve(tolerance, max_iter, warmup=warmup, freeze_pressure=freeze_pressure, nan_exit=nan_exit)
-        idx = [self.sample_iterations(n, skip, max_points) for n in first.iterations]
-        rec = np.unique(np.concatenate(idx)) if self.B > 1 else idx[0]
-        if rec.size == 0:
-            return first, [np.zeros((0, 7)) for _ in range(self.B)], idx
-        self.set_state(*state0)
+    def solve_segment(self, tolerance, start: int, stop: int, max_iter: int, warmup: int = 0,
+                      freeze_pressure: bool = False, nan_exit: bool = True) -> SolveResult:
+        """Iterations [start, stop) of the solve `solve(tolerance, max_iter, ...)` (`ldc_solve_segment`): start = 0
+        starts it, start > 0 continues the previous call.  Cutting a solve into segments does not change its steps."""
         tol = _per_case(tolerance, self.B, "tolerance")
+        iters = np.zeros(self.B, dtype=np.int64)
+        conv = np.zeros(self.B, dtype=np.int32)
+        divg = np.zeros(self.B, dtype=np.int32)
+        rel = np.zeros(self.B)
+        _lib.check(self.lib.ldc_solve_segment(self._h, _lib.ptr(tol), int(start), int(stop), int(max_iter), int(warmup),
+                                              int(bool(freeze_pressure)), int(bool(nan_exit)), _lib.ptr(iters),
+                                              _lib.ptr(conv), _lib.ptr(divg), _lib.ptr(rel)), "ldc_solve_segment")
+        return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, self.last_kernel_ms)
+
+    def _sampled_records(self, tol, max_iter, warmup, freeze_pressure, nan_exit, rec):
+        """`ldc_solve_sampled` from the current state: (iters, conv, divg, rel, buf[B, len(rec), 7])."""
         iters = np.zeros(self.B, dtype=np.int64)
         conv = np.zeros(self.B, dtype=np.int32)
         divg = np.zeros(self.B, dtype=np.int32)
@@ -267,12 +273,108 @@ class BatchedSpectralLDC:
                                               int(bool(freeze_pressure)), int(bool(nan_exit)), _lib.ptr(W), rec.size,
                                               _lib.ptr(rec), _lib.ptr(buf), _lib.ptr(iters), _lib.ptr(conv),
                                               _lib.ptr(divg), _lib.ptr(rel)), "ldc_solve_sampled")
+        return iters, conv, divg, rel, buf
+
+    def solve_history_sampled(self, tolerance, max_iter: int, warmup: int = 10, freeze_pressure: bool = True,
+                              nan_exit: bool = False, skip: int = 10, max_points: int = 1000, method: str = "auto"):
+        """The down-sampled history the reference ends up with, without a record per iteration.
+
+        Which iterations survive the reference's thinning (`sample_iterations`) is known once a cavity's iteration count
+        is, so the solve comes first and the records second.  Returns (SolveResult, history, iterations): history[b] is
+        (n_b, 7) in the layout of `solve_history`, iterations[b] the 0-based iteration of each row.  The SolveResult and
+        the final state are those of `solve` (bitwise) on both routes:
+
+        * "replay" (`auto` for batch <= REPLAY_MAX_BATCH): the solve is cut into segments (`ldc_solve_segment`) with a
+          snapshot of the state at every segment start.  The segments are then independent of each other: ONE batch
+          holding a cavity per (cavity, segment), started from the snapshots, takes the steps of a single segment and
+          forms the kept records on the way (`ldc_solve_sampled` on a second handle) -- the time of one segment instead
+          of a second pass over the whole trajectory.
+        * "two_pass": the solve is repeated from the same start state on this handle (the stepping kernels are bitwise
+          reproducible) and the kept records are formed on the way.
+        Records are one iteration of the history path on a canonical copy of the state; they agree with the
+        every-iteration history of `solve_history` to rounding (a replayed segment starts from the unpacked snapshot).
+        """
+        if method not in ("auto", "replay", "two_pass"):
+            raise ValueError("method must be 'auto', 'replay' or 'two_pass'")
+        if method == "auto":
+            method = "replay" if self.B <= self.REPLAY_MAX_BATCH else "two_pass"
+        if method == "replay":
+            return self._sampled_by_replay(tolerance, int(max_iter), warmup, freeze_pressure, nan_exit, skip, max_points)
+        state0 = self.get_state()
+        first = self.solve(tolerance, max_iter, warmup=warmup, freeze_pressure=freeze_pressure, nan_exit=nan_exit)
+        idx = [self.sample_iterations(n, skip, max_points) for n in first.iterations]
+        rec = np.unique(np.concatenate(idx)) if self.B > 1 else idx[0]
+        if rec.size == 0:
+            return first, [np.zeros((0, 7)) for _ in range(self.B)], idx
+        self.set_state(*state0)
+        tol = _per_case(tolerance, self.B, "tolerance")
+        iters, conv, divg, rel, buf = self._sampled_records(tol, max_iter, warmup, freeze_pressure, nan_exit, rec)
         res = SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, first.kernel_ms + self.last_kernel_ms)
         if not np.array_equal(iters, first.iterations):
             raise RuntimeError("solve_history_sampled: the second pass took a different number of iterations "
                                f"({iters.tolist()} vs {first.iterations.tolist()}); use solve_history")
         hist = [buf[b, np.searchsorted(rec, idx[b])] for b in range(self.B)]
         return res, hist, idx
+
+    def _sampled_by_replay(self, tolerance, max_iter, warmup, freeze_pressure, nan_exit, skip, max_points):
+        B = self.B
+        max_seg = max(2, self.REPLAY_MAX_SEGMENTS // B)
+        seg = int(self.REPLAY_SEGMENT)
+        snaps = []   # (iteration, (u, v, p)) at the start of every segment
+        ms, done, res = 0.0, 0, None
+        while True:
+            if len(snaps) == max_seg:   # keep every other snapshot, segments twice as long from here on
+                snaps = snaps[::2]
+                seg *= 2
+            if done % seg == 0:
+                snaps.append((done, self.get_state()))
+            stop = min(max_iter, (done // seg + 1) * seg)
+            res = self.solve_segment(tolerance, done, stop, max_iter, warmup=warmup, freeze_pressure=freeze_pressure,
+                                     nan_exit=nan_exit)
+            ms += res.kernel_ms
+            done = stop
+            if done >= max_iter or not np.any((res.iterations >= done) & ~res.converged & ~res.diverged):
+                break
+        idx = [self.sample_iterations(n, skip, max_points) for n in res.iterations]
+        if sum(i.size for i in idx) == 0:
+            return SolveResult(res.iterations, res.converged, res.diverged, res.rel_residual, ms), \
+                [np.zeros((0, 7)) for _ in range(B)], idx
+        # one replay cavity per (cavity, segment that holds a kept iteration)
+        starts = np.array([it for it, _ in snaps], dtype=np.int64)
+        pairs = sorted({(b, int(j)) for b in range(B) for j in np.unique(np.searchsorted(starts, idx[b], "right") - 1)})
+        slot = {bj: k for k, bj in enumerate(pairs)}
+        offsets = np.unique(np.concatenate([idx[b] - starts[np.searchsorted(starts, idx[b], "right") - 1]
+                                            for b in range(B)]))
+        sel = np.array([b for b, _ in pairs])
+        if len(pairs) * offsets.size * 56 > self.REPLAY_MAX_BYTES:
+            # a very long solve of several cavities: segments so long that the replay batch would need a record buffer of
+            # this size; repeat the solve on this handle instead (the two-pass route from the first snapshot)
+            self.set_state(*snaps[0][1])
+            tol = _per_case(tolerance, B, "tolerance")
+            rec = np.unique(np.concatenate(idx))
+            iters, conv, divg, rel, buf = self._sampled_records(tol, max_iter, warmup, freeze_pressure, nan_exit, rec)
+            if not np.array_equal(iters, res.iterations):
+                raise RuntimeError("solve_history_sampled: the second pass took a different number of iterations "
+                                   f"({iters.tolist()} vs {res.iterations.tolist()}); use solve_history")
+            return SolveResult(iters, conv.astype(bool), divg.astype(bool), rel, ms + self.last_kernel_ms), \
+                [buf[b, np.searchsorted(rec, idx[b])] for b in range(B)], idx
+        with BatchedSpectralLDC(self.nx, self.ny, batch=len(pairs), Lx=self.Lx, Ly=self.Ly, basis=self.basis,
+                                device=self.device) as r:
+            if self.path == "tiled":
+                r.set_path("tiled")
+            r.set_cases(self.Re[sel], self.beta_squared[sel], self.CFL[sel], self.lid_velocity[sel],
+                        u_lid=self.u_lid[sel], v_lid=self.v_lid[sel])
+            r.set_state(*[np.stack([snaps[j][1][f][b] for b, j in pairs]) for f in range(3)])
+            # tolerance 0: a replay cavity never stops by itself (iteration numbers are local to the segment there)
+            _, _, _, _, buf = r._sampled_records(np.zeros(len(pairs)), int(offsets[-1]) + 1, 0, freeze_pressure, nan_exit,
+                                                 offsets)
+            ms += r.last_kernel_ms
+        hist = []
+        for b in range(B):
+            j = np.searchsorted(starts, idx[b], "right") - 1
+            rows = np.array([slot[(b, int(jj))] for jj in j], dtype=np.int64)
+            hist.append(buf[rows, np.searchsorted(offsets, idx[b] - starts[j])] if idx[b].size else np.zeros((0, 7)))
+        return SolveResult(res.iterations, res.converged, res.diverged, res.rel_residual, ms), hist, idx
 
     def diagnostics(self):
         """[B,3] = (energy, enstrophy, palinstrophy)."""

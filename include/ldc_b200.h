@@ -106,6 +106,15 @@ int ldc_step(ldc_t* h, int64_t n_steps, int freeze_pressure, double* rel);
 int ldc_solve(ldc_t* h, const double* tol, int64_t max_iter, int warmup, int freeze_pressure, int nan_exit,
               int64_t* iters, int32_t* converged, int32_t* diverged, double* rel_res);
 
+/* ldc_solve cut into pieces: iterations [start_iter, stop_iter) of the solve whose limit is max_iter (same loop, same
+ * convergence rule: base.py:243-313 / multigrid/fsg.py:1168-1202).  start_iter = 0 starts a solve (status reset);
+ * start_iter > 0 continues the previous call of this handle, whose active cavities have taken exactly start_iter
+ * iterations.  A solve cut into segments takes bitwise the steps of the uncut ldc_solve; the caller may read the state
+ * (ldc_get_state) between segments without disturbing it.  Outputs as ldc_solve (any may be NULL). */
+int ldc_solve_segment(ldc_t* h, const double* tol, int64_t start_iter, int64_t stop_iter, int64_t max_iter, int warmup,
+                      int freeze_pressure, int nan_exit, int64_t* iters, int32_t* converged, int32_t* diverged,
+                      double* rel_res);
+
 /* base.solve with its per-iteration records (base.py:243-313): ldc_solve on the launch-per-stage path, and after every
  * iteration i (0-based) of a cavity, hist[b][i - start_iter][7] = { rel_iter = max(u_res, v_res), ||R_u||, ||R_v||, ||R_p||
  * of the LAST stage's residual on all nodes (what arrays.R_* hold after step(), spectral/sg.py:463-473), energy,

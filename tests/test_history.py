@@ -182,3 +182,101 @@ def test_sampled_history_edge_cases(built_lib):
         for bad in (np.array([5, 5], dtype=np.int64), np.array([7, 3], dtype=np.int64), np.array([300], dtype=np.int64),
                     np.array([-1], dtype=np.int64)):
             assert call(bad) != 0 and "rec_iter" in b.lib.ldc_last_error().decode()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,path,batch", [(16, "auto", 1), (16, "auto", 3), (16, "tiled", 2), (40, "auto", 200), (72, "auto", 2)])
+def test_solve_cut_into_segments_takes_the_steps_of_the_uncut_solve(built_lib, n, path, batch):
+    """ldc_solve_segment: iteration counts, flags, residuals and the final state of a solve cut into uneven segments (with
+    the state read back in between) are bitwise those of ldc_solve."""
+    Re = np.linspace(70.0, 150.0, batch)
+    tol, cap = (2e-3 if n < 72 else 2e-2), 4000
+    with built_lib.BatchedSpectralLDC(n, batch=batch, path=path) as b:
+        b.set_cases(Re).init_state()
+        whole = b.solve(tol, cap, warmup=10, freeze_pressure=True)
+        s_whole = b.get_state()
+        b.init_state()
+        done, cuts = 0, [1, 7, 64, 65, 300, 1000, cap]
+        for stop in cuts:
+            part = b.solve_segment(tol, done, stop, cap, warmup=10, freeze_pressure=True)
+            b.get_state()
+            done = stop
+        s_cut = b.get_state()
+    assert whole.converged.all() and whole.iterations.max() > 65
+    assert np.array_equal(part.iterations, whole.iterations) and np.array_equal(part.converged, whole.converged)
+    assert np.array_equal(part.rel_residual, whole.rel_residual)
+    for a, c in zip(s_whole, s_cut):
+        assert np.array_equal(a, c)
+
+
+@pytest.mark.gpu
+def test_solve_segment_argument_checks(built_lib):
+    from ldc_b200 import _lib
+
+    with built_lib.BatchedSpectralLDC(16, batch=1) as b:
+        b.set_cases(100.0).init_state()
+        tol = np.full(1, 1e-3)
+        for start, stop, cap in ((-1, 5, 10), (5, 3, 10), (0, 11, 10)):
+            assert b.lib.ldc_solve_segment(b._h, _lib.ptr(tol), start, stop, cap, 0, 0, 1, None, None, None, None) != 0
+            assert "ldc_solve_segment" in b.lib.ldc_last_error().decode()
+        assert b.lib.ldc_solve_segment(b._h, None, 0, 5, 10, 0, 0, 1, None, None, None, None) != 0
+        r = b.solve_segment(1e-3, 0, 0, 10)            # an empty first segment resets the status
+        assert r.iterations[0] == 0 and not r.converged[0]
+        r = b.solve_segment(1e-3, 0, 10, 10)
+        assert r.iterations[0] == 10
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,batch,seg,max_seg", [(16, 1, 64, 512), (16, 3, 64, 12), (16, 2, 32, 7), (40, 1, 64, 512),
+                                                 (72, 1, 32, 512)])
+def test_sampled_history_by_replay_equals_the_two_pass_route(built_lib, monkeypatch, n, batch, seg, max_seg):
+    """The replay route (snapshots at segment starts, ONE batch of segments for the records) against the two-pass route:
+    same SolveResult and final state (bitwise), same kept iterations, records equal to rounding; also with a segment
+    limit small enough that snapshots are thinned on the way (even and odd limits)."""
+    cls = built_lib.BatchedSpectralLDC
+    monkeypatch.setattr(cls, "REPLAY_SEGMENT", seg)
+    monkeypatch.setattr(cls, "REPLAY_MAX_SEGMENTS", max_seg)
+    Re = np.linspace(80.0, 140.0, batch)
+    tol, cap, pts = (2e-3 if n < 72 else 2e-2), 4000, 61
+    with cls(n, batch=batch) as b:
+        b.set_cases(Re).init_state()
+        r2, h2, i2 = b.solve_history_sampled(tol, cap, max_points=pts, method="two_pass")
+        s2 = b.get_state()
+        b.init_state()
+        r1, h1, i1 = b.solve_history_sampled(tol, cap, max_points=pts, method="replay")
+        s1 = b.get_state()
+    assert r2.converged.all() and r2.iterations.min() > 2 * seg      # at least three segments each
+    assert np.array_equal(r1.iterations, r2.iterations) and np.array_equal(r1.converged, r2.converged)
+    assert np.array_equal(r1.rel_residual, r2.rel_residual)
+    for a, c in zip(s1, s2):
+        assert np.array_equal(a, c)
+    for b_ in range(batch):
+        assert np.array_equal(i1[b_], i2[b_]) and h1[b_].shape == h2[b_].shape == (pts, 7)
+        assert relcols(h1[b_], h2[b_]).max() < 1e-9
+        assert np.all(h1[b_][:, 4] > 0)
+
+
+@pytest.mark.gpu
+def test_sampled_history_by_replay_edge_cases(built_lib, monkeypatch):
+    """Replay route: a solve shorter than the record warm-up (no records), one that stops at max_iter inside a segment,
+    a cavity that goes non-finite next to one that does not, and the byte limit that sends it back to two passes."""
+    cls = built_lib.BatchedSpectralLDC
+    monkeypatch.setattr(cls, "REPLAY_SEGMENT", 32)
+    with cls(16, batch=2) as b:
+        b.set_cases([100.0, 1000.0], corner_smoothing=[0.15, 0.01], CFL=[1.5, 50.0]).init_state()   # second one blows up
+        r, h, idx = b.solve_history_sampled(1e-12, 7, nan_exit=True, method="replay")
+        assert r.iterations.tolist() == [7, 7] and all(x.shape == (0, 7) for x in h)
+        b.init_state()
+        full, hf = b.solve_history(1e-12, 150, nan_exit=True)
+        assert full.diverged[1] and full.iterations[0] == 150 and 20 < full.iterations[1] < 150
+        for limit in (cls.REPLAY_MAX_BYTES, 1):
+            monkeypatch.setattr(cls, "REPLAY_MAX_BYTES", limit)
+            b.init_state()
+            r, h, idx = b.solve_history_sampled(1e-12, 150, nan_exit=True, max_points=25, method="replay")
+            assert np.array_equal(r.iterations, full.iterations) and np.array_equal(r.diverged, full.diverged)
+            assert idx[0][-1] == 149 and idx[1][-1] == full.iterations[1] - 1
+            assert relcols(h[0], hf[0][idx[0]]).max() < 1e-9
+            early = idx[1] < full.iterations[1] // 2
+            assert early.any() and relcols(h[1][early], hf[1][idx[1][early]]).max() < 1e-6   # a trajectory that blows up
+    with pytest.raises(ValueError):
+        b.solve_history_sampled(1e-3, 10, method="nope")
