@@ -120,6 +120,17 @@ def run_cpu_windows(args, windows: int, seconds: float):
     return cores, rates
 
 
+def cpu_step_seconds(N: int, seconds: float = 2.0) -> float:
+    """Seconds per RK4 pseudo-step of ONE cavity at order N with the oracle port (one single-threaded process, second of
+    two windows): a single cavity's solve is a serial chain of steps, on the CPU as on the GPU."""
+    env = dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    so = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-worker", "--worker-index", "0", "--windows", "2",
+                         "--seconds", str(seconds), "--N", str(N), "--batch", "1"], stdout=subprocess.PIPE, env=env,
+                        text=True, check=True).stdout
+    n, el = json.loads(so.strip().splitlines()[-1])[1]
+    return el / n
+
+
 def reference_arm(args):
     """--impl reference: the reference's CPU algorithm (oracle port; the reference itself is Python under
     /root/reference and does not exist on the GPU box) on every host core, same metric/config/unit."""
@@ -370,6 +381,15 @@ def gpu_arm(args):
         tt = {"config": "FSG Re=1000 N=30 levels [15,30] cs=0.15 tol=1e-6, single cavity", "wall_s": time.perf_counter() - w0,
               "kernel_s": r.kernel_ms * 1e-3, "iterations": int(r.iterations[0]), "converged": bool(r.converged[0]),
               "reference_iterations": 123483}
+        if not args.no_cpu_baseline:
+            # the same solve with the CPU port, from a bounded sample: seconds per step of the oracle at each level's
+            # order (2 s windows) x the iterations this solve took on that level (those of the reference)
+            lev = [int(np.asarray(x).ravel()[0]) for x in r.per_level_iterations]
+            per = [cpu_step_seconds(int(n)) for n in r.orders]
+            tt["cpu_port"] = {"wall_s_estimated": float(sum(a * b for a, b in zip(lev, per))), "orders": [int(n) for n in r.orders],
+                              "iterations_per_level": lev, "cpu_us_per_step": [1e6 * x for x in per], "cores": 1,
+                              "sample": "2 s of oracle rk4_step per level (one process, one BLAS thread) x the iteration "
+                                        "count of each level"}
 
     if rank == 0:
         flop_launch = B * P * f_step(N)
