@@ -286,13 +286,15 @@ class BatchedSpectralLDC:
 
         * "replay" (`auto` for batch <= REPLAY_MAX_BATCH): the solve is cut into segments (`ldc_solve_segment`) with a
           snapshot of the state at every segment start.  The segments are then independent of each other: ONE batch
-          holding a cavity per (cavity, segment), started from the snapshots, takes the steps of a single segment and
-          forms the kept records on the way (`ldc_solve_sampled` on a second handle) -- the time of one segment instead
-          of a second pass over the whole trajectory.
+          holding a cavity per (cavity, segment), started from the snapshots on a second handle, takes the steps of a
+          single segment on the history path (`ldc_solve_history`: one launch for the lot on grids that fit an SM) and
+          the kept records are picked from its rows -- the time of one segment instead of a second pass over the whole
+          trajectory.
         * "two_pass": the solve is repeated from the same start state on this handle (the stepping kernels are bitwise
           reproducible) and the kept records are formed on the way.
-        Records are one iteration of the history path on a canonical copy of the state; they agree with the
-        every-iteration history of `solve_history` to rounding (a replayed segment starts from the unpacked snapshot).
+        Either way a record is what the history path forms for that iteration; the routes agree with each other and
+        with the every-iteration history of `solve_history` to rounding (a replayed segment starts from the unpacked
+        snapshot and is stepped by the history kernels).
         """
         if method not in ("auto", "replay", "two_pass"):
             raise ValueError("method must be 'auto', 'replay' or 'two_pass'")
@@ -346,7 +348,8 @@ class BatchedSpectralLDC:
         offsets = np.unique(np.concatenate([idx[b] - starts[np.searchsorted(starts, idx[b], "right") - 1]
                                             for b in range(B)]))
         sel = np.array([b for b, _ in pairs])
-        if len(pairs) * offsets.size * 56 > self.REPLAY_MAX_BYTES:
+        n_local = int(offsets[-1]) + 1
+        if len(pairs) * n_local * 56 > self.REPLAY_MAX_BYTES:
             # a very long solve of several cavities: segments so long that the replay batch would need a record buffer of
             # this size; repeat the solve on this handle instead (the two-pass route from the first snapshot)
             self.set_state(*snaps[0][1])
@@ -365,10 +368,16 @@ class BatchedSpectralLDC:
             r.set_cases(self.Re[sel], self.beta_squared[sel], self.CFL[sel], self.lid_velocity[sel],
                         u_lid=self.u_lid[sel], v_lid=self.v_lid[sel])
             r.set_state(*[np.stack([snaps[j][1][f][b] for b, j in pairs]) for f in range(3)])
-            # tolerance 0: a replay cavity never stops by itself (iteration numbers are local to the segment there)
-            _, _, _, _, buf = r._sampled_records(np.zeros(len(pairs)), int(offsets[-1]) + 1, 0, freeze_pressure, nan_exit,
-                                                 offsets)
-            ms += r.last_kernel_ms
+            # every replay cavity takes the steps of one segment on the history path, ONE launch for the lot where the grid
+            # fits an SM (k_history_fused), with a record per iteration; tolerance 0: a replay cavity never stops by
+            # itself (iteration numbers are local to the segment there)
+            rr, rows = r.solve_history(0.0, n_local, warmup=0, freeze_pressure=freeze_pressure, nan_exit=nan_exit,
+                                       chunk=n_local)
+            ms += rr.kernel_ms
+        buf = np.zeros((len(pairs), n_local, 7))
+        for k, a in enumerate(rows):     # a cavity that went non-finite stopped early: its later rows stay zero
+            buf[k, :a.shape[0]] = a
+        offsets = np.arange(n_local)
         hist = []
         for b in range(B):
             j = np.searchsorted(starts, idx[b], "right") - 1

@@ -381,7 +381,7 @@ def gpu_arm(args):
         tt = {"config": "FSG Re=1000 N=30 levels [15,30] cs=0.15 tol=1e-6, single cavity", "wall_s": time.perf_counter() - w0,
               "kernel_s": r.kernel_ms * 1e-3, "iterations": int(r.iterations[0]), "converged": bool(r.converged[0]),
               "reference_iterations": 123483}
-        if not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline:
             # the same solve with the CPU port, from a bounded sample: seconds per step of the oracle at each level's
             # order (2 s windows) x the iterations this solve took on that level (those of the reference)
             lev = [int(np.asarray(x).ravel()[0]) for x in r.per_level_iterations]
