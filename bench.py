@@ -269,6 +269,11 @@ def gpu_arm(args):
     # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION/INFO) out of it
     if "LDC_KEEP_NCCL_DEBUG" not in os.environ:
         os.environ["NCCL_DEBUG"] = "WARN"
+    # ... and whatever else native code writes to file descriptor 1 (the banner still showed up on some boxes): from here
+    # on fd 1 is stderr, the JSON line goes to a private copy of the original stdout
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; ldc_b200 has no CPU fallback (use --impl reference for the CPU arm)")
 
@@ -436,7 +441,8 @@ def gpu_arm(args):
             line["cpu_baseline"] = cpu_baseline
         if tt is not None:
             line["time_to_tol"] = tt
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     s.close()
     if world > 1:
         dist.barrier()
