@@ -88,7 +88,8 @@ struct ldc_handle {
     double* r_ops = nullptr;
     double* r_state = nullptr;
     size_t r_state_stride = 0;    // doubles per cavity
-    int packed_valid = 0;         // which packed record holds the current state: 0 none, 1 r_state, 2 e_state, 3 s_state (buffer 0)
+    int packed_valid = 0;         // which packed record holds the current state: 0 none, 1 r_state, 2 e_state, 3 s_state (buffer 0),
+                                  // 4 t_state (buffer 0; stream_tma.cuh)
     // even-odd resident path (resident_eo.cuh)
     int HP = 0;
     double* e_ops = nullptr;
@@ -109,6 +110,12 @@ struct ldc_handle {
     // also takes (half size <= 32) can use either
     double* s_ops = nullptr;
     size_t s_stride = 0;
+    // persistent TMA-fed streamed path (stream_tma.cuh): three rotating records per cavity in the k4-interleaved tile layout,
+    // per-cavity operator panels, team barrier counters + mailboxes
+    double* t_state = nullptr;
+    double* t_opsc = nullptr;
+    double* t_team = nullptr;     // [teams] unsigned counters, then [teams] 64-bit mailboxes
+    bool eo_sym = false;          // operators pass the centro-(anti)symmetry test the even-odd kernels rely on
     // per-iteration history of ldc_solve_history: [B][hist_cap][7] records + the quadrature weights
     double* hist = nullptr;
     size_t hist_cap = 0;

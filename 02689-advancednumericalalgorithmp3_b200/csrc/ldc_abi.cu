@@ -1,6 +1,7 @@
 // C ABI of ldc_b200 (include/ldc_b200.h): handle management, host<->device plumbing and the launch
 // sequences of the tiled and resident kernel paths.  No exception crosses the boundary.
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <new>
 #include <vector>
@@ -11,6 +12,7 @@
 #include "resident_eo_split.cuh"
 #include "resident_main.cuh"
 #include "stream_eo.cuh"
+#include "stream_tma.cuh"
 #include "tiled.cuh"
 #include "validate.cuh"
 #include "history_fused.cuh"
@@ -45,10 +47,12 @@ static int copy_out(ldc_handle* h, void* dst, const void* src_dev, size_t bytes)
     return LDC_OK;
 }
 
+// Zero-filled device allocation.  The fill is ordered on the handle's stream (a caller stream may be non-blocking, i.e.
+// not ordered against the legacy default stream a plain cudaMemset would use).
 template <typename T>
-static int dalloc(T** p, size_t n) {
+static int dalloc(ldc_handle* h, T** p, size_t n) {
     LDC_CUDA(cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T)));
-    LDC_CUDA(cudaMemset(*p, 0, std::max<size_t>(n, 1) * sizeof(T)));
+    LDC_CUDA(cudaMemsetAsync(*p, 0, std::max<size_t>(n, 1) * sizeof(T), h->stream));
     return LDC_OK;
 }
 
@@ -149,7 +153,7 @@ static size_t eo_smem_bytes(int HP) {
 
 // the even-odd kernel needs one set of operators for both directions (checked bit for bit in ldc_set_operators)
 static bool eo_ok(const ldc_handle* h) {
-    if (!eo_shape_ok(h) || !h->square_ops) return false;
+    if (!eo_shape_ok(h) || !h->square_ops || !h->eo_sym) return false;
     int max_optin = 0;
     if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return false;
     return eo_smem_bytes(h->HP) <= (size_t)max_optin;
@@ -175,11 +179,26 @@ static bool stream_shape_ok(const ldc_handle* h) {
     const int hh = eo_half(h->mx);
     return h->nx == h->ny && hh > 16 && hh <= ST_HP;   // below: one 16 x 16 tile per block, nothing to spread
 }
-static bool stream_ok(const ldc_handle* h) { return stream_shape_ok(h) && h->square_ops; }
+static bool stream_ok(const ldc_handle* h) { return stream_shape_ok(h) && h->square_ops && h->eo_sym; }
+// persistent TMA-fed variant: needs a cooperative launch (co-resident teams) and its shared memory
+static bool stream_tma_ok(const ldc_handle* h) {
+    if (!stream_ok(h)) return false;
+    int coop = 0, max_optin = 0;
+    if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device) != cudaSuccess || !coop) return false;
+    if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return false;
+    return S2_SMEM_DOUBLES * sizeof(double) <= (size_t)max_optin;
+}
+// which streamed kernel AUTO takes: the persistent one unless LDC_STREAM_TMA=0 (A / B runs)
+static int stream_auto(const ldc_handle* h) {
+    const char* e = getenv("LDC_STREAM_TMA");
+    return (stream_tma_ok(h) && !(e && atoi(e) == 0)) ? 5 : 3;
+}
 
-// 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd, 4 even-odd resident split by equation
+// 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd, 4 even-odd resident split by equation,
+// 5 streamed even-odd, persistent + TMA
 static int pick_kernel(const ldc_handle* h) {
     if (h->path == LDC_PATH_TILED) return 0;
+    if (h->path == LDC_PATH_STREAM_TMA) return stream_tma_ok(h) ? 5 : -1;
     if (h->path == LDC_PATH_RESIDENT_EO_SPLIT) return eo_split_ok(h) ? 4 : -1;
     if (h->path == LDC_PATH_RESIDENT) return resident_ok(h) ? 1 : -1;
     if (h->path == LDC_PATH_RESIDENT_EO) return eo_ok(h) ? 2 : -1;
@@ -188,10 +207,10 @@ static int pick_kernel(const ldc_handle* h) {
     if (eo_split_ok(h) && h->HP <= 16 && h->B <= h->num_sms) return 4;   // measured: no gain at HP = 24
     // few cavities on the largest resident grids (50 <= N <= 65): four SMs per cavity on the streamed path beat one
     // (N = 64: 28.0 k against 16.7 k steps/s for one cavity, 822 k against 614 k for 37; 74 cavities: 1.02 M against 1.23 M)
-    if (stream_ok(h) && eo_half(h->mx) > 24 && eo_half(h->mx) <= 32 && 4LL * h->B <= h->num_sms) return 3;
+    if (stream_ok(h) && eo_half(h->mx) > 24 && eo_half(h->mx) <= 32 && 4LL * h->B <= h->num_sms) return stream_auto(h);
     if (eo_ok(h)) return 2;
     if (resident_ok(h)) return 1;
-    return stream_ok(h) ? 3 : 0;
+    return stream_ok(h) ? stream_auto(h) : 0;
 }
 
 // canonical <-> packed state synchronisation
@@ -199,7 +218,9 @@ static int ensure_canonical(ldc_handle* h) {
     if (h->canon_valid) return LDC_OK;
     const int n1 = h->n1x;
     const dim3 grid((n1 * n1 + 255) / 256, h->B);
-    if (h->packed_valid == 3)
+    if (h->packed_valid == 4)
+        k_s2_unpack_state<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->t_state, (size_t)h->B * S2_STRIDE, h->status, n1);
+    else if (h->packed_valid == 3)
         k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->s_state, h->s_stride, n1, ST_HP);
     else if (h->packed_valid == 2)
         k_unpack_state_eo<<<grid, 256, 0, h->stream>>>(h->u, h->v, h->p, h->e_state, h->e_state_stride, n1, h->HP);
@@ -215,7 +236,9 @@ static int ensure_packed(ldc_handle* h, int kind) {
     if (h->packed_valid == kind) return LDC_OK;
     int rc = ensure_canonical(h);
     if (rc) return rc;
-    if (kind == 2 || kind == 3) {
+    if (kind == 4) {
+        k_s2_pack_state<<<dim3((S2_HP * S2_HP + 255) / 256, h->B), 256, 0, h->stream>>>(h->u, h->v, h->p, h->t_state, h->n1x);
+    } else if (kind == 2 || kind == 3) {
         const int HP = kind == 3 ? ST_HP : h->HP, LD = eo_ld(HP);
         k_pack_state_eo<<<dim3((std::max(HP * LD, 2 * HP) + 255) / 256, h->B), 256, 0, h->stream>>>(
             h->u, h->v, h->p, kind == 3 ? h->s_state : h->e_state, kind == 3 ? h->s_stride : h->e_state_stride, h->n1x, HP);
@@ -241,6 +264,8 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
     if (!out) return fail(LDC_ERR_INVALID, "ldc_create: out is null");
     *out = nullptr;
     if (nx < 2 || ny < 2 || batch < 1) return fail(LDC_ERR_INVALID, "ldc_create: need nx, ny >= 2 and batch >= 1");
+    if (batch > 65535)   // the batch index is gridDim.y / gridDim.z of the per-cavity kernels
+        return fail(LDC_ERR_INVALID, "ldc_create: batch must be <= 65535 (split larger sweeps over several handles)");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
@@ -254,7 +279,7 @@ int ldc_create(ldc_t** out, int nx, int ny, int batch, int device, void* cuda_st
     h->B = batch; h->device = device; h->stream = (cudaStream_t)cuda_stream;
     const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my, B = batch;
     int rc = LDC_OK;
-#define A_(p, n) if (rc == LDC_OK) rc = dalloc(&h->p, (n))
+#define A_(p, n) if (rc == LDC_OK) rc = dalloc(h, &h->p, (n))
     A_(Dx, (size_t)h->n1x * h->n1x); A_(Dxx, (size_t)h->n1x * h->n1x);
     A_(Dy, (size_t)h->n1y * h->n1y); A_(Dyy, (size_t)h->n1y * h->n1y);
     A_(DyT, (size_t)h->n1y * h->n1y); A_(DyyT, (size_t)h->n1y * h->n1y);
@@ -304,7 +329,8 @@ void ldc_destroy(ldc_t* h) {
     cudaSetDevice(h->device);
     double* ptrs[] = {h->Dx, h->Dxx, h->Dy, h->Dyy, h->DyT, h->DyyT, h->Ix, h->Iy, h->IyT, h->Re, h->beta2, h->CFL, h->lidvel,
                       h->ulid, h->vlid, h->u, h->v, h->p, h->u0, h->v0, h->p0, h->Ru, h->Rv, h->Rp, h->ptmp, h->pfull, h->dt,
-                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->s_ops, h->hist, h->Wq, h->fork};
+                      h->tol, h->r_ops, h->r_state, h->e_ops, h->e_state, h->s_state, h->s_partials, h->s_opsc, h->s_ops, h->hist, h->Wq, h->fork, h->t_state,
+                      h->t_opsc, h->t_team};
     for (double* q : ptrs) if (q) cudaFree(q);
     if (h->status) cudaFree(h->status);
     if (h->n_active) cudaFree(h->n_active);
@@ -320,10 +346,10 @@ void ldc_destroy(ldc_t* h) {
 }
 
 int ldc_set_path(ldc_t* h, int path) {
-    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_RESIDENT_EO_SPLIT) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
+    if (!h || path < LDC_PATH_AUTO || path > LDC_PATH_STREAM_TMA) return fail(LDC_ERR_INVALID, "ldc_set_path: bad argument");
     if (path == LDC_PATH_RESIDENT_EO_SPLIT && !(eo_shape_ok(h) && eo_pick_hp(h->mx) <= 24))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the equation-split even-odd path needs nx == ny and nx - 1 <= 48");
-    if (path == LDC_PATH_STREAM_EO && !stream_shape_ok(h))
+    if ((path == LDC_PATH_STREAM_EO || path == LDC_PATH_STREAM_TMA) && !stream_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the streamed even-odd path needs nx == ny and 34 <= nx <= 129");
     if (path == LDC_PATH_RESIDENT_EO && !eo_shape_ok(h))
         return fail(LDC_ERR_UNSUPPORTED, "ldc_set_path: the even-odd resident path needs nx == ny and nx - 1 <= 64");
@@ -346,6 +372,7 @@ const char* ldc_kernel_name(const ldc_t* h) {
         case 2: return "k_resident_eo";
         case 3: return "k_stream_stage";
         case 4: return "k_resident_eo_split";
+        case 5: return "k_stream_tma";
     }
     return "unsupported";
 }
@@ -385,6 +412,37 @@ int ldc_set_operators(ldc_t* h, const double* Dx, const double* Dxx, const doubl
             same = std::memcmp(a.data(), b.data(), sz[q] * sizeof(double)) == 0;
         }
         h->square_ops = same;
+        // The even-odd kernels keep only the D_SA / D_AS, DD_SS / DD_AA and G_SA / G_AS parity blocks: they need D centro-
+        // antisymmetric and DD, I centro-symmetric (nodes symmetric about the mid-point, as the Chebyshev and Legendre
+        // Gauss-Lobatto grids are).  Checked here to 1e-10 of the largest entry; operators that fail it (a mapped or
+        // stretched grid) run on the plain resident / tiled kernels, and a forced even-odd path reports LDC_ERR_UNSUPPORTED.
+        h->eo_sym = false;
+        if (same) {
+            const int n1 = h->n1x, m = h->mx, N = n1 - 1;
+            std::vector<double> d(sx), dd(sx), ix((size_t)n1 * m);
+            LDC_CUDA(cudaMemcpyAsync(d.data(), h->Dx, sx * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(dd.data(), h->Dxx, sx * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            LDC_CUDA(cudaMemcpyAsync(ix.data(), h->Ix, ix.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            LDC_CUDA(cudaStreamSynchronize(h->stream));
+            double md = 0, mdd = 0, mi = 0, ed = 0, edd = 0, ei = 0;
+            for (int i = 0; i < n1; ++i)
+                for (int k = 0; k < n1; ++k) {
+                    const double a = d[(size_t)i * n1 + k], a2 = d[(size_t)(N - i) * n1 + (N - k)];
+                    const double c = dd[(size_t)i * n1 + k], c2 = dd[(size_t)(N - i) * n1 + (N - k)];
+                    md = std::max(md, std::fabs(a));
+                    ed = std::max(ed, std::fabs(a + a2));
+                    mdd = std::max(mdd, std::fabs(c));
+                    edd = std::max(edd, std::fabs(c - c2));
+                }
+            for (int i = 0; i < n1; ++i)
+                for (int k = 0; k < m; ++k) {
+                    const double a = ix[(size_t)i * m + k], a2 = ix[(size_t)(N - i) * m + (m - 1 - k)];
+                    mi = std::max(mi, std::fabs(a));
+                    ei = std::max(ei, std::fabs(a - a2));
+                }
+            const double tol = 1e-10;
+            h->eo_sym = ed <= tol * md && edd <= tol * mdd && ei <= tol * mi;   // (false when an entry is NaN)
+        }
     }
     if (h->r_ops) {
         // G = (D I) rows 1..n-2: the pressure interpolation folded into the derivative (resident.cuh)
@@ -669,11 +727,78 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         return fail(LDC_ERR_UNSUPPORTED, "the requested resident path cannot run this shape (shared memory, or x / y "
                                          "operators differ for the even-odd kernel)");
     const bool resident = kernel == 1 || kernel == 2 || kernel == 4, eo = kernel == 2 || kernel == 4, split = kernel == 4;
-    if (kernel == 3) {
+    if (kernel == 5) {
+        // persistent TMA-fed streamed path (stream_tma.cuh): teams of ntile^2 co-resident CTAs, one cooperative launch per
+        // batch of steps
+        const int ntile = (eo_half(h->mx) + ST_T - 1) / ST_T, team_size = ntile * ntile;
+        const size_t smem = S2_SMEM_DOUBLES * sizeof(double);
+        LDC_CUDA(cudaFuncSetAttribute(k_stream_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma, S2_THREADS, smem));
+        int teams = std::min(h->B, per_sm * h->num_sms / team_size);
+        if (const char* e = getenv("LDC_STREAM_TEAMS")) teams = std::max(1, std::min(teams, atoi(e)));   // A / B measurements
+        if (teams < 1) return fail(LDC_ERR_UNSUPPORTED, "streamed TMA path: a team of CTAs does not fit the device");
+        const size_t bs = (size_t)h->B * S2_STRIDE;
+        if (!h->t_state) {
+            if ((rc = dalloc(h, &h->t_state, 3 * bs))) return rc;
+            if ((rc = dalloc(h, &h->t_opsc, (size_t)h->B * S2_OPS))) return rc;
+            if ((rc = dalloc(h, &h->t_team, 2 * (size_t)h->num_sms))) return rc;
+            if (!h->s_partials && (rc = dalloc(h, &h->s_partials, (size_t)h->B * ST_TILES * 8))) return rc;
+            if (!h->q_data) {
+                if ((rc = dalloc(h, &h->q_data, h->B))) return rc;
+                if ((rc = dalloc(h, &h->q_seq, h->B))) return rc;
+                if ((rc = dalloc(h, &h->q_ctl, 4))) return rc;
+            }
+        }
+        if ((rc = ensure_packed(h, 4))) return rc;
+        LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
+        k_s2_pack_ops<<<dim3(48, h->B), 256, 0, h->stream>>>(h->s_ops, h->Re, h->t_opsc);
+        h->launches += 1;
+        k_s2_begin<<<h->B, 256, 0, h->stream>>>(h->t_state, h->mx, h->status);   // max|u|, max|v| of the start state
+        h->launches += 1;
+        S2Params P;
+        P.ops = h->s_ops; P.opsc = h->t_opsc; P.rec = h->t_state; P.buf_stride = bs;
+        P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
+        P.n1 = h->n1x; P.m = h->mx; P.K4 = (eo_half(h->mx) + 3) / 4 * 4; P.ntile = ntile;
+        P.status = h->status; P.partials = h->s_partials; P.tol = tol_dev;
+        P.warmup = warmup; P.nan_exit = nan_exit; P.freeze = freeze; P.max_iter = max_iter;
+        P.dx_min = h->dx_min; P.dy_min = h->dy_min;
+        P.q_data = h->q_data; P.q_seq = h->q_seq; P.q_ctl = h->q_ctl; P.B = h->B;
+        P.team_bar = reinterpret_cast<unsigned*>(h->t_team);
+        P.team_mail = reinterpret_cast<unsigned long long*>(h->t_team + h->num_sms);
+        h->canon_valid = false;
+        const long long per_launch = 512;   // steps per launch (the host looks at the active count between launches)
+        for (long long done = start; done < stop; done += per_launch) {
+            const long long L = std::min(per_launch, stop - done);
+            P.launch_end = done + L;
+            // steps per queue visit: the whole launch when every cavity has a team, else ~32 visits per team so that the
+            // tail of the launch (teams idling while the last visits finish) stays small
+            P.chunk = L;
+            if (h->B > teams) {
+                const long long c = (L * h->B + 32LL * teams - 1) / (32LL * teams);
+                P.chunk = std::min(L, std::max(4LL, c));
+            }
+            k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
+            LDC_CUDA(cudaMemsetAsync(h->t_team, 0, 2 * (size_t)h->num_sms * sizeof(double), h->stream));
+            void* args[] = {(void*)&P};
+            LDC_CUDA(cudaLaunchCooperativeKernel((const void*)k_stream_tma, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
+                                                 h->stream));
+            h->launches += 2;
+            if (done + per_launch < stop) {
+                int na = 0;
+                if ((rc = count_active(h, &na))) return rc;
+                if (na == 0) break;
+            }
+        }
+        // every cavity's record back into buffer 0
+        k_s2_normalise<<<dim3(64, h->B), 256, 0, h->stream>>>(h->t_state, bs, h->status);
+        k_stream_clear_pad<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
+        h->launches += 2;
+    } else if (kernel == 3) {
         if (!h->s_state) {
-            if ((rc = dalloc(&h->s_state, 3 * (size_t)h->B * h->s_stride))) return rc;
-            if ((rc = dalloc(&h->s_partials, (size_t)h->B * ST_TILES * 8))) return rc;
-            if ((rc = dalloc(&h->s_opsc, (size_t)h->B * 6 * ST_BLK))) return rc;
+            if ((rc = dalloc(h, &h->s_state, 3 * (size_t)h->B * h->s_stride))) return rc;
+            if ((rc = dalloc(h, &h->s_partials, (size_t)h->B * ST_TILES * 8))) return rc;
+            if ((rc = dalloc(h, &h->s_opsc, (size_t)h->B * 6 * ST_BLK))) return rc;
         }
         if ((rc = ensure_packed(h, 3))) return rc;
         // few CTAs (one per SM): double-buffer the chunk panels inside the CTA; many: two CTAs per SM overlap each other
@@ -915,12 +1040,12 @@ int ldc_solve_history(ldc_t* h, const double* tol, int64_t start_iter, int64_t m
         return fail(LDC_ERR_INVALID, "ldc_solve_history: bad argument");
     LDC_CUDA(cudaSetDevice(h->device));
     const size_t nf = (size_t)h->n1x * h->n1y, B = h->B;
-    if (!h->Wq && (rc = dalloc(&h->Wq, nf))) return rc;
+    if (!h->Wq && (rc = dalloc(h, &h->Wq, nf))) return rc;
     if (h->hist_cap < (size_t)hist_cap) {
         if (h->hist) cudaFree(h->hist);
         h->hist = nullptr;
         h->hist_cap = 0;
-        if ((rc = dalloc(&h->hist, B * (size_t)hist_cap * HIST_W))) return rc;
+        if ((rc = dalloc(h, &h->hist, B * (size_t)hist_cap * HIST_W))) return rc;
         h->hist_cap = (size_t)hist_cap;
     }
     if ((rc = copy_in(h, h->tol, tol, B))) return rc;
@@ -965,13 +1090,13 @@ int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup,
     LDC_CUDA(cudaSetDevice(h->device));
     const size_t nf = (size_t)h->n1x * h->n1y, ni = (size_t)h->mx * h->my, B = h->B;
     const size_t st_doubles = (B * sizeof(CavityStatus) + 7) / 8;
-    if (!h->Wq && (rc = dalloc(&h->Wq, nf))) return rc;
-    if (!h->fork && (rc = dalloc(&h->fork, st_doubles + B * (2 * nf + ni)))) return rc;
+    if (!h->Wq && (rc = dalloc(h, &h->Wq, nf))) return rc;
+    if (!h->fork && (rc = dalloc(h, &h->fork, st_doubles + B * (2 * nf + ni)))) return rc;
     if (h->hist_cap < (size_t)n_rec) {
         if (h->hist) cudaFree(h->hist);
         h->hist = nullptr;
         h->hist_cap = 0;
-        if ((rc = dalloc(&h->hist, B * (size_t)n_rec * HIST_W))) return rc;
+        if ((rc = dalloc(h, &h->hist, B * (size_t)n_rec * HIST_W))) return rc;
         h->hist_cap = (size_t)n_rec;
     }
     if ((rc = copy_in(h, h->tol, tol, B))) return rc;

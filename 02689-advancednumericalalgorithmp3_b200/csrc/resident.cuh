@@ -187,7 +187,8 @@ __device__ __forceinline__ void store_status(CavityStatus* p, const CavityStatus
 // Protocol: bounded ring with per-slot sequence numbers (slot free for ticket t when seq == t, full when
 // seq == t + 1); every CTA of the launch is co-resident, so the spins cannot deadlock.
 struct CavityQueue {
-    __device__ static int pop(const ResParams& P) {
+    template <class PT>
+    __device__ static int pop(const PT& P) {
         const unsigned h = atomicAdd(&P.q_ctl[0], 1u);
         const unsigned slot = h % (unsigned)P.B;
         volatile unsigned* seq = P.q_seq + slot;
@@ -202,7 +203,8 @@ struct CavityQueue {
         *seq = h + (unsigned)P.B;
         return b;
     }
-    __device__ static void push(const ResParams& P, int b) {
+    template <class PT>
+    __device__ static void push(const PT& P, int b) {
         const unsigned t = atomicAdd(&P.q_ctl[1], 1u);
         const unsigned slot = t % (unsigned)P.B;
         volatile unsigned* seq = P.q_seq + slot;
@@ -211,7 +213,8 @@ struct CavityQueue {
         __threadfence();
         *seq = t + 1u;
     }
-    __device__ static void retire(const ResParams& P) { atomicSub(&P.q_ctl[2], 1u); }
+    template <class PT>
+    __device__ static void retire(const PT& P) { atomicSub(&P.q_ctl[2], 1u); }
 };
 
 // Fill the queue with the cavities that still have work in this launch, in index order (one block).

@@ -1,0 +1,1064 @@
+// Persistent TMA-fed streamed even-odd path (grids whose parity state does not fit one SM: 34 <= N <= 129).
+//
+// Same parity algebra and tile shape as stream_eo.cuh (a cavity spread over up to 16 CTAs, each owning a 16 x 16 tile
+// of all four parity blocks of both momentum equations), but
+//   * ONE cooperative launch runs many RK4 steps: a team of (tiles per cavity) co-resident CTAs pops a cavity from the
+//     work queue, advances it `chunk` steps and hands it back.  The stages of a step are separated by a team barrier in
+//     global memory (release / acquire counter) instead of a kernel boundary, and the end-of-step reduction (convergence
+//     norms, next dt) is done redundantly, in fixed order, by the idle producer warp of every CTA of the team.
+//   * operand panels arrive by TMA bulk copies (cp.async.bulk, SASS UBLKCP) with mbarrier completion into a ring of
+//     S2_SLOTS chunk slots: a producer warp issues, eight consumer warps wait on the slot's "full" barrier and hand the
+//     slot back through its "empty" barrier -- no CTA-wide barrier and no cp.async wait inside the K loop.
+//   * state and operators live in global memory in a k4-interleaved tile layout: for a 16-row tile and one k4-step (four
+//     consecutive k) the 16 x 4 doubles of a block are contiguous, [row][k % 4].  Every chunk panel is then ONE contiguous
+//     bulk copy, and a DMMA fragment load (lane (g, t) -> row g, k t) reads 256 contiguous bytes: conflict-free with no
+//     padding.  Every field is stored twice, row-type (A operands) and column-type (its transpose, B operands).
+//   * the two warp groups split K by chunk parity (even chunks: group 0, odd: group 1), swap half of their accumulators
+//     through the two last chunk slots, and EACH runs the epilogue of one 8-column half of the tile.
+//   * the stage input u, v at the thread's own elements are picked out of the row panels as they pass through shared
+//     memory (no global re-read); phi^n comes from the CTA's own earlier stores.
+#pragma once
+#include "stream_eo.cuh"
+
+namespace ldc {
+
+constexpr int S2_HP = ST_HP;                 // padded parity-block edge (64)
+constexpr int S2_NK4 = S2_HP / 4;            // k4-steps per block row
+constexpr int S2_KC4 = 2;                    // k4-steps per chunk (K-chunk of 8)
+constexpr int S2_SLOTS = 5;                  // chunk slots in flight
+constexpr int S2_CONSUMERS = 256;            // 8 warps: (k-group) x (u | v equation) x (row half)
+constexpr int S2_THREADS = S2_CONSUMERS + 128;   // + the producer's warpgroup (setmaxnreg works on warpgroups)
+constexpr int S2_ME = 2 * S2_HP;
+// global record of one cavity (doubles): UV_R | UV_C | P_R | P_C | boundary lines (8 x ME) | 8 corners
+//   X_R[rt][kk][blk][r][kq] = X_blk[16 rt + r][4 kk + kq]      (row-type)
+//   X_C[ct][kk][blk][c][kq] = X_blk[4 kk + kq][16 ct + c]      (column-type: the transpose, row-type)
+constexpr size_t S2_UV = (size_t)4 * S2_NK4 * 8 * 64;
+constexpr size_t S2_P = (size_t)4 * S2_NK4 * 4 * 64;
+constexpr size_t S2_OPS = (size_t)4 * S2_NK4 * 6 * 64;   // per-cavity operators D_SA D_AS nuDD_SS nuDD_AA -G_SA -G_AS, row-type
+constexpr size_t S2_EDGE_OFF = 2 * S2_UV + 2 * S2_P;
+constexpr size_t S2_STRIDE = S2_EDGE_OFF + 8 * S2_ME + 8;
+// one chunk slot (doubles): O at tile rows | O at tile columns | UV rows | UV columns | P rows | P columns
+constexpr int S2_SL_OA = 0, S2_SL_OB = S2_KC4 * 6 * 64, S2_SL_FA = 2 * S2_KC4 * 6 * 64, S2_SL_FB = S2_SL_FA + S2_KC4 * 8 * 64,
+              S2_SL_PA = S2_SL_FB + S2_KC4 * 8 * 64, S2_SL_PB = S2_SL_PA + S2_KC4 * 4 * 64, S2_SLOT = S2_SL_PB + S2_KC4 * 4 * 64;
+constexpr unsigned S2_SLOT_BYTES = S2_SLOT * sizeof(double);
+constexpr size_t S2_SMEM_DOUBLES = (size_t)S2_SLOTS * S2_SLOT   // chunk ring
+                                   + 8 * 256                    // stage input u, v at the tile's own elements
+                                   + 8 * S2_HP + 16 * S2_HP     // boundary-column vectors, boundary lines in parity form
+                                   + 4 * 8 * 32                 // dv/dy hand-over v warps -> u warps
+                                   + 16 * 8 + 80 + 16           // tile partials, reduction scratch, step info
+                                   + 2 * S2_SLOTS + 2;          // mbarriers
+
+__host__ __device__ inline size_t s2_off(int nblk, int tile, int kk, int blk, int r, int kq) {
+    return (((size_t)tile * S2_NK4 + kk) * nblk + blk) * 64 + r * 4 + kq;
+}
+
+struct S2Params {
+    const double* ops;            // eo packed operators (HP = 64): only the 8 boundary-column vectors are read here
+    const double* opsc;           // [B][S2_OPS]
+    double* rec;                  // [3][B][S2_STRIDE] rotating records
+    size_t buf_stride;            // B * S2_STRIDE
+    const double *Re, *beta2, *CFL, *lidvel, *ulid, *vlid;
+    int n1, m, K4, ntile;         // ntile: tiles per block edge that hold data
+    CavityStatus* status;         // status.pad = index of the record holding phi^n
+    double* partials;             // [B][16][8]
+    const double* tol;
+    int warmup, nan_exit, freeze;
+    long long max_iter, launch_end, chunk;
+    double dx_min, dy_min;
+    int* q_data; unsigned* q_seq; unsigned* q_ctl; int B;   // cavity work queue (resident.cuh)
+    unsigned* team_bar;           // [teams] arrivals at the team's stage barriers (zero at launch)
+    unsigned long long* team_mail;// [teams] (visit number << 32) | (cavity + 1), written by the team's leader
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned s2_smem(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s2_smem(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s2_smem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s2_smem(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    const unsigned a = s2_smem(bar);
+    unsigned ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    } while (!ok);
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS UBLKCP)
+__device__ __forceinline__ void bulk_g2s(double* dst, const double* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(s2_smem(dst)), "l"(src), "r"(bytes), "r"(s2_smem(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---- layout conversion kernels -----------------------------------------------------------------------------------------
+// canonical (u, v, p) -> record (row-type and column-type copies of the twelve parity blocks + boundary lines)
+__global__ void k_s2_pack_state(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ p,
+                                double* __restrict__ rec, int n1) {
+    const int b = blockIdx.y, HP = S2_HP, m = n1 - 2, h = eo_half(m), N = n1 - 1;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    double* s = rec + (size_t)b * S2_STRIDE;
+    const double *ub = u + (size_t)b * n1 * n1, *vb = v + (size_t)b * n1 * n1, *pb = p + (size_t)b * m * m;
+    if (e < HP * HP) {
+        const int i = e / HP, k = e % HP;
+        const bool in = (i < h && k < h);
+        const int ip = m - 1 - i, kp = m - 1 - k;
+#pragma unroll
+        for (int f = 0; f < 3; ++f) {
+            double q0 = 0, q1 = 0, q2 = 0, q3 = 0;   // F(i,k) F(i',k) F(i,k') F(i',k')
+            if (in) {
+                if (f < 2) {
+                    const double* F = f ? vb : ub;
+                    q0 = F[(i + 1) * n1 + k + 1]; q1 = F[(ip + 1) * n1 + k + 1];
+                    q2 = F[(i + 1) * n1 + kp + 1]; q3 = F[(ip + 1) * n1 + kp + 1];
+                } else {
+                    q0 = pb[i * m + k]; q1 = pb[ip * m + k]; q2 = pb[i * m + kp]; q3 = pb[ip * m + kp];
+                }
+            }
+            const double blk4[4] = {0.25 * ((q0 + q1) + (q2 + q3)), 0.25 * ((q0 + q1) - (q2 + q3)),
+                                    0.25 * ((q0 - q1) + (q2 - q3)), 0.25 * ((q0 - q1) - (q2 - q3))};   // SS SA AS AA
+            const int nblk = f < 2 ? 8 : 4, b0 = f == 1 ? 4 : 0;
+            double* R = s + (f < 2 ? 0 : 2 * S2_UV);
+            double* C = R + (f < 2 ? S2_UV : S2_P);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                R[s2_off(nblk, i / 16, k / 4, b0 + q, i % 16, k % 4)] = blk4[q];
+                C[s2_off(nblk, k / 16, i / 4, b0 + q, k % 16, i % 4)] = blk4[q];
+            }
+        }
+    }
+    double* ed = s + S2_EDGE_OFF;
+    const int ME = S2_ME;
+    if (e < ME) {
+        const bool in = e < m;
+        ed[e] = in ? ub[e + 1] : 0.0;                         // uW: row 0
+        ed[ME + e] = in ? ub[N * n1 + e + 1] : 0.0;           // uE: row N
+        ed[2 * ME + e] = in ? ub[(e + 1) * n1] : 0.0;         // uS: column 0
+        ed[3 * ME + e] = in ? ub[(e + 1) * n1 + N] : 0.0;     // uN: column N (lid)
+        ed[4 * ME + e] = in ? vb[e + 1] : 0.0;
+        ed[5 * ME + e] = in ? vb[N * n1 + e + 1] : 0.0;
+        ed[6 * ME + e] = in ? vb[(e + 1) * n1] : 0.0;
+        ed[7 * ME + e] = in ? vb[(e + 1) * n1 + N] : 0.0;
+    }
+    if (e < 8) {
+        const double* f = e < 4 ? ub : vb;
+        const int c = e & 3;
+        const int i = (c & 2) ? N : 0, j = (c & 1) ? N : 0;
+        ed[8 * ME + e] = f[i * n1 + j];
+    }
+}
+
+// record -> canonical (u, v, p); bufs = base of the three rotating copies, the cavity's current one is status.pad
+__global__ void k_s2_unpack_state(double* __restrict__ u, double* __restrict__ v, double* __restrict__ p,
+                                  const double* __restrict__ bufs, size_t buf_stride, const CavityStatus* __restrict__ status,
+                                  int n1) {
+    const int b = blockIdx.y, m = n1 - 2, N = n1 - 1, ME = S2_ME;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n1 * n1) return;
+    const double* s = bufs + (size_t)status[b].pad * buf_stride + (size_t)b * S2_STRIDE;
+    const double* ed = s + S2_EDGE_OFF;
+    const int i = e / n1, j = e % n1;
+    double uu, vv;
+    const bool ci = (i == 0 || i == N), cj = (j == 0 || j == N);
+    if (ci && cj) {
+        const int c = (i == N ? 2 : 0) + (j == N ? 1 : 0);
+        uu = ed[8 * ME + c];
+        vv = ed[8 * ME + 4 + c];
+    } else if (i == 0) {
+        uu = ed[j - 1];
+        vv = ed[4 * ME + j - 1];
+    } else if (i == N) {
+        uu = ed[ME + j - 1];
+        vv = ed[5 * ME + j - 1];
+    } else if (j == 0) {
+        uu = ed[2 * ME + i - 1];
+        vv = ed[6 * ME + i - 1];
+    } else if (j == N) {
+        uu = ed[3 * ME + i - 1];
+        vv = ed[7 * ME + i - 1];
+    } else {
+        const int ii = i - 1, jj = j - 1, ip = m - 1 - ii, jp = m - 1 - jj;
+        const int r = ii < ip ? ii : ip, c = jj < jp ? jj : jp;
+        const double sa = ii > ip ? -1.0 : 1.0, sb = jj > jp ? -1.0 : 1.0;
+        double f[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const int nblk = q < 2 ? 8 : 4, b0 = q == 1 ? 4 : 0;
+            const double* R = s + (q < 2 ? 0 : 2 * S2_UV);
+            const double ss = R[s2_off(nblk, r / 16, c / 4, b0 + 0, r % 16, c % 4)];
+            const double sA = R[s2_off(nblk, r / 16, c / 4, b0 + 1, r % 16, c % 4)];
+            const double as = R[s2_off(nblk, r / 16, c / 4, b0 + 2, r % 16, c % 4)];
+            const double aa = R[s2_off(nblk, r / 16, c / 4, b0 + 3, r % 16, c % 4)];
+            f[q] = (ss + sb * sA) + sa * (as + sb * aa);
+        }
+        uu = f[0];
+        vv = f[1];
+        p[(size_t)b * m * m + ii * m + jj] = f[2];
+    }
+    u[(size_t)b * n1 * n1 + e] = uu;
+    v[(size_t)b * n1 * n1 + e] = vv;
+}
+
+// per-cavity operator panels: D as is, DD scaled by nu = 1 / Re, G negated; row-type k4-interleaved layout
+__global__ void k_s2_pack_ops(const double* __restrict__ ops, const double* __restrict__ Re, double* __restrict__ opsc) {
+    const int b = blockIdx.y;
+    const double nu = 1.0 / Re[b];
+    double* dst = opsc + (size_t)b * S2_OPS;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 6 * S2_HP * S2_HP; e += gridDim.x * blockDim.x) {
+        const int blk = e / (S2_HP * S2_HP), i = (e / S2_HP) % S2_HP, k = e % S2_HP;
+        const double sc = blk < 2 ? 1.0 : (blk < 4 ? nu : -1.0);
+        dst[s2_off(6, i / 16, k / 4, blk, i % 16, k % 4)] = sc * ops[(size_t)blk * ST_BLK + i * ST_LD + k];
+    }
+}
+
+// start of a solve: max|u|, max|v| of the record in buffer 0 into the status (the kernel forms dt from them)
+__global__ void __launch_bounds__(256) k_s2_begin(const double* __restrict__ buf0, int m, CavityStatus* __restrict__ status) {
+    __shared__ double sh[2 * 32];
+    const int b = blockIdx.x, h = eo_half(m);
+    const double* rec = buf0 + (size_t)b * S2_STRIDE;
+    double mx[2] = {0.0, 0.0};
+    bool isnan_[2] = {false, false};
+    for (int e = threadIdx.x; e < h * h; e += blockDim.x) {
+        const int i = e / h, k = e % h;
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            double r[4];
+            eo_to_points(rec[s2_off(8, i / 16, k / 4, 4 * f + 0, i % 16, k % 4)], rec[s2_off(8, i / 16, k / 4, 4 * f + 1, i % 16, k % 4)],
+                         rec[s2_off(8, i / 16, k / 4, 4 * f + 2, i % 16, k % 4)], rec[s2_off(8, i / 16, k / 4, 4 * f + 3, i % 16, k % 4)], r);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                isnan_[f] |= (r[q] != r[q]);
+                mx[f] = fmax(mx[f], fabs(r[q]));
+            }
+        }
+    }
+    const double* ed = rec + S2_EDGE_OFF;
+    for (int e = threadIdx.x; e < 4 * S2_ME + 4; e += blockDim.x) {
+        const int q = e < 4 * S2_ME ? e : 8 * S2_ME + (e - 4 * S2_ME);
+        const double a = ed[q], c = ed[q + (e < 4 * S2_ME ? 4 * S2_ME : 4)];
+        isnan_[0] |= (a != a);
+        isnan_[1] |= (c != c);
+        mx[0] = fmax(mx[0], fabs(a));
+        mx[1] = fmax(mx[1], fabs(c));
+    }
+    double flag[2] = {isnan_[0] ? 1.0 : 0.0, isnan_[1] ? 1.0 : 0.0};
+    block_reduce<2, true>(mx, sh);
+    block_reduce<2, true>(flag, sh);
+    if (threadIdx.x == 0) {
+        status[b].umax = flag[0] > 0.0 ? nan("") : mx[0];
+        status[b].vmax = flag[1] > 0.0 ? nan("") : mx[1];
+    }
+}
+
+// ---- the K loop of one chunk -------------------------------------------------------------------------------------------
+// Contractions of the warp's field for `ksteps` k4-steps of one chunk slot (cf. st_chunk / eo_field_pass).
+//   ro = (8 tw + g) * 4 + t : the thread's A-fragment offset inside a 16 x 4 block;  co = g * 4 + t : B-fragment offset
+template <bool P_LEFT>
+__device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int ksteps, int ro, int co, int fld,
+                                         double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    constexpr int NT = 2;
+    const double* sOa = sl + S2_SL_OA + ro;
+    const double* sOb = sl + S2_SL_OB + co;
+    const double* sFa = sl + S2_SL_FA + fld * 256 + ro;
+    const double* sFb = sl + S2_SL_FB + fld * 256 + co;
+    const double* sPa = sl + S2_SL_PA + ro;
+    const double* sPb = sl + S2_SL_PB + co;
+#pragma unroll 1
+    for (int kk = 0; kk < ksteps; ++kk) {
+        double FA[4], FB[4][NT];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            FA[q] = sFa[(kk * 8 + q) * 64];
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) FB[q][nt] = sFb[(kk * 8 + q) * 64 + nt * 32];
+        }
+        {
+            double dA[2], ddA[2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                dA[a] = sOa[(kk * 6 + a) * 64];
+                ddA[a] = sOa[(kk * 6 + 2 + a) * 64];
+            }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
+                    }
+        }
+        {
+            double dB[2][NT], ddB[2][NT];
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    dB[b][nt] = sOb[(kk * 6 + b) * 64 + nt * 32];
+                    ddB[b][nt] = sOb[(kk * 6 + 2 + b) * 64 + nt * 32];
+                }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
+                    }
+        }
+        if (P_LEFT) {
+            double gA[2], PB[4][NT];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) gA[a] = sOa[(kk * 6 + 4 + a) * 64];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) PB[q][nt] = sPb[(kk * 4 + q) * 64 + nt * 32];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
+        } else {
+            double PA[4], gB[2][NT];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) PA[q] = sPa[(kk * 4 + q) * 64];
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) gB[b][nt] = sOb[(kk * 6 + 4 + b) * 64 + nt * 32];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], PA[2 * a + (1 - b)], gB[b][nt]);
+        }
+    }
+}
+
+// Boundary-line corrections + nonlinear assembly at the thread's two elements (columns j, j + 1) of every parity block
+// (cf. st_assemble).  On return bL = momentum residual blocks, b1 = d(field)/dx (IS_U) or d(field)/dy (!IS_U) blocks.
+template <bool IS_U>
+__device__ __forceinline__ void s2_assemble(const double* __restrict__ sVec, const double* __restrict__ sEdgeF, double nu,
+                                            bool bc_lines, int i, int j0, const double (&uo)[4][2], const double (&vo)[4][2],
+                                            double (&b1)[4][2], double (&b2)[4][2], double (&bL)[4][2]) {
+    constexpr int HP = S2_HP;
+    double d0i[2], dNi[2], dd0i[2], ddNi[2], Si[2], Ni[2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        d0i[a] = sVec[(0 + a) * HP + i];
+        dNi[a] = sVec[(2 + a) * HP + i];
+        dd0i[a] = sVec[(4 + a) * HP + i];
+        ddNi[a] = sVec[(6 + a) * HP + i];
+        Si[a] = sEdgeF[(4 + a) * HP + i];
+        Ni[a] = sEdgeF[(6 + a) * HP + i];
+    }
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+        const int j = j0 + hh;
+        double dx[4], dy[4];
+        if (bc_lines) {   // W = E = S = 0: only the lid line contributes, and only to the y-derivatives
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const double dNj = sVec[(2 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    const int q = 2 * a + b;
+                    dx[q] = b1[q][hh];
+                    dy[q] = fma(Ni[a], dNj, b2[q][hh]);
+                    bL[q][hh] = fma(nu * Ni[a], ddNj, bL[q][hh]);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
+                const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
+                const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    const int q = 2 * a + b;
+                    dx[q] = b1[q][hh] + d0i[a] * Wj + dNi[a] * Ej;
+                    dy[q] = b2[q][hh] + Si[a] * d0j + Ni[a] * dNj;
+                    bL[q][hh] += nu * (dd0i[a] * Wj + ddNi[a] * Ej + Si[a] * dd0j + Ni[a] * ddNj);
+                }
+            }
+        }
+        // convective term in parity form: Z2 x Z2 group convolution (see eo_assemble)
+        double cq[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            double c = uo[q][hh] * dx[0];
+#pragma unroll
+            for (int bb = 1; bb < 4; ++bb) c = fma(uo[q ^ bb][hh], dx[bb], c);
+#pragma unroll
+            for (int bb = 0; bb < 4; ++bb) c = fma(vo[q ^ bb][hh], dy[bb], c);
+            cq[q] = c;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            bL[q][hh] -= cq[q];
+            b1[q][hh] = IS_U ? dx[q] : dy[q];
+        }
+    }
+}
+
+// dt from the start-of-step maxima (spectral/sg.py:387-408).  Python's max(np.max(|u|), lid): a NaN first argument wins.
+__device__ __forceinline__ double s2_dt(double umax, double vmax, double lidv, double nu, double b2, double cfl, double dx_min,
+                                        double dy_min) {
+    const double ua = (lidv > umax) ? lidv : umax, va = (1e-10 > vmax) ? 1e-10 : vmax;
+    const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu / (dx_min * dx_min);
+    const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu / (dy_min * dy_min);
+    return cfl / (lam_x + lam_y);
+}
+
+// per-visit constants of a cavity, shared by the roles of a CTA
+struct S2Visit {
+    double nu, beta2, cfl, lidv, tol;
+    int first;   // the cavity has taken no step yet: its boundary lines are as stored, not yet the boundary conditions
+};
+
+// After the K loop: swap accumulator halves with the other k-group (X = this group: it keeps the 8-column half X of the
+// tile), then the epilogue of that half.  Returns nothing; writes the stage output, and at the last stage the tile partials.
+template <int X>
+__device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, double* __restrict__ exch_own,
+                                          const double* __restrict__ exch_other, unsigned long long* empty_other,
+                                          const double* __restrict__ sUV, const double* __restrict__ sVec,
+                                          double* __restrict__ sEdgeP, double* __restrict__ sX, double* __restrict__ sRed,
+                                          const double* __restrict__ recN, double* __restrict__ recO, int tile, int b,
+                                          int r0, int c0, int stage, bool bc_lines, double dt, int fld, int tw, int lane,
+                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    const int g = lane >> 2, t = lane & 3;
+    const int tid128 = threadIdx.x & 127;
+    const int m = P.m, h = eo_half(m), centre = (m & 1) ? h - 1 : -1;
+    const int i = r0 + 8 * tw + g, j0 = c0 + 8 * X + 2 * t;
+    const int rt = r0 >> 4, ct = c0 >> 4, ir = i & 15;
+    // phi^n of the warp's field (and p^n for the u warps) at the thread's elements: issued now, used after the swap
+    const size_t offR = s2_off(8, rt, j0 >> 2, 4 * fld, ir, j0 & 3);    // + q * 64
+    const size_t offPR = s2_off(4, rt, j0 >> 2, 0, ir, j0 & 3);
+    double2 f0[4], p0[4];
+    if (stage != 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) f0[q] = __ldcg(reinterpret_cast<const double2*>(recN + offR + q * 64));
+    }
+    if (fld == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) p0[q] = __ldcg(reinterpret_cast<const double2*>(recN + 2 * S2_UV + offPR + q * 64));
+    }
+    // ---- split-K hand-over: give away the other half, take the partner's contribution to this half ----
+    consumer_sync();   // both groups are done reading their last chunk slots
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int idx = q * 2 + hh;
+            exch_own[(0 + idx) * 128 + tid128] = a1[q][1 - X][hh];
+            exch_own[(8 + idx) * 128 + tid128] = a2[q][1 - X][hh];
+            exch_own[(16 + idx) * 128 + tid128] = aL[q][1 - X][hh];
+        }
+    fence_proxy_async();   // these generic writes land in a slot the TMA refills later
+    consumer_sync();
+    double b1[4][2], b2[4][2], bL[4][2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int idx = q * 2 + hh;
+            // group 0's sum first, whichever group does the addition (bitwise the same in both)
+            const double o1 = exch_other[(0 + idx) * 128 + tid128], o2 = exch_other[(8 + idx) * 128 + tid128],
+                         oL = exch_other[(16 + idx) * 128 + tid128];
+            b1[q][hh] = X == 0 ? a1[q][X][hh] + o1 : o1 + a1[q][X][hh];
+            b2[q][hh] = X == 0 ? a2[q][X][hh] + o2 : o2 + a2[q][X][hh];
+            bL[q][hh] = X == 0 ? aL[q][X][hh] + oL : oL + aL[q][X][hh];
+        }
+    // the partner's slot has been read: hand it back to the producer (generic reads/writes before the async refill)
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty_other);
+
+    // ---- stage input u, v at the thread's elements (picked out of the row panels during the K loop) ----
+    double uo[4][2], vo[4][2];
+    {
+        const int pos = (X * 2 + tw) * 32 + lane;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double2 a = *reinterpret_cast<const double2*>(sUV + ((0 + q) * 128 + pos) * 2);
+            const double2 c = *reinterpret_cast<const double2*>(sUV + ((4 + q) * 128 + pos) * 2);
+            uo[q][0] = a.x; uo[q][1] = a.y;
+            vo[q][0] = c.x; vo[q][1] = c.y;
+        }
+    }
+    if (fld == 0) s2_assemble<true>(sVec, sEdgeP, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
+    else s2_assemble<false>(sVec, sEdgeP + 8 * S2_HP, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
+
+    const double adt = rk_alpha(stage) * dt;
+    const bool last = (stage == 3);
+    double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
+    {
+        const double wi = (i == centre) ? 0.5 : 1.0;
+        const double w0 = 4.0 * wi * (j0 == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j0 + 1 == centre ? 0.5 : 1.0);
+        double fn[4][2];
+        double* outR = recO + offR;
+        double* outC = recO + S2_UV + s2_off(8, ct, i >> 2, 4 * fld, j0 & 15, i & 3);   // + q * 64; second column + 4
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double fx = stage == 0 ? (fld == 0 ? uo[q][0] : vo[q][0]) : f0[q].x;
+            const double fy = stage == 0 ? (fld == 0 ? uo[q][1] : vo[q][1]) : f0[q].y;
+            fn[q][0] = fx + adt * bL[q][0];
+            fn[q][1] = fy + adt * bL[q][1];
+            if (last) {
+                double d;
+                d = fn[q][0] - fx; s0 = fma(w0 * d, d, s0); s1 = fma(w0 * fx, fx, s1);
+                d = fn[q][1] - fy; s0 = fma(w1 * d, d, s0); s1 = fma(w1 * fy, fy, s1);
+            }
+            __stcg(reinterpret_cast<double2*>(outR + q * 64), make_double2(fn[q][0], fn[q][1]));
+            __stcg(outC + q * 64, fn[q][0]);
+            __stcg(outC + q * 64 + 4, fn[q][1]);
+            if (fld == 1) {
+                sX[((X * 2 + tw) * 8 + q * 2 + 0) * 32 + lane] = b1[q][0];
+                sX[((X * 2 + tw) * 8 + q * 2 + 1) * 32 + lane] = b1[q][1];
+            }
+        }
+        if (last) {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                double fr[4];
+                eo_to_points(fn[0][hh], fn[1][hh], fn[2][hh], fn[3][hh], fr);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) mx = nanmax(mx, fabs(fr[q]));
+            }
+        }
+    }
+    if (last) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            mx = nanmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        }
+        if (lane == 0) {
+            const int w = threadIdx.x >> 5;
+            sRed[w * 4 + 0] = s0;
+            sRed[w * 4 + 1] = s1;
+            sRed[w * 4 + 2] = mx;
+        }
+    }
+    consumer_sync();   // dv/dy of the v warps is in sX (and the warps' partial sums in sRed)
+    if (fld == 0) {
+        double* outR = recO + 2 * S2_UV + offPR;
+        double* outC = recO + 2 * S2_UV + S2_P + s2_off(4, ct, i >> 2, 0, j0 & 15, i & 3);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double dv0 = b1[q][0] + sX[((X * 2 + tw) * 8 + q * 2 + 0) * 32 + lane];
+            const double dv1 = b1[q][1] + sX[((X * 2 + tw) * 8 + q * 2 + 1) * 32 + lane];
+            const double pn0 = p0[q].x + adt * (-V.beta2 * dv0), pn1 = p0[q].y + adt * (-V.beta2 * dv1);
+            __stcg(reinterpret_cast<double2*>(outR + q * 64), make_double2(pn0, pn1));
+            __stcg(outC + q * 64, pn0);
+            __stcg(outC + q * 64 + 4, pn1);
+        }
+    }
+    if (!bc_lines) {
+        // first stage after a load done: from now on the boundary lines are the boundary conditions (walls zero, lid line)
+        for (int e = threadIdx.x; e < 8 * S2_HP; e += S2_CONSUMERS) {
+            const int line = e / S2_HP, k = e % S2_HP;
+            double x = 0.0, y = 0.0;
+            if (k < h && (line & 3) == 3) {
+                const double* lid = (line < 4 ? P.ulid : P.vlid) + (size_t)b * P.n1 + 1;
+                x = lid[k];
+                y = lid[m - 1 - k];
+            }
+            sEdgeP[2 * line * S2_HP + k] = 0.5 * (x + y);
+            sEdgeP[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
+        }
+    }
+    if (last && threadIdx.x == 0) {
+        // warps: w = 4 X + 2 fld + tw.  u: warps 0, 1, 4, 5; v: warps 2, 3, 6, 7 -- always in this order
+        double* out = P.partials + ((size_t)b * ST_TILES + tile) * 8;
+        __stcg(out + 0, ((sRed[0 * 4 + 0] + sRed[1 * 4 + 0]) + sRed[4 * 4 + 0]) + sRed[5 * 4 + 0]);
+        __stcg(out + 1, ((sRed[0 * 4 + 1] + sRed[1 * 4 + 1]) + sRed[4 * 4 + 1]) + sRed[5 * 4 + 1]);
+        __stcg(out + 2, ((sRed[2 * 4 + 0] + sRed[3 * 4 + 0]) + sRed[6 * 4 + 0]) + sRed[7 * 4 + 0]);
+        __stcg(out + 3, ((sRed[2 * 4 + 1] + sRed[3 * 4 + 1]) + sRed[6 * 4 + 1]) + sRed[7 * 4 + 1]);
+        __stcg(out + 4, nanmax(nanmax(sRed[0 * 4 + 2], sRed[1 * 4 + 2]), nanmax(sRed[4 * 4 + 2], sRed[5 * 4 + 2])));
+        __stcg(out + 5, nanmax(nanmax(sRed[2 * 4 + 2], sRed[3 * 4 + 2]), nanmax(sRed[6 * 4 + 2], sRed[7 * 4 + 2])));
+    }
+}
+
+// 4 sums + 2 NaN-propagating maxima across the eight consumer warps, fixed order, result in every consumer thread.
+__device__ __forceinline__ void s2_consumer_reduce(double (&s)[4], double (&mx)[2], double* sRed, int warp, int lane) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s[q] += __shfl_xor_sync(0xffffffffu, s[q], o);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) mx[q] = nanmax(mx[q], __shfl_xor_sync(0xffffffffu, mx[q], o));
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sRed[warp * 8 + q] = s[q];
+        sRed[warp * 8 + 4] = mx[0];
+        sRed[warp * 8 + 5] = mx[1];
+    }
+    consumer_sync();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) s[q] = sRed[q];
+    mx[0] = sRed[4];
+    mx[1] = sRed[5];
+    for (int w = 1; w < 8; ++w) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s[q] += sRed[w * 8 + q];
+        mx[0] = nanmax(mx[0], sRed[w * 8 + 4]);
+        mx[1] = nanmax(mx[1], sRed[w * 8 + 5]);
+    }
+    consumer_sync();
+}
+
+// shared-memory carve-up of k_stream_tma
+struct S2Smem {
+    double *slot, *uv, *vec, *edgep, *x, *part, *red, *step;
+    unsigned long long *full, *empty, *stepbar;
+    int* cavity;
+    __device__ explicit S2Smem(double* smem) {
+        slot = smem;
+        uv = slot + (size_t)S2_SLOTS * S2_SLOT;
+        vec = uv + 8 * 256;
+        edgep = vec + 8 * S2_HP;
+        x = edgep + 16 * S2_HP;
+        part = x + 4 * 8 * 32;             // [16 tiles][8]
+        red = part + 16 * 8;               // 80
+        step = red + 80;                   // dt, active | boundary-line sums: first step 4, max|lid| 2, later steps 4 | cavity
+        full = reinterpret_cast<unsigned long long*>(step + 16);
+        empty = full + S2_SLOTS;
+        stepbar = empty + S2_SLOTS;
+        cavity = reinterpret_cast<int*>(step + 15);
+    }
+};
+
+// CTA geometry inside its team
+struct S2Geo {
+    int ntile, team_size, team, tin, trow, tcol, tile, r0, c0, m, h, n1, nk4, nch;
+    __device__ explicit S2Geo(const S2Params& P) {
+        ntile = P.ntile; team_size = ntile * ntile;
+        team = blockIdx.x / team_size; tin = blockIdx.x % team_size;
+        trow = tin / ntile; tcol = tin % ntile; tile = trow * (S2_HP / 16) + tcol;
+        r0 = trow * 16; c0 = tcol * 16;
+        m = P.m; h = eo_half(m); n1 = P.n1;
+        nk4 = P.K4 / 4; nch = (nk4 + S2_KC4 - 1) / S2_KC4;
+    }
+};
+
+// named barriers: 1 = the eight consumer warps (consumer_sync); 2 = consumers + producer warp, start of a visit;
+// 3 = consumers arrive / producer waits: the visit's boundary-line sums are in shared memory
+__device__ __forceinline__ void visit_sync() { asm volatile("bar.sync 2, 288;" ::: "memory"); }
+__device__ __forceinline__ void sums_arrive() { asm volatile("bar.arrive 3, 288;" ::: "memory"); }
+__device__ __forceinline__ void sums_wait() { asm volatile("bar.sync 3, 288;" ::: "memory"); }
+
+// ================================================ consumer warps ================================================
+__device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem& S, const S2Geo& G) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int X = warp >> 2, fld = (warp >> 1) & 1, tw = warp & 1, g = lane >> 2, t = lane & 3;
+    const int ro = (8 * tw + g) * 4 + t, co = g * 4 + t;
+    const int m = G.m, h = G.h, n1 = G.n1, nch = G.nch;
+    const int cgrab = (G.c0 >> 3) + X;                       // the chunk holding this group's 8 columns of the tile
+    const int clast_own = ((nch - 1 - X) & ~1) + X;          // the group's last chunk
+    const int clast_other = ((nch - 1 - (1 - X)) & ~1) + (1 - X);
+    unsigned gcb = 0;        // chunks consumed before the current stage (ring position)
+    unsigned nstepinfo = 0;  // step-info hand-overs consumed so far
+
+    for (;;) {
+        visit_sync();   // the producer warp has the team's next cavity
+        const int b = *S.cavity;
+        if (b < 0) return;
+        const CavityStatus st = load_status(P.status + b);
+        int cur = __ldcg(&P.status[b].pad);
+        S2Visit V;
+        V.nu = 1.0 / P.Re[b]; V.beta2 = P.beta2[b]; V.cfl = P.CFL[b]; V.lidv = P.lidvel[b];
+        V.tol = 0.0;
+        V.first = st.iters == 0 ? 1 : 0;
+        long long nsteps = P.launch_end - st.iters;
+        if (nsteps > P.chunk) nsteps = P.chunk;
+        const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
+        double* rec0 = P.rec + (size_t)b * S2_STRIDE;
+
+        // ---- boundary lines in parity form for the first stage; boundary-line parts of the convergence sums ----
+        {
+            const double* ed = rec0 + (size_t)cur * P.buf_stride + S2_EDGE_OFF;
+            for (int e = tid; e < 8 * S2_HP; e += S2_CONSUMERS) {
+                const int line = e / S2_HP, k = e % S2_HP;
+                double x = 0.0, y = 0.0;
+                if (k < h) {
+                    if (V.first) {
+                        x = __ldcg(ed + line * S2_ME + k);
+                        y = __ldcg(ed + line * S2_ME + m - 1 - k);
+                    } else if ((line & 3) == 3) {
+                        const double* lid = (line < 4 ? ul : vl) + 1;
+                        x = lid[k];
+                        y = lid[m - 1 - k];
+                    }
+                }
+                S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
+                S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
+            }
+            // sums over the boundary lines of ||phi^{n+1} - phi^n||^2, ||phi^n||^2 and max |lid|: with the lines as stored
+            // (first step after a load) and with the boundary-condition lines (every later step)
+            double sf[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, bm[2] = {0, 0}, dummy[2] = {0, 0};
+            for (int e = tid; e < m; e += S2_CONSUMERS) {
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    const double lid = (f ? vl : ul)[e + 1];
+                    const double* L = ed + f * 4 * S2_ME;
+                    const double w = __ldcg(L + e), ea = __ldcg(L + S2_ME + e), so = __ldcg(L + 2 * S2_ME + e),
+                                 no = __ldcg(L + 3 * S2_ME + e);
+                    const double dn = lid - no;
+                    sf[2 * f] += w * w + ea * ea + so * so + dn * dn;
+                    sf[2 * f + 1] += w * w + ea * ea + so * so + no * no;
+                    sb[2 * f + 1] += lid * lid;
+                    bm[f] = nanmax(bm[f], fabs(lid));
+                }
+            }
+            if (tid == 0) {
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    const double* c = ed + 8 * S2_ME + 4 * f;   // c00 c0N cN0 cNN
+                    const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
+                    const double q0 = __ldcg(c), q1 = __ldcg(c + 1), q2 = __ldcg(c + 2), q3 = __ldcg(c + 3);
+                    const double d1 = l0 - q1, d3 = lN - q3;
+                    sf[2 * f] += q0 * q0 + d1 * d1 + q2 * q2 + d3 * d3;
+                    sf[2 * f + 1] += q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3;
+                    sb[2 * f + 1] += l0 * l0 + lN * lN;
+                    bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
+                }
+            }
+            s2_consumer_reduce(sf, bm, S.red, warp, lane);
+            s2_consumer_reduce(sb, dummy, S.red, warp, lane);
+            if (tid == 0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    S.step[2 + q] = sf[q];
+                    S.step[8 + q] = sb[q];
+                }
+                S.step[6] = bm[0];
+                S.step[7] = bm[1];
+            }
+            __threadfence_block();
+            sums_arrive();     // the producer warp reads them at its first reduction of the visit
+            consumer_sync();   // S.edgep complete
+        }
+        // dt of the first step of the visit from the status (spectral/sg.py:387-408)
+        double dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+        bool bc_lines = !V.first;
+        bool aborted = false;
+        for (long long step = 0; step < nsteps && !aborted; ++step) {
+            for (int stage = 0; stage < 4; ++stage) {
+                const double* recN = rec0 + (size_t)cur * P.buf_stride;
+                double* recO = rec0 + (size_t)st_out(cur, stage) * P.buf_stride;
+                double a1[4][2][2], a2[4][2][2], aL[4][2][2];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                        for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+                if (cgrab >= nch) {   // the group's columns lie in the zero padding
+                    const int pos = (X * 2 + tw) * 32 + lane;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        *reinterpret_cast<double2*>(S.uv + ((4 * fld + q) * 128 + pos) * 2) = make_double2(0.0, 0.0);
+                }
+                for (int c = X; c < nch; c += 2) {
+                    const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
+                    mbar_wait(S.full + slot, (gc / S2_SLOTS) & 1);
+                    const double* sl = S.slot + (size_t)slot * S2_SLOT;
+                    if (c == cgrab) {
+                        // the thread's own elements of its field's stage input: columns 8 X + 2 t, + 1 of the tile
+                        const int pos = (X * 2 + tw) * 32 + lane;
+                        const double* src = sl + S2_SL_FA + ((t >> 1) * 8 + 4 * fld) * 64 + (8 * tw + g) * 4 + 2 * (t & 1);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            *reinterpret_cast<double2*>(S.uv + ((4 * fld + q) * 128 + pos) * 2) =
+                                *reinterpret_cast<const double2*>(src + q * 64);
+                    }
+                    const int ksteps = min(S2_KC4, G.nk4 - c * S2_KC4);
+                    if (fld == 0) s2_chunk<true>(sl, ksteps, ro, co, fld, a1, a2, aL);
+                    else s2_chunk<false>(sl, ksteps, ro, co, fld, a1, a2, aL);
+                    if (c != clast_own) {
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(S.empty + slot);
+                    }
+                }
+                const unsigned slot_own = (gcb + clast_own) % S2_SLOTS, slot_other = (gcb + clast_other) % S2_SLOTS;
+                gcb += nch;
+                if (stage == 0 && step > 0) {
+                    // the reduction of the previous step (producer warp): dt of this step, and whether there is one
+                    mbar_wait(S.stepbar, nstepinfo & 1);
+                    ++nstepinfo;
+                    dt = S.step[0];
+                    if (S.step[1] == 0.0) {
+                        // the cavity went inactive with the previous step: this stage was speculative
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(S.empty + slot_own);
+                        aborted = true;
+                        break;
+                    }
+                }
+                double* exch_own = S.slot + (size_t)slot_own * S2_SLOT;
+                const double* exch_other = S.slot + (size_t)slot_other * S2_SLOT;
+                if (X == 0)
+                    s2_finish<0>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.vec, S.edgep, S.x, S.red, recN, recO,
+                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL);
+                else
+                    s2_finish<1>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.vec, S.edgep, S.x, S.red, recN, recO,
+                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL);
+                bc_lines = true;
+                // ---- arrive at the team's stage barrier: this CTA's stage output is complete ----
+                fence_proxy_async();   // the stage output is read by the team's TMA copies (async proxy)
+                consumer_sync();
+                if (tid == 0) {
+                    __threadfence();
+                    red_release_add(P.team_bar + G.team, 1u);
+                }
+                if (stage == 3) cur = (cur + 2) % 3;
+            }
+        }
+    }
+}
+
+// ============================================ producer / reducer warp ============================================
+__device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem& S, const S2Geo& G) {
+    const int lane = threadIdx.x & 31;
+    const int m = G.m, n1 = G.n1, nch = G.nch, team_size = G.team_size;
+    const int npre = nch < S2_SLOTS ? nch : S2_SLOTS;
+    unsigned gcb = 0;        // chunks issued before the current stage (ring position)
+    unsigned nbar = 0;       // team barriers completed before the current stage
+    unsigned visit = 0;
+
+    for (;;) {
+        // ---- the team's next cavity ----
+        int b = 0;
+        if (lane == 0) {
+            if (G.tin == 0) {
+                b = CavityQueue::pop(P);
+                st_release_u64(P.team_mail + G.team, ((unsigned long long)(visit + 1) << 32) | (unsigned)(b + 1));
+            } else {
+                unsigned long long mail;
+                while (((mail = ld_acquire_u64(P.team_mail + G.team)) >> 32) != visit + 1) __nanosleep(100);
+                b = (int)(unsigned)(mail & 0xffffffffu) - 1;
+            }
+            *S.cavity = b;
+        }
+        b = __shfl_sync(0xffffffffu, b, 0);
+        __threadfence_block();
+        visit_sync();
+        if (b < 0) return;
+        ++visit;
+        fence_proxy_async();   // the record was written through the generic proxy (another team, or the pack kernel)
+
+        CavityStatus st = load_status(P.status + b);
+        int cur = __ldcg(&P.status[b].pad);
+        const double nu = 1.0 / P.Re[b], beta2 = P.beta2[b], cfl = P.CFL[b], lidv = P.lidvel[b];
+        const double tol = P.tol ? P.tol[b] : -1.0;
+        const bool first = st.iters == 0;
+        long long nsteps = P.launch_end - st.iters;
+        if (nsteps > P.chunk) nsteps = P.chunk;
+        const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
+        double* rec0 = P.rec + (size_t)b * S2_STRIDE;
+        const double* opsc = P.opsc + (size_t)b * S2_OPS;
+        bool active = true, sums_ready = false;
+
+        auto issue_ops = [&](int c, unsigned slot) {
+            double* sl = S.slot + (size_t)slot * S2_SLOT;
+            mbar_expect_tx(S.full + slot, S2_SLOT_BYTES);
+            bulk_g2s(sl + S2_SL_OA, opsc + s2_off(6, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 6 * 64 * 8, S.full + slot);
+            bulk_g2s(sl + S2_SL_OB, opsc + s2_off(6, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 6 * 64 * 8, S.full + slot);
+        };
+        auto issue_state = [&](int c, unsigned slot, const double* recI, const double* recP) {
+            double* sl = S.slot + (size_t)slot * S2_SLOT;
+            bulk_g2s(sl + S2_SL_FA, recI + s2_off(8, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 8 * 64 * 8, S.full + slot);
+            bulk_g2s(sl + S2_SL_FB, recI + S2_UV + s2_off(8, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 8 * 64 * 8, S.full + slot);
+            bulk_g2s(sl + S2_SL_PA, recP + 2 * S2_UV + s2_off(4, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 4 * 64 * 8, S.full + slot);
+            bulk_g2s(sl + S2_SL_PB, recP + 2 * S2_UV + S2_P + s2_off(4, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 4 * 64 * 8,
+                     S.full + slot);
+        };
+        // end-of-step reduction: tile partials in fixed order + boundary lines, convergence bookkeeping
+        auto reduce_step = [&](bool first_step) {
+            if (!sums_ready) {
+                sums_wait();   // the consumers' boundary-line sums of this visit
+                sums_ready = true;
+            }
+            if (lane < team_size) {
+                const int tl = (lane / G.ntile) * (S2_HP / 16) + lane % G.ntile;
+                const double* part = P.partials + ((size_t)b * ST_TILES + tl) * 8;
+#pragma unroll
+                for (int q = 0; q < 6; ++q) S.part[lane * 8 + q] = __ldcg(part + q);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                const double* es = S.step + (first_step ? 2 : 8);
+                double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0, 0};
+                for (int tl = 0; tl < team_size; ++tl) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
+                    mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
+                    mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
+                }
+                const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+                update_status(st, ures, vres, tol, P.warmup, P.max_iter, P.nan_exit);
+                st.umax = nanmax(mx[0], S.step[6]);
+                st.vmax = nanmax(mx[1], S.step[7]);
+            }
+            __syncwarp();
+        };
+        auto wait_team = [&]() {
+            const unsigned target = nbar * (unsigned)team_size;
+            while ((int)(ld_acquire_u32(P.team_bar + G.team) - target) < 0) {}
+        };
+
+        for (long long step = 0; step < nsteps && active; ++step) {
+            for (int stage = 0; stage < 4; ++stage) {
+                const double* recN = rec0 + (size_t)cur * P.buf_stride;
+                const double* recI = rec0 + (size_t)st_in(cur, stage) * P.buf_stride;
+                const double* recP = P.freeze ? recN : recI;   // pressure operand
+                const bool need_bar = !(step == 0 && stage == 0);
+                if (lane == 0) {
+                    for (int c = 0; c < npre; ++c) {
+                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
+                        mbar_wait(S.empty + slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                        issue_ops(c, slot);
+                    }
+                    if (need_bar) {
+                        wait_team();
+                        fence_proxy_async();
+                    }
+                    for (int c = 0; c < npre; ++c) issue_state(c, (gcb + c) % S2_SLOTS, recI, recP);
+                }
+                __syncwarp();
+                if (stage == 0 && step > 0) {
+                    reduce_step(first && step == 1);
+                    if (lane == 0) {
+                        active = st.active != 0;
+                        S.step[0] = s2_dt(st.umax, st.vmax, lidv, nu, beta2, cfl, P.dx_min, P.dy_min);
+                        S.step[1] = active ? 1.0 : 0.0;
+                        __threadfence_block();
+                        mbar_arrive(S.stepbar);
+                    }
+                    active = __shfl_sync(0xffffffffu, (int)active, 0) != 0;
+                }
+                if (lane == 0) {
+                    for (int c = npre; c < nch; ++c) {
+                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
+                        mbar_wait(S.empty + slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                        issue_ops(c, slot);
+                        issue_state(c, slot, recI, recP);
+                    }
+                }
+                __syncwarp();
+                gcb += nch;
+                if (!active) break;   // the consumers drop this (speculative) stage as well: no barrier follows it
+                ++nbar;
+                if (stage == 3) cur = (cur + 2) % 3;
+            }
+        }
+        if (active) {
+            // the last step of the visit: wait for the team, then its reduction
+            if (lane == 0) wait_team();
+            __syncwarp();
+            reduce_step(first && nsteps == 1);
+        }
+        if (!sums_ready) sums_wait();   // (keeps the arrive / wait pairs of barrier 3 matched)
+        // ---- visit end (leader CTA): boundary-condition lines with the new record, status, hand the cavity back ----
+        if (G.tin == 0) {
+            double* edn = rec0 + (size_t)cur * P.buf_stride + S2_EDGE_OFF;
+            for (int e = lane; e < S2_ME; e += 32) {
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    double* Ln = edn + f * 4 * S2_ME;
+                    __stcg(Ln + e, 0.0);
+                    __stcg(Ln + S2_ME + e, 0.0);
+                    __stcg(Ln + 2 * S2_ME + e, 0.0);
+                    __stcg(Ln + 3 * S2_ME + e, e < m ? (f ? vl : ul)[e + 1] : 0.0);
+                }
+            }
+            if (lane < 2) {
+                double* cn = edn + 8 * S2_ME + 4 * lane;
+                __stcg(cn + 0, 0.0);
+                __stcg(cn + 1, (lane ? vl : ul)[0]);
+                __stcg(cn + 2, 0.0);
+                __stcg(cn + 3, (lane ? vl : ul)[n1 - 1]);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                store_status(P.status + b, st);
+                __stcg(&P.status[b].pad, cur);
+                __threadfence();
+                if (st.active && st.iters < P.launch_end) CavityQueue::push(P, b);
+                else CavityQueue::retire(P);
+            }
+        }
+    }
+}
+
+// The persistent kernel.  grid = teams x (tiles per cavity), cooperative launch (every CTA co-resident: the team barriers
+// and the queue spin).  384 threads: warps 0..7 consume (232 registers each after setmaxnreg), warp 8 produces and
+// reduces (40 registers), warps 9..11 exist only because setmaxnreg works on whole warpgroups and leave at once.
+__global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) {
+    extern __shared__ __align__(16) double smem[];
+    const S2Smem S(smem);
+    const S2Geo G(P);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) {
+        for (int s = 0; s < S2_SLOTS; ++s) {
+            mbar_init(S.full + s, 1);
+            mbar_init(S.empty + s, 4);
+        }
+        mbar_init(S.stepbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int e = tid; e < 8 * S2_HP; e += S2_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    __syncthreads();
+    if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8) s2_producer_main(P, S, G);
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        s2_consumer_main(P, S, G);
+    }
+}
+
+// After a run: move every cavity's record into buffer 0 so that the next run (or a continued solve) finds it there.
+__global__ void k_s2_normalise(double* __restrict__ bufs, size_t buf_stride, CavityStatus* __restrict__ status) {
+    const int b = blockIdx.y, cur = status[b].pad;
+    if (cur == 0) return;
+    const double2* src = reinterpret_cast<const double2*>(bufs + cur * buf_stride + (size_t)b * S2_STRIDE);
+    double2* dst = reinterpret_cast<double2*>(bufs + (size_t)b * S2_STRIDE);
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < S2_STRIDE / 2; e += (size_t)gridDim.x * blockDim.x)
+        dst[e] = src[e];
+}
+
+}  // namespace ldc

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libldc_b200.so")
 
 LDC_PATH_AUTO, LDC_PATH_TILED, LDC_PATH_RESIDENT, LDC_PATH_RESIDENT_EO, LDC_PATH_STREAM_EO = 0, 1, 2, 3, 4
 LDC_PATH_RESIDENT_EO_SPLIT = 5
+LDC_PATH_STREAM_TMA = 6
 
 _dp = C.POINTER(C.c_double)
 _vp = C.c_void_p

@@ -15,7 +15,7 @@ from . import operators as ops
 
 _PATHS = {"auto": _lib.LDC_PATH_AUTO, "tiled": _lib.LDC_PATH_TILED, "resident": _lib.LDC_PATH_RESIDENT,
           "resident_eo": _lib.LDC_PATH_RESIDENT_EO, "stream_eo": _lib.LDC_PATH_STREAM_EO,
-          "resident_eo_split": _lib.LDC_PATH_RESIDENT_EO_SPLIT}
+          "resident_eo_split": _lib.LDC_PATH_RESIDENT_EO_SPLIT, "stream_tma": _lib.LDC_PATH_STREAM_TMA}
 
 
 @dataclass

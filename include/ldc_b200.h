@@ -47,9 +47,15 @@ enum {
                                  RK stage (a programmatic-dependent-launch chain): 34 <= nx <= 129, nx == ny, identical
                                  x / y operators; AUTO picks it for nx >= 66 (e.g. N = 128) and, when 4 x batch <= #SM,
                                  for 50 <= nx <= 65 (four SMs per cavity instead of one) */
-    LDC_PATH_RESIDENT_EO_SPLIT = 5 /* resident even-odd with the u and v equations of a tile on different warps and the
+    LDC_PATH_RESIDENT_EO_SPLIT = 5, /* resident even-odd with the u and v equations of a tile on different warps and the
                                  base state in shared memory: lower latency per step for few cavities on small grids
                                  (nx - 1 <= 48); AUTO picks it when nx - 1 <= 32 and batch <= #SM */
+    LDC_PATH_STREAM_TMA = 6   /* the streamed even-odd algebra as ONE persistent cooperative launch per batch of steps:
+                                 teams of up to 16 co-resident CTAs per cavity fed from a cavity queue, operand panels by TMA
+                                 bulk copies (cp.async.bulk + mbarrier) from a k4-interleaved tile layout, the RK stages
+                                 separated by a team barrier in global memory instead of a kernel boundary.  Same shapes as
+                                 LDC_PATH_STREAM_EO; AUTO picks it wherever it picked that path (LDC_STREAM_TMA=0 in the
+                                 environment keeps the launch-per-stage kernels for A / B runs) */
 };
 
 /* Library / build information: "ldc_b200 <version> sm_100a". */
