@@ -24,11 +24,12 @@ class FSGResult:
     kernel_ms: float = 0.0
     launches: int = 0
     finest: BatchedSpectralLDC | None = None
+    zero_mask: np.ndarray | None = None   # FSG: cavities whose finest level was never reached (fields reported as zeros)
 
 
 def solve_sg_batched(N, Re, tolerance, max_iter, *, beta_squared=5.0, CFL=1.5, lid_velocity=1.0,
                      corner_treatment="smoothing", corner_smoothing=0.15, Lx=1.0, Ly=1.0, basis="chebyshev",
-                     device=0, path="auto", keep_handle=False) -> FSGResult:
+                     device=0, path="auto", keep_handle=False, host_fields=True) -> FSGResult:
     """`LidDrivenCavitySolver.solve` + `SGSolver.step` for a batch: zero start + lid, frozen-pressure RK4
     (SURVEY Q1), converged iff i >= 10 and rel < tol (base.py:243-313).  The reference has no NaN exit on this
     path (it would spin to max_iterations on NaNs); a non-finite residual here stops the cavity and reports
@@ -39,7 +40,7 @@ def solve_sg_batched(N, Re, tolerance, max_iter, *, beta_squared=5.0, CFL=1.5, l
     s.init_state()
     r = s.solve(tolerance, max_iter, warmup=10, freeze_pressure=True, nan_exit=True)
     iters = np.where(r.diverged, max_iter, r.iterations)
-    u, v, p = s.get_state()
+    u, v, p = s.get_state() if host_fields else (None, None, None)
     out = FSGResult(u, v, p, iters, r.converged, r.diverged, r.rel_residual, [r.iterations.copy()], [N], r.kernel_ms,
                     s.launches, s if keep_handle else None)
     if not keep_handle:
@@ -50,10 +51,13 @@ def solve_sg_batched(N, Re, tolerance, max_iter, *, beta_squared=5.0, CFL=1.5, l
 def solve_fsg_batched(N, Re, tolerance, max_iter, *, n_levels=2, coarse_tolerance_factor=1.0, prolongation="fft",
                       beta_squared=5.0, CFL=1.5, lid_velocity=1.0, corner_treatment="smoothing",
                       corner_smoothing=0.15, Lx=1.0, Ly=1.0, basis="chebyshev", device=0, path="auto",
-                      keep_handle=False) -> FSGResult:
+                      keep_handle=False, host_fields=True) -> FSGResult:
     """Coarse-to-fine sequence for a batch.  Per level: tol * ctf**levels_from_finest, no warm-up, staged
     pressure, NaN/Inf exit; max_iter applies per level; iterations are summed over levels.  A cavity that
-    diverges on a level leaves every finer level untouched: zero fields, converged=False."""
+    diverges on a COARSER level leaves every finer level untouched: zero fields, converged=False (SURVEY Q8,
+    multigrid/fsg.py:1200-1202); one that diverges on the finest level keeps that level's non-finite fields, as
+    `solve_fsg` returns them.  host_fields=False leaves the fields on the device (keep_handle=True: `finest`;
+    `zero_mask` marks the cavities to report as zeros)."""
     if prolongation not in ("fft", "polynomial"):
         raise ValueError(f"Unknown prolongation method: {prolongation}. Use 'fft' or 'polynomial'.")
     B = int(np.broadcast(np.asarray(Re), np.asarray(corner_smoothing), np.asarray(tolerance)).size)
@@ -82,15 +86,18 @@ def solve_fsg_batched(N, Re, tolerance, max_iter, *, n_levels=2, coarse_toleranc
         per_level.append(it)
         conv = np.where(dead, False, r.converged)
         rel = np.where(dead, rel, r.rel_residual)
+        dead_before = dead.copy()   # dead before THIS level: its fields were never legitimately stepped
         dead = dead | r.diverged
         prev = lvl
-    u, v, p = prev.get_state()
     launches += prev.launches
-    u[dead] = 0.0
-    v[dead] = 0.0
-    p[dead] = 0.0
+    u = v = p = None
+    if host_fields:
+        u, v, p = prev.get_state()
+        u[dead_before] = 0.0
+        v[dead_before] = 0.0
+        p[dead_before] = 0.0
     out = FSGResult(u, v, p, total, conv & ~dead, dead, rel, per_level, orders, kernel_ms, launches,
-                    prev if keep_handle else None)
+                    prev if keep_handle else None, dead_before)
     if not keep_handle:
         prev.close()
     return out

@@ -36,6 +36,7 @@ class SweepResult:
     p: np.ndarray | None
     kernel_ms: float         # max over ranks
     bounds: list
+    per_rank_kernel_ms: np.ndarray | None = None   # [world], when asked for
 
 
 def _dist():
@@ -74,6 +75,28 @@ def _allgather_blocks(local: np.ndarray, counts, dtype):
     return np.concatenate([out[r, :counts[r]] for r in range(world)], axis=0)
 
 
+def _gather_fields(tensors, counts, dst_all: bool):
+    """Gather of the per-rank field blocks (torch tensors on the communication device, padded to the largest block) to
+    rank 0 -- `dist.gather`, SURVEY 8(e) -- or to every rank (`all_gather_into_tensor`).  Returns NumPy arrays where the
+    fields are wanted, else None; one device -> host copy per field on the receiving ranks only."""
+    import torch
+
+    dist = _dist()
+    world, rank, pad = dist.get_world_size(), dist.get_rank(), max(counts)
+    out = []
+    for t in tensors:
+        if dst_all:
+            full = torch.empty((world * pad,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            dist.all_gather_into_tensor(full, t)
+            parts = full.reshape((world, pad) + tuple(t.shape[1:]))
+            out.append(np.concatenate([parts[r, :counts[r]].cpu().numpy() for r in range(world)], axis=0))
+        else:
+            recv = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+            dist.gather(t, recv, dst=0)
+            out.append(np.concatenate([recv[r][:counts[r]].cpu().numpy() for r in range(world)], axis=0) if rank == 0 else None)
+    return out
+
+
 def interleave_permutation(n_cases: int, world: int) -> np.ndarray:
     """Order in which the cavities are laid out before the contiguous split so that rank r gets cavities r, r + world,
     r + 2 world, ...: a sweep ordered by Re or corner_smoothing then hands every rank the same mix of short and long solves
@@ -82,7 +105,8 @@ def interleave_permutation(n_cases: int, world: int) -> np.ndarray:
 
 
 def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fsg", fields: str = "rank0",
-                local_solver=None, device=None, balance: str = "block", **solver_kw) -> SweepResult:
+                local_solver=None, device=None, balance: str = "block", per_rank_kernel_ms: bool = False,
+                **solver_kw) -> SweepResult:
     """Solve B = len(Re) cavities (per-cavity Re and corner_smoothing; everything in solver_kw is shared),
     sharded over the ranks of the initialised process group (or on this process alone if there is none).
 
@@ -121,6 +145,11 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
         per_case = not isinstance(val, str) and np.ndim(val) == 1 and len(val) == Re.size
         local_kw[k] = (list(val[lo:hi]) if isinstance(val, (list, tuple)) else np.asarray(val)[lo:hi]) if per_case else val
     n1 = N + 1
+    # with NCCL the fields stay on the device from the solver's state to the gather (no host round trip on the senders)
+    dev_route = (dist is not None and world > 1 and dist.get_backend() == "nccl" and fields != "none"
+                 and local_solver is None)
+    if dev_route:
+        local_kw.update(keep_handle=True, host_fields=False)
     if hi > lo:
         r: FSGResult = fn(N, Re[lo:hi], tol[lo:hi], max_iter, corner_smoothing=cs[lo:hi], device=device, **local_kw)
     else:  # more ranks than cavities
@@ -131,9 +160,23 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
                      r.rel_residual], axis=1) if hi > lo else np.zeros((0, 4))
     scal = _allgather_blocks(scal, counts, torch.float64)
     kms = np.array([[r.kernel_ms]])
-    kms = _allgather_blocks(kms, [1] * world, torch.float64).max()
+    kms_all = _allgather_blocks(kms, [1] * world, torch.float64).ravel()
+    kms = kms_all.max()
     u = v = p = None
-    if fields != "none":
+    if dev_route:
+        dev = _comm_device()
+        pad, cnt = max(counts), hi - lo
+        bufs = [torch.zeros((pad, n1, n1), dtype=torch.float64, device=dev), torch.zeros((pad, n1, n1), dtype=torch.float64, device=dev),
+                torch.zeros((pad, N - 1, N - 1), dtype=torch.float64, device=dev)]
+        if cnt:
+            r.finest.get_state(tuple(b[:cnt] for b in bufs))
+            if r.zero_mask is not None and r.zero_mask.any():
+                zm = torch.from_numpy(np.ascontiguousarray(r.zero_mask)).to(dev)
+                for b in bufs:
+                    b[:cnt][zm] = 0.0
+            r.finest.close()
+        u, v, p = _gather_fields(bufs, counts, dst_all=(fields == "all"))
+    elif fields != "none":
         # NCCL has no variable-size gather: all-gather the padded blocks, keep them where asked
         gu = _allgather_blocks(r.u, counts, torch.float64)
         gv = _allgather_blocks(r.v, counts, torch.float64)
@@ -145,4 +188,4 @@ def solve_sweep(N, Re, corner_smoothing, tolerance, max_iter, *, kind: str = "fs
         scal = scal[inv]
         u, v, p = (None if a is None else a[inv] for a in (u, v, p))
     return SweepResult(np.rint(scal[:, 0]).astype(np.int64), scal[:, 1] > 0.5, scal[:, 2] > 0.5, scal[:, 3], u, v, p,
-                       float(kms), bounds)
+                       float(kms), bounds, kms_all if per_rank_kernel_ms else None)

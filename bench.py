@@ -67,79 +67,123 @@ def reynolds(args, world):
 # CPU arm: the oracle port, one single-threaded process per host core, each stepping its own cavity
 # ----------------------------------------------------------------------------------------------------------
 def cpu_worker(args):
-    """Child process: `windows` fixed-duration windows of oracle rk4_step calls; prints one JSON line."""
+    """Child process: `windows` fixed-duration windows of pseudo-steps of one cavity; prints one JSON line
+    {"kind": "reference" | "port", "why": ..., "windows": [[steps, seconds], ...]}.
+
+    kind "reference": the reference's own `MultigridSmoother.step` (spectral/multigrid/fsg.py:956-995, Numba kernels
+    81-216) imported from the staged copy oracle/_ref (oracle/build_ref.sh); "port": the NumPy oracle, with the reason."""
     import numpy as np
 
-    from oracle import ldc_oracle as orc
-
-    lv = orc.build_level(args.N)
     Re = float(reynolds(args, 1)[args.worker_index % args.batch])
-    case = orc.Case(Re=Re)
-    ul, vl = orc.lid_profile(lv.x, "smoothing", 0.15, 1.0, 1.0)
-    u, v, p = orc.initial_state(lv, ul, vl)
+    kind, why, step = "port", None, None
+    if not args.cpu_port:
+        try:
+            from oracle import ref_loader
+
+            ref = ref_loader.load_reference()
+            sm = ref_loader.make_smoother(ref, args.N, Re, corner_smoothing=0.15)
+            step, kind = sm.step, "reference"
+            state = lambda: sm.level.u
+        except Exception as e:   # no oracle/_ref, or numba missing on this box
+            why = f"{type(e).__name__}: {e}"
+    else:
+        why = "--cpu-port"
+    if step is None:
+        from oracle import ldc_oracle as orc
+
+        lv = orc.build_level(args.N)
+        case = orc.Case(Re=Re)
+        ul, vl = orc.lid_profile(lv.x, "smoothing", 0.15, 1.0, 1.0)
+        u, v, p = orc.initial_state(lv, ul, vl)
+        step = lambda: orc.rk4_step(lv, u, v, p, case, ul, vl, False)
+        state = lambda: u
     for _ in range(5):
-        orc.rk4_step(lv, u, v, p, case, ul, vl, False)
+        step()
     out = []
     for _ in range(args.windows):
         n, t0 = 0, time.perf_counter()
         while True:
-            orc.rk4_step(lv, u, v, p, case, ul, vl, False)
+            step()
             n += 1
             el = time.perf_counter() - t0
             if el >= args.seconds:
                 break
         out.append((n, el))
-    assert np.isfinite(u).all()
-    print(json.dumps(out), flush=True)
+    assert np.isfinite(state()).all()
+    print(json.dumps({"kind": kind, "why": why, "windows": out}), flush=True)
+
+
+def _cpu_env():
+    return dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", NUMBA_NUM_THREADS="1",
+                NUMBA_CACHE_DIR=os.environ.get("NUMBA_CACHE_DIR", "/tmp/numba_cache_ldc"), CUDA_VISIBLE_DEVICES="")
 
 
 def run_cpu_windows(args, windows: int, seconds: float):
-    """Spawn one worker per usable core; returns (cores, [aggregate cavity-steps/s per window])."""
+    """Spawn one worker per usable core; returns (cores, [aggregate cavity-steps/s per window], kind, why)."""
     try:
         cores = len(os.sched_getaffinity(0))
     except AttributeError:
         cores = os.cpu_count() or 1
     if args.cpu_cores:
         cores = min(cores, args.cpu_cores)
-    env = dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
-    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", "--worker-index", str(i),
-                               "--windows", str(windows), "--seconds", str(seconds), "--N", str(args.N),
-                               "--batch", str(args.batch)], stdout=subprocess.PIPE, env=env, text=True)
+    cmd = [sys.executable, os.path.abspath(__file__), "--cpu-worker", "--windows", str(windows), "--seconds", str(seconds),
+           "--N", str(args.N), "--batch", str(args.batch)] + (["--cpu-port"] if args.cpu_port else [])
+    # one warm worker first: it compiles the reference's Numba kernels into the shared cache, so that the timed
+    # workers load them instead of compiling 16 times side by side
+    subprocess.run(cmd + ["--worker-index", "0", "--windows", "1", "--seconds", "0.05"], stdout=subprocess.PIPE, env=_cpu_env(),
+                   text=True)
+    procs = [subprocess.Popen(cmd + ["--worker-index", str(i)], stdout=subprocess.PIPE, env=_cpu_env(), text=True)
              for i in range(cores)]
-    per = []
+    per, kinds, whys = [], set(), set()
     for pr in procs:
         so, _ = pr.communicate()
         if pr.returncode != 0:
             raise RuntimeError("cpu worker failed")
-        per.append(json.loads(so.strip().splitlines()[-1]))
+        d = json.loads(so.strip().splitlines()[-1])
+        per.append(d["windows"])
+        kinds.add(d["kind"])
+        if d["why"]:
+            whys.add(d["why"])
     rates = []
     for w in range(windows):
         steps = sum(p[w][0] for p in per)
         el = max(p[w][1] for p in per)
         rates.append(steps / el)
-    return cores, rates
+    kind = "reference" if kinds == {"reference"} else "port"
+    return cores, rates, kind, ("; ".join(sorted(whys)) or None)
 
 
-def cpu_step_seconds(N: int, seconds: float = 2.0) -> float:
-    """Seconds per RK4 pseudo-step of ONE cavity at order N with the oracle port (one single-threaded process, second of
-    two windows): a single cavity's solve is a serial chain of steps, on the CPU as on the GPU."""
-    env = dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+def cpu_step_seconds(N: int, seconds: float = 2.0, port: bool = False):
+    """(seconds per RK4 pseudo-step, kind) of ONE cavity at order N on one host core (second of two windows): a single
+    cavity's solve is a serial chain of steps, on the CPU as on the GPU."""
     so = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-worker", "--worker-index", "0", "--windows", "2",
-                         "--seconds", str(seconds), "--N", str(N), "--batch", "1"], stdout=subprocess.PIPE, env=env,
-                        text=True, check=True).stdout
-    n, el = json.loads(so.strip().splitlines()[-1])[1]
-    return el / n
+                         "--seconds", str(seconds), "--N", str(N), "--batch", "1"] + (["--cpu-port"] if port else []),
+                        stdout=subprocess.PIPE, env=_cpu_env(), text=True, check=True).stdout
+    d = json.loads(so.strip().splitlines()[-1])
+    n, el = d["windows"][1]
+    return el / n, d["kind"]
+
+
+def _cpu_sample_text(kind, why, cores, seconds, N):
+    what = ("the reference's own MultigridSmoother.step (spectral/multigrid/fsg.py:956-995, Numba kernels, imported "
+            "unmodified from oracle/_ref)" if kind == "reference" else "oracle rk4_step (NumPy port of MultigridSmoother.step)")
+    txt = (f"{cores} single-threaded processes x {seconds:.1f} s windows of {what} at N={N}, one cavity each "
+           "(the reference's joblib-style case parallelism, conf/machine/local.yaml:9)")
+    if kind != "reference" and why:
+        txt += f"; the reference itself was not used: {why}"
+    return txt
 
 
 def reference_arm(args):
-    """--impl reference: the reference's CPU algorithm (oracle port; the reference itself is Python under
-    /root/reference and does not exist on the GPU box) on every host core, same metric/config/unit."""
+    """--impl reference: the reference's own CPU implementation of the path (MultigridSmoother.step from the staged copy
+    oracle/_ref; the NumPy port if that cannot be imported on this box, with the reason) on every host core, same
+    metric / config / unit."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     windows = args.steps + args.warmup
     seconds = max(0.5, min(4.0, 150.0 / max(windows, 1)))
-    cores, rates = run_cpu_windows(args, windows, seconds)
+    cores, rates, kind, why = run_cpu_windows(args, windows, seconds)
     timed = rates[args.warmup:]
     value = sum(timed) / len(timed)
     line = {
@@ -147,9 +191,8 @@ def reference_arm(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * args.pseudo * args.batch / value, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, 1),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{cores} single-threaded processes x {seconds:.1f} s windows of oracle rk4_step at "
-                                   f"N={args.N} (one cavity each; the reference's joblib-style case parallelism)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": _cpu_sample_text(kind, why, cores, seconds, args.N)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -266,11 +309,9 @@ def gpu_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION/INFO) out of it
-    if "LDC_KEEP_NCCL_DEBUG" not in os.environ:
-        os.environ["NCCL_DEBUG"] = "WARN"
-    # ... and whatever else native code writes to file descriptor 1 (the banner still showed up on some boxes): from here
-    # on fd 1 is stderr, the JSON line goes to a private copy of the original stdout
+    # stdout carries exactly one JSON line: whatever native code writes to file descriptor 1 (NCCL's version banner and
+    # its NCCL_DEBUG=INFO log, which the driver reads for the rank count) goes to stderr from here on; the JSON line goes
+    # to a private copy of the original stdout.  NCCL_DEBUG itself is left as the caller set it.
     sys.stdout.flush()
     json_fd = os.dup(1)
     os.dup2(2, 1)
@@ -280,10 +321,9 @@ def gpu_arm(args):
     # CPU baseline first (rank 0, single-GPU run only), before the GPU is busy and before CUDA is initialised here
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        cores, rates = run_cpu_windows(args, 2, 6.0)
-        cpu_baseline = {"value": rates[1], "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"{cores} single-threaded processes x 6 s (after a 6 s warm-up window) of oracle rk4_step "
-                                  f"at N={args.N}, one cavity each"}
+        cores, rates, kind, why = run_cpu_windows(args, 2, 6.0)
+        cpu_baseline = {"value": rates[1], "unit": UNIT, "cores": cores, "kind": kind,
+                        "sample": "second of two windows: " + _cpu_sample_text(kind, why, cores, 6.0, args.N)}
 
     torch.cuda.set_device(local)
     if world > 1:
@@ -306,8 +346,32 @@ def gpu_arm(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    # FP64 ceilings, measured live on this device
+    # FP64 ceilings, measured live on this device: register-resident DMMA / DFMA loops of this library, and an independent
+    # one -- cuBLAS DGEMM 8192^3 through torch.matmul, best of 5
     peaks = {k: ldc_b200.fp64_peak_tflops(local, k) for k in ("dmma", "dfma")}
+    dgemm_tflops = None
+    if rank == 0 and not args.no_dgemm:
+        try:
+            n_g = 8192
+            ga = torch.randn(n_g, n_g, dtype=torch.float64, device="cuda")
+            gb = torch.randn(n_g, n_g, dtype=torch.float64, device="cuda")
+            gc = torch.empty_like(ga)
+            torch.matmul(ga, gb, out=gc)
+            torch.cuda.synchronize()
+            best = None
+            for _ in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                torch.matmul(ga, gb, out=gc)
+                e1.record()
+                torch.cuda.synchronize()
+                ms_g = e0.elapsed_time(e1)
+                best = ms_g if best is None else min(best, ms_g)
+            dgemm_tflops = 2.0 * n_g**3 / (best * 1e-3) / 1e12
+            del ga, gb, gc
+            torch.cuda.empty_cache()
+        except Exception as e:   # out of memory on a shared device: report, do not fail the bench
+            dgemm_tflops = f"unavailable: {type(e).__name__}"
 
     # ---- device-resident throughput ("value") ----
     for _ in range(args.warmup):
@@ -390,11 +454,42 @@ def gpu_arm(args):
             # the same solve with the CPU port, from a bounded sample: seconds per step of the oracle at each level's
             # order (2 s windows) x the iterations this solve took on that level (those of the reference)
             lev = [int(np.asarray(x).ravel()[0]) for x in r.per_level_iterations]
-            per = [cpu_step_seconds(int(n)) for n in r.orders]
-            tt["cpu_port"] = {"wall_s_estimated": float(sum(a * b for a, b in zip(lev, per))), "orders": [int(n) for n in r.orders],
-                              "iterations_per_level": lev, "cpu_us_per_step": [1e6 * x for x in per], "cores": 1,
-                              "sample": "2 s of oracle rk4_step per level (one process, one BLAS thread) x the iteration "
-                                        "count of each level"}
+            pk = [cpu_step_seconds(int(n), port=args.cpu_port) for n in r.orders]
+            per = [x[0] for x in pk]
+            tt["cpu"] = {"wall_s_estimated": float(sum(a * b for a, b in zip(lev, per))), "orders": [int(n) for n in r.orders],
+                         "iterations_per_level": lev, "cpu_us_per_step": [1e6 * x for x in per], "cores": 1,
+                         "kind": "reference" if all(x[1] == "reference" for x in pk) else "port",
+                         "sample": "2 s of MultigridSmoother.step (reference, or its NumPy port: see kind) per level on one "
+                                   "host core x the iteration count of each level"}
+
+    kernel_name = s.kernel_name
+    # ---- sweep_to_tol: BASELINE config 4 to tolerance -- 32 x 32 corner_smoothing x Re, N = 64, FSG [32, 64], 1024 cavities
+    # IN TOTAL, dealt round-robin over the ranks (strong scaling: the work is fixed as N grows) ----
+    sweep = None
+    if not args.no_sweep:
+        from ldc_b200.sharded import solve_sweep
+
+        g = args.sweep_grid
+        cs_g, re_g = np.meshgrid(np.linspace(0.02, 0.35, g), np.linspace(100.0, 1000.0, g), indexing="ij")
+        s.close()            # free the bench handle's device memory first
+        s = None
+        barrier()
+        w0 = time.perf_counter()
+        sw = solve_sweep(args.sweep_N, re_g.ravel(), cs_g.ravel(), 1e-6, 2_000_000, kind="fsg", n_levels=2,
+                         coarse_tolerance_factor=1.0, balance="interleave", fields="rank0", device=local,
+                         per_rank_kernel_ms=True)
+        barrier()
+        wall = time.perf_counter() - w0
+        if rank == 0:
+            km = np.asarray(sw.per_rank_kernel_ms)
+            sweep = {"config": f"BASELINE config 4: {g} x {g} corner_smoothing x Re sweep, N={args.sweep_N}, FSG "
+                               f"[{args.sweep_N // 2},{args.sweep_N}], tol 1e-6, {g * g} cavities in total dealt round-robin "
+                               f"over {world} rank(s); fields gathered to rank 0",
+                     "scaling": "strong", "cavities": int(g * g), "wall_s": wall, "kernel_s_max": float(km.max()) * 1e-3,
+                     "kernel_s_min": float(km.min()) * 1e-3, "iterations_total": int(sw.iterations.sum()),
+                     "iterations_max": int(sw.iterations.max()), "converged": int(sw.converged.sum()),
+                     "diverged": int(sw.diverged.sum()),
+                     "cavity_steps_per_s": float(sw.iterations.sum() / wall)}
 
     if rank == 0:
         flop_launch = B * P * f_step(N)
@@ -402,10 +497,10 @@ def gpu_arm(args):
         # DMMA flops the kernel actually issues (padded tiles): the even-odd kernel runs 40 block GEMMs of HP^3 per
         # stage, the plain resident kernel 10 GEMMs of MP^3; the algorithmic count above is the reference's 12 GEMMs
         m = N - 1
-        if s.kernel_name == "k_resident_eo":
+        if kernel_name == "k_resident_eo":
             hp = -(-((m + 1) // 2) // 8) * 8
             exec_step = 4 * 40 * 2.0 * hp**3
-        elif s.kernel_name == "k_resident_rk4":
+        elif kernel_name == "k_resident_rk4":
             mp = -(-m // 16) * 16
             exec_step = 4 * 10 * 2.0 * mp**3
         else:
@@ -425,15 +520,20 @@ def gpu_arm(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches),
             "clocks": clk,
-            "roofline": {"bound": "tensor", "kernel": f"{s.kernel_name} (FP64 DMMA, mma.sync m8n8k4)", "achieved": achieved,
-                         "peak": peaks["dmma"], "unit": "TFLOP/s", "frac": achieved / peaks["dmma"], "traffic": traffic,
+            "roofline": {"bound": "tensor", "kernel": f"{kernel_name} (FP64 DMMA, mma.sync m8n8k4)",
+                         "achieved": executed, "peak": peaks["dmma"], "unit": "TFLOP/s", "frac": executed / peaks["dmma"],
+                         "achieved_algorithmic": achieved, "frac_algorithmic": achieved / peaks["dmma"],
+                         "traffic": traffic,
                          "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 on this GPU (ldc_fp64_peak); "
-                                        "MEASURED_PEAKS.json has no FP64 figure",
-                         "dfma_peak": peaks["dfma"], "flop_per_launch": flop_launch,
-                         "executed_tflops": executed, "pipe_frac": executed / peaks["dmma"],
-                         "note": "achieved counts the reference's algorithmic flops (12 n^3-GEMMs per stage); the kernel "
-                                 "issues fewer (interior-only tiles, folded pressure interpolation, even-odd splitting), "
-                                 "so frac can exceed 1; pipe_frac = issued DMMA flops / peak",
+                                        "MEASURED_PEAKS.json has no FP64 figure; dgemm_tflops = cuBLAS DGEMM 8192^3 "
+                                        "(torch.matmul, best of 5) measured beside it",
+                         "dfma_peak": peaks["dfma"], "dgemm_tflops": dgemm_tflops, "flop_per_launch": flop_launch,
+                         "executed_flop_per_launch": B * P * exec_step,
+                         "note": "achieved / frac count the DMMA flops the kernel ISSUES (padded parity blocks: 40 block "
+                                 "GEMMs of HP^3 per stage) against the measured DMMA pipe peak; achieved_algorithmic / "
+                                 "frac_algorithmic count the reference's 12 n^3-GEMMs per stage (SURVEY 8d) -- the kernel "
+                                 "issues 40 % of those (interior-only tiles, folded pressure interpolation, even-odd "
+                                 "splitting), so frac_algorithmic exceeds 1",
                          "kernel_ms_per_launch": kern_ms / args.steps},
             "all_finite": finite,
         }
@@ -441,9 +541,12 @@ def gpu_arm(args):
             line["cpu_baseline"] = cpu_baseline
         if tt is not None:
             line["time_to_tol"] = tt
+        if sweep is not None:
+            line["sweep_to_tol"] = sweep
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
-    s.close()
+    if s is not None:
+        s.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -463,6 +566,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-time-to-tol", action="store_true")
     ap.add_argument("--cpu-cores", type=int, default=0)
+    ap.add_argument("--cpu-port", action="store_true", help="time the NumPy oracle port instead of the staged reference")
+    ap.add_argument("--no-dgemm", action="store_true", help="skip the cuBLAS DGEMM 8192^3 ceiling")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the sweep_to_tol leg (BASELINE config 4 to tolerance)")
+    ap.add_argument("--sweep-N", type=int, default=64)
+    ap.add_argument("--sweep-grid", type=int, default=32, help="sweep_to_tol: grid x grid cavities IN TOTAL over all ranks")
     # internal: CPU worker processes
     ap.add_argument("--cpu-worker", action="store_true")
     ap.add_argument("--worker-index", type=int, default=0)

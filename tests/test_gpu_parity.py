@@ -237,34 +237,37 @@ def test_streamed_even_odd_kernel_large_grids(ldc, N):
     p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
     Re = np.array([400.0, 5000.0])
     out = {}
-    for path in ("tiled", "stream_eo"):
+    names = {"tiled": "tiled", "stream_eo": "k_stream_stage", "stream_tma": "k_stream_tma"}
+    for path in names:
         with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
-            assert s.kernel_name == ("tiled" if path == "tiled" else "k_stream_stage")
+            assert s.kernel_name == names[path]
             s.set_cases(Re, corner_smoothing=[0.15, 0.05]).set_state(u, v, p)
             s.step(2, freeze_pressure=(N % 2 == 0))
             r = s.step(3, freeze_pressure=(N % 2 == 0))   # second call: state comes back from the rotated buffers
             out[path] = (*s.get_state(), r)
-    for a, b in zip(out["stream_eo"][:3], out["tiled"][:3]):
-        assert rel(a, b) < 1e-10
-    assert np.allclose(out["stream_eo"][3], out["tiled"][3], rtol=1e-8)
+    for path in ("stream_eo", "stream_tma"):
+        for a, b in zip(out[path][:3], out["tiled"][:3]):
+            assert rel(a, b) < 1e-10, path
+        assert np.allclose(out[path][3], out["tiled"][3], rtol=1e-8), path
     if N >= 66:
         with ldc.BatchedSpectralLDC(N, batch=1) as s:
-            assert s.kernel_name == "k_stream_stage"   # the default path for these sizes
+            assert s.kernel_name == "k_stream_tma"   # the default path for these sizes (persistent TMA-fed kernel)
 
 
 def test_streamed_solve_stops_converged_cavities(ldc):
     """ldc_solve on the streamed path: per-cavity convergence, iteration counts equal to the tiled path."""
     N = 66
     res = {}
-    for path in ("tiled", "stream_eo"):
+    for path in ("tiled", "stream_eo", "stream_tma"):
         with ldc.BatchedSpectralLDC(N, batch=2, path=path) as s:
             s.set_cases([100.0, 400.0]).init_state()
             r = s.solve([1e-2, 3e-3], 3000, warmup=0)
             res[path] = (r.iterations.copy(), r.converged.copy(), s.get_state())
-    assert np.array_equal(res["tiled"][0], res["stream_eo"][0]) and res["tiled"][1].all() and res["stream_eo"][1].all()
     assert res["tiled"][0][0] != res["tiled"][0][1]
-    for a, b in zip(res["stream_eo"][2], res["tiled"][2]):
-        assert rel(a, b) < 1e-10
+    for path in ("stream_eo", "stream_tma"):
+        assert np.array_equal(res["tiled"][0], res[path][0]) and res["tiled"][1].all() and res[path][1].all(), path
+        for a, b in zip(res[path][2], res["tiled"][2]):
+            assert rel(a, b) < 1e-10, path
 
 
 def test_error_paths(ldc):
@@ -370,14 +373,17 @@ def test_full_bench_batch_properties(ldc):
     assert np.all(u[:, 20:-20, -1] == 1.0)   # the unsmoothed middle of the lid
 
 
-@pytest.mark.parametrize("N,B", [(128, 3), (80, 12)])
-def test_streamed_kernel_is_deterministic_and_batch_independent(ldc, N, B):
-    """Both shapes of the streamed stage kernel (one CTA per SM with the split-K warp group; two CTAs per SM): repeated
-    runs agree bit for bit (no shared-memory race shows up as run-to-run noise) and a cavity does not see its batch-mates."""
+@pytest.mark.parametrize("path", ["stream_eo", "stream_tma"])
+@pytest.mark.parametrize("N,B", [(128, 3), (80, 12), (80, 40)])
+def test_streamed_kernel_is_deterministic_and_batch_independent(ldc, N, B, path):
+    """Both shapes of the streamed stage kernel (one CTA per SM with the split-K warp group; two CTAs per SM) and the
+    persistent TMA-fed kernel (B = 40 at N = 80: more cavities than teams, so cavities migrate between teams through the
+    queue): repeated runs agree bit for bit (no shared-memory or team-barrier race shows up as run-to-run noise) and a
+    cavity does not see its batch-mates."""
     Re = np.linspace(300.0, 900.0, B)
     runs = []
     for _ in range(2):
-        with ldc.BatchedSpectralLDC(N, batch=B, path="stream_eo") as s:
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
             s.set_cases(Re).init_state()
             r = s.step(6)
             runs.append((*s.get_state(), r))
@@ -386,13 +392,13 @@ def test_streamed_kernel_is_deterministic_and_batch_independent(ldc, N, B):
     # same kernel shape for the solo run: (128, 1) and (80, 12 -> 1) both keep their template (h > 48 resp. B x 16 <= #SM
     # would switch the N = 80 case, so compare it inside one batch instead: duplicate cavities must agree)
     if N == 128:
-        with ldc.BatchedSpectralLDC(N, batch=1, path="stream_eo") as s:
+        with ldc.BatchedSpectralLDC(N, batch=1, path=path) as s:
             s.set_cases(Re[1]).init_state()
             s.step(6)
             u1, v1, p1 = s.get_state()
         assert np.array_equal(runs[0][0][1], u1[0]) and np.array_equal(runs[0][2][1], p1[0])
     else:
-        with ldc.BatchedSpectralLDC(N, batch=B, path="stream_eo") as s:
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
             s.set_cases(np.full(B, Re[3])).init_state()
             s.step(6)
             u, v, p = s.get_state()
@@ -436,7 +442,7 @@ def test_largest_streamed_grid_and_beyond_against_the_oracle(ldc, N):
     for _ in range(2):
         orc.rk4_step(lv, uo, vo, po, case, ul, vl, freeze_pressure=False)
     with ldc.BatchedSpectralLDC(N, batch=1) as s:
-        assert s.kernel_name == ("k_stream_stage" if N <= 129 else "tiled")
+        assert s.kernel_name == ("k_stream_tma" if N <= 129 else "tiled")
         s.set_cases(400.0).init_state()
         s.step(2, want_rel=False)
         u, v, p = s.get_state()
