@@ -39,6 +39,17 @@ def test_library_contains_sm100a_dmma_code(built_lib):
     out = subprocess.run([cuobjdump, "-sass", built_lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "sm_100a" in out
     assert "DMMA.8x8x4" in out, "the resident kernel must issue FP64 tensor-core instructions"
+    # the persistent streamed kernel is fed by TMA bulk copies with mbarrier completion
+    assert "UBLKCP" in out and "SYNCS.ARRIVE.TRANS64" in out, "k_stream_tma must issue cp.async.bulk (TMA) copies"
+
+
+def test_batch_beyond_the_grid_limit_is_refused(built_lib):
+    """The batch index is gridDim.y / z of the per-cavity kernels: ldc_create refuses what a launch could not take."""
+    lib = ctypes.CDLL(built_lib.LIB_PATH)
+    lib.ldc_last_error.restype = ctypes.c_char_p
+    h = ctypes.c_void_p()
+    assert lib.ldc_create(ctypes.byref(h), 8, 8, 65536, 0, None) == 1   # LDC_ERR_INVALID, before any device is touched
+    assert b"65535" in lib.ldc_last_error() and not h.value
 
 
 def test_no_cpu_fallback_without_a_device(built_lib):

@@ -1,0 +1,212 @@
+"""Round-2 parity cases: BASELINE config 5 pinned to the reference (N = 128, Re = 5000, 200 steps from the
+prolongated 64 -> 128 state), config 3's jittered-Re cavities at N = 64, the corners of the config-4 grid to tolerance,
+`ldc_restrict`, a solve on a non-blocking stream, operators that are not mirror-symmetric, and the MRO recipe of
+INTEGRATION.md against the reference's own base class.  Tolerances: fields rel-L2 <= 1e-10, iterations +-1."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def ldc(built_lib):
+    import torch
+
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return built_lib
+
+
+@pytest.mark.parametrize("path", ["stream_tma", "stream_eo"])
+def test_config5_n128_re5000_from_the_prolongated_state(ldc, golden, path):
+    """`ldc_prolongate` 64 -> 128 (fft, BC quirk Q3, endpoint weights Q10) of the reference's N = 64
+    state, then 200 `MultigridSmoother.step` equivalents at N = 128, Re = 5000 (1 +- 2 %) on the streamed kernels, against
+    the reference's own run (tests/golden/make_golden_n128.py): fields after 1 and 200 steps <= 1e-10, norms after 50."""
+    g = golden.n128
+    ncav, k64, k128 = (int(x) for x in g["meta"])
+    Re = g["Re"]
+    with ldc.BatchedSpectralLDC(64, batch=ncav) as c, ldc.BatchedSpectralLDC(128, batch=ncav, path=path) as f:
+        c.set_cases(Re, corner_smoothing=0.15)
+        f.set_cases(Re, corner_smoothing=0.15)
+        c.set_state(np.stack([g[f"c{b}_u64"] for b in range(ncav)]), np.stack([g[f"c{b}_v64"] for b in range(ncav)]),
+                    np.stack([g[f"c{b}_p64"] for b in range(ncav)]))
+        c.prolongate_to(f, "fft", bc_quirk=True)
+        u, v, p = f.get_state()
+        for b in range(ncav):   # the fixture was taken BEFORE initialize_lid: compare off the lid column
+            assert rel(u[b][:, :-1], g[f"c{b}_u128_0"][:, :-1]) < 1e-12
+            assert rel(v[b][:, :-1], g[f"c{b}_v128_0"][:, :-1]) < 1e-12
+            assert rel(p[b], g[f"c{b}_p128_0"]) < 1e-12
+            assert np.all(u[b][-1, 1:-1] == 1.0)   # Q3: the east wall carries lid_velocity into the first step
+        assert f.kernel_name == ("k_stream_tma" if path == "stream_tma" else "k_stream_stage")
+        done = 0
+        for k in (1, 50, k128):
+            r = f.step(k - done)
+            done = k
+            u, v, p = f.get_state()
+            for b in range(ncav):
+                if k == 50:
+                    nr = g[f"c{b}_norms128_50"]
+                    assert np.allclose([np.linalg.norm(u[b]), np.linalg.norm(v[b]), np.linalg.norm(p[b])], nr, rtol=1e-11)
+                else:
+                    assert rel(u[b], g[f"c{b}_u128_{k}"]) < 1e-10, (k, b)
+                    assert rel(v[b], g[f"c{b}_v128_{k}"]) < 1e-10, (k, b)
+                    assert rel(p[b], g[f"c{b}_p128_{k}"]) < 1e-10, (k, b)
+                assert np.allclose(r[b], g[f"c{b}_res128"][k - 1], rtol=1e-8), (k, b)
+
+
+@pytest.mark.parametrize("path", ["resident_eo", "resident", "stream_tma", "tiled"])
+def test_config3_jittered_re_cavities_n64(ldc, golden, path):
+    """BASELINE config 3: the first three cavities of the jittered-Re batch (seed 0) at N = 64, 200 staged-pressure steps
+    from the cold start against the reference's smoother."""
+    g = golden.holes
+    Re = g["c3_Re"]
+    n2 = 65 * 65
+    with ldc.BatchedSpectralLDC(64, batch=3, path=path) as s:
+        s.set_cases(Re, corner_smoothing=0.15).init_state()
+        r = s.step(200)
+        u, v, p = s.get_state()
+    for b in range(3):
+        ref = g["c3_state"][b]
+        assert rel(u[b].ravel(), ref[:n2]) < 1e-10 and rel(v[b].ravel(), ref[n2:2 * n2]) < 1e-10
+        assert rel(p[b].ravel(), ref[2 * n2:]) < 1e-10
+        assert np.allclose(r[b], g["c3_res"][b], rtol=1e-8)
+
+
+def test_config4_grid_corners_to_tolerance_through_solve_sweep(ldc, golden):
+    """BASELINE config 4: the four corners of the corner_smoothing x Re grid (cs in {0.02, 0.35}, Re in {100, 1000}) as FSG
+    [16, 32] solves to 1e-6 through `solve_sweep`, against the reference's FSGSolver: iteration counts (incl. the cavity that
+    diverges on the coarse level, Q8), flags and converged fields."""
+    from ldc_b200.sharded import solve_sweep
+
+    g = golden.holes
+    meta = np.array([g[f"c4_{k}_meta"] for k in range(4)])
+    r = solve_sweep(32, meta[:, 1], meta[:, 0], 1e-6, 500_000, kind="fsg", n_levels=2, coarse_tolerance_factor=1.0,
+                    balance="interleave")
+    for k in range(4):
+        assert abs(int(r.iterations[k]) - int(meta[k, 2])) <= 1, (k, r.iterations[k], meta[k, 2])
+        assert bool(r.converged[k]) == bool(meta[k, 3])
+        if meta[k, 3]:
+            for f in ("u", "v", "p"):
+                assert rel(getattr(r, f)[k], g[f"c4_{k}_{f}"]) < 1e-10, (k, f)
+        else:   # diverged on the coarse level: the finest level is never touched (zeros), as the reference returns it
+            assert r.diverged[k] and not np.any(r.u[k]) and not np.any(g[f"c4_{k}_u"])
+
+
+@pytest.mark.parametrize("method", ["fft", "injection"])
+def test_restrict_against_the_reference_maps(ldc, golden, method):
+    """`ldc_restrict` (reference: `restrict_solution`, multigrid/fsg.py:622-664; FFTRestriction / InjectionRestriction,
+    operators/transfer_operators.py:258-325, 379-428 -- uncalled by the reference's driver): interior of the restricted
+    fields against the reference's 2-D maps, boundary = walls + lid as the ABI documents."""
+    g = golden.holes
+    with ldc.BatchedSpectralLDC(16, batch=2) as f, ldc.BatchedSpectralLDC(8, batch=2) as c:
+        f.set_cases(100.0)
+        c.set_cases(100.0)
+        f.set_state(np.stack([g["r_uf"], 2 * g["r_uf"]]), np.stack([g["r_vf"], -g["r_vf"]]), np.stack([g["r_pf"], g["r_pf"]]))
+        f.restrict_to(c, method)
+        u, v, p = c.get_state()
+    tol = 1e-12
+    assert rel(u[0][1:-1, 1:-1], g[f"r_uc_{method}"][1:-1, 1:-1]) < tol
+    assert rel(v[0][1:-1, 1:-1], g[f"r_vc_{method}"][1:-1, 1:-1]) < tol
+    assert rel(p[0], g[f"r_pc_{method}"]) < tol
+    assert rel(u[1][1:-1, 1:-1], 2 * g[f"r_uc_{method}"][1:-1, 1:-1]) < tol
+    if method == "injection":   # what restrict_solution itself does
+        assert rel(u[0][1:-1, 1:-1], g["r_uc_solution"][1:-1, 1:-1]) < tol and rel(p[0], g["r_pc_solution"]) < tol
+    assert not u[0][0].any() and not u[0][-1].any() and not u[0][:, 0].any() and np.array_equal(u[0][:, -1], c.u_lid[0])
+
+
+@pytest.mark.parametrize("N,path", [(24, "resident_eo"), (72, "stream_tma"), (72, "stream_eo"), (20, "tiled")])
+def test_solve_on_a_non_blocking_stream(ldc, N, path):
+    """A caller stream created non-blocking (every torch.cuda.Stream) is not ordered against the legacy default stream: the
+    handle's lazy allocations must be zero-filled on the handle's own stream.  Same result as on the default stream."""
+    import torch
+
+    out = []
+    for use_stream in (False, True):
+        st = torch.cuda.Stream() if use_stream else None
+        with ldc.BatchedSpectralLDC(N, batch=3, path=path, stream=(st.cuda_stream if st else None)) as s:
+            s.set_cases([100.0, 200.0, 300.0]).init_state()
+            s.step(4)
+            r = s.solve(1e-3, 400, warmup=0)
+            out.append((r.iterations.copy(), *s.get_state()))
+        torch.cuda.synchronize()
+    for a, b in zip(out[0], out[1]):
+        assert np.array_equal(a, b)
+
+
+def test_operators_without_mirror_symmetry_do_not_take_the_even_odd_kernels(ldc):
+    """The even-odd kernels keep only the parity blocks of D, DD, I: operators of a grid that is not symmetric about its
+    mid-point must run on the plain kernels under AUTO and be refused (LDC_ERR_UNSUPPORTED) on a forced even-odd path."""
+    from ldc_b200 import _lib
+    from oracle import ldc_oracle as orc
+
+    N = 16
+    lv = orc.build_level(N)
+    xi = 2.0 * lv.x - 1.0
+    x = 0.5 * (np.tanh(1.2 * xi + 0.3) / np.tanh(1.5) + 1.0)          # a stretched, asymmetric node set
+    x = (x - x[0]) / (x[-1] - x[0])
+    n = N + 1
+    # Lagrange differentiation matrix on x (barycentric form), Dxx = D @ D, interpolation inner -> full by polynomial fit
+    w = np.array([1.0 / np.prod([x[j] - x[k] for k in range(n) if k != j]) for j in range(n)])
+    D = np.zeros((n, n))
+    for i in range(n):
+        for j in range(n):
+            if i != j:
+                D[i, j] = (w[j] / w[i]) / (x[i] - x[j])
+        D[i, i] = -D[i].sum()
+    DD = D @ D
+    V = np.polynomial.chebyshev.chebvander(2 * x - 1, N - 2)
+    Ix = V @ np.linalg.solve(V[1:-1], np.eye(N - 1))
+    dxm = float(np.min(np.diff(x)))
+    ul, vl = orc.lid_profile(x, "smoothing", 0.15, 1.0, 1.0)
+
+    def run(path):
+        with ldc.BatchedSpectralLDC(N, batch=2, path=path) as s:
+            args = [np.ascontiguousarray(a) for a in (D, DD, D, DD, Ix, Ix)]
+            import ctypes
+
+            _lib.check(s.lib.ldc_set_operators(s._h, *[_lib.ptr(a) for a in args], ctypes.c_double(dxm), ctypes.c_double(dxm)),
+                       "ldc_set_operators")
+            s.set_cases([100.0, 400.0], u_lid=np.stack([ul, ul]), v_lid=np.stack([vl, vl])).init_state()
+            name = s.kernel_name
+            s.step(5)
+            return name, s.get_state()
+
+    name, ref = run("tiled")
+    name, got = run("auto")
+    assert name == "k_resident_rk4"      # not k_resident_eo / _split: the symmetry test failed
+    for a, b in zip(got, ref):
+        assert rel(a, b) < 1e-11
+    with pytest.raises(ldc.LdcError, match="cannot run this shape"):
+        run("resident_eo")
+
+
+def test_mro_recipe_of_integration_md_against_the_reference_base(ldc):
+    """`class SGSolver(_b200.SGSolver, LidDrivenCavitySolver)` -- the B200 numerics first, the
+    reference's I/O helpers second -- built on the reference's own base class (staged copy oracle/_ref) and solved."""
+    from oracle import ref_loader
+
+    if ref_loader.why_unavailable():
+        pytest.skip(ref_loader.why_unavailable())
+    ref = ref_loader.load_reference()
+    from ldc_b200 import solvers as _b200
+
+    class SGSolver(_b200.SGSolver, ref.LidDrivenCavitySolver):   # MRO: B200 numerics first, reference helpers second
+        pass
+
+    assert SGSolver.__mro__[1] is _b200.SGSolver and ref.LidDrivenCavitySolver in SGSolver.__mro__
+    s = SGSolver(name="spectral", Re=100.0, lid_velocity=1.0, Lx=1.0, Ly=1.0, nx=16, ny=16, tolerance=1e-6,
+                 max_iterations=10_000_000, basis_type="chebyshev", CFL=1.5, beta_squared=5.0, corner_treatment="smoothing",
+                 corner_smoothing=0.15, multigrid="none")
+    assert SGSolver.solve is _b200.SGSolver.solve            # the time loop is the B200 one
+    s.solve()
+    assert s.metrics.iterations == 14155 and s.metrics.converged   # the reference's count
+    assert s.fields.u.shape == (17 * 17,) or s.fields.u.size == 17 * 17
+    d = s.metrics.to_mlflow()
+    assert "iterations" in d

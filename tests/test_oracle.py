@@ -136,3 +136,48 @@ def test_fsg_divergence_semantics(golden):
     assert not out["converged"] and out["diverged"] and meta[1] == 0.0
     assert not out["u"].any() and not g["fsg_Re1000_N30_cs005_u"].any()
     assert 0.5 * meta[0] < out["iterations"] < 2.0 * meta[0]
+
+
+def test_config5_n128_prolongated_trajectory(golden):
+    """BASELINE config 5 (tests/golden/make_golden_n128.py): the oracle's prolongation 64 -> 128 and 200 steps at N = 128,
+    Re = 5000 against the reference's own run -- the same fixture the streamed CUDA kernels are held to."""
+    g = golden.n128
+    lc, lf = orc.build_level(64), orc.build_level(128)
+    b = 0
+    Re = float(g["Re"][b])
+    uf, vf, pf = orc.prolongate_state(lc, lf, g[f"c{b}_u64"], g[f"c{b}_v64"], g[f"c{b}_p64"], "fft", 1.0)
+    assert rel(uf, g[f"c{b}_u128_0"]) < 1e-13 and rel(vf, g[f"c{b}_v128_0"]) < 1e-13 and rel(pf, g[f"c{b}_p128_0"]) < 1e-13
+    ul, vl = orc.lid_profile(lf.x, "smoothing", 0.15, 1.0, 1.0)
+    uf[:, -1] = ul
+    vf[:, -1] = vl
+    case = orc.Case(Re=Re)
+    for k in range(1, 201):
+        orc.rk4_step(lf, uf, vf, pf, case, ul, vl, freeze_pressure=False)
+        if k == 1:
+            assert rel(uf, g[f"c{b}_u128_1"]) < 1e-12 and rel(pf, g[f"c{b}_p128_1"]) < 1e-12
+        if k == 50:
+            assert np.allclose([np.linalg.norm(uf), np.linalg.norm(vf), np.linalg.norm(pf)], g[f"c{b}_norms128_50"], rtol=1e-11)
+    assert rel(uf, g[f"c{b}_u128_200"]) < 1e-10 and rel(vf, g[f"c{b}_v128_200"]) < 1e-10 and rel(pf, g[f"c{b}_p128_200"]) < 1e-10
+
+
+def test_restriction_maps(golden):
+    g = golden.holes
+    for method in ("fft", "injection"):
+        fn = orc.RESTRICT_1D[method]
+        assert rel(orc.transfer_2d(fn, g["r_uf"], (9, 9)), g[f"r_uc_{method}"]) < 1e-13
+        assert rel(orc.transfer_2d(fn, g["r_pf"], (7, 7)), g[f"r_pc_{method}"]) < 1e-13
+    assert np.array_equal(g["r_uc_solution"], g["r_uc_injection"])   # restrict_solution always injects
+
+
+def test_config3_jittered_cavity_n64(golden):
+    g = golden.holes
+    lv = orc.build_level(64)
+    Re = float(g["c3_Re"][1])
+    ul, vl = orc.lid_profile(lv.x, "smoothing", 0.15, 1.0, 1.0)
+    u, v, p = orc.initial_state(lv, ul, vl)
+    case = orc.Case(Re=Re)
+    for _ in range(200):
+        orc.rk4_step(lv, u, v, p, case, ul, vl, freeze_pressure=False)
+    n2 = 65 * 65
+    ref = g["c3_state"][1]
+    assert rel(u.ravel(), ref[:n2]) < 1e-11 and rel(v.ravel(), ref[n2:2 * n2]) < 1e-11 and rel(p.ravel(), ref[2 * n2:]) < 1e-11
