@@ -741,7 +741,6 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         const size_t bs = (size_t)h->B * S2_STRIDE;
         if (!h->t_state) {
             if ((rc = dalloc(h, &h->t_state, 3 * bs))) return rc;
-            if ((rc = dalloc(h, &h->t_opsc, (size_t)h->B * S2_OPS))) return rc;
             if ((rc = dalloc(h, &h->t_team, 2 * (size_t)h->num_sms))) return rc;
             if (!h->s_partials && (rc = dalloc(h, &h->s_partials, (size_t)h->B * ST_TILES * 8))) return rc;
             if (!h->q_data) {
@@ -752,12 +751,12 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         }
         if ((rc = ensure_packed(h, 4))) return rc;
         LDC_CUDA(cudaEventRecord(h->ev0, h->stream));
-        k_s2_pack_ops<<<dim3(48, h->B), 256, 0, h->stream>>>(h->s_ops, h->Re, h->t_opsc);
+        k_s2_pack_ops<<<dim3(48, h->B), 256, 0, h->stream>>>(h->s_ops, h->Re, h->t_state, bs);
         h->launches += 1;
         k_s2_begin<<<h->B, 256, 0, h->stream>>>(h->t_state, h->mx, h->status);   // max|u|, max|v| of the start state
         h->launches += 1;
         S2Params P;
-        P.ops = h->s_ops; P.opsc = h->t_opsc; P.rec = h->t_state; P.buf_stride = bs;
+        P.ops = h->s_ops; P.rec = h->t_state; P.buf_stride = bs;
         P.Re = h->Re; P.beta2 = h->beta2; P.CFL = h->CFL; P.lidvel = h->lidvel; P.ulid = h->ulid; P.vlid = h->vlid;
         P.n1 = h->n1x; P.m = h->mx; P.K4 = (eo_half(h->mx) + 3) / 4 * 4; P.ntile = ntile;
         P.status = h->status; P.partials = h->s_partials; P.tol = tol_dev;
@@ -766,6 +765,14 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         P.q_data = h->q_data; P.q_seq = h->q_seq; P.q_ctl = h->q_ctl; P.B = h->B;
         P.team_bar = reinterpret_cast<unsigned*>(h->t_team);
         P.team_mail = reinterpret_cast<unsigned long long*>(h->t_team + h->num_sms);
+        // LDC_S2_DEBUG=<file>: clock samples of CTA 0 for the first stages of the first launch (stream_tma.cuh)
+        const char* dbg_path = getenv("LDC_S2_DEBUG");
+        long long* dbg = nullptr;
+        if (dbg_path) {
+            LDC_CUDA(cudaMalloc((void**)&dbg, S2_DBG_STAGES * 16 * sizeof(long long)));
+            LDC_CUDA(cudaMemsetAsync(dbg, 0, S2_DBG_STAGES * 16 * sizeof(long long), h->stream));
+        }
+        P.dbg = dbg;
         h->canon_valid = false;
         const long long per_launch = 512;   // steps per launch (the host looks at the active count between launches)
         for (long long done = start; done < stop; done += per_launch) {
@@ -784,12 +791,28 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             LDC_CUDA(cudaLaunchCooperativeKernel((const void*)k_stream_tma, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
                                                  h->stream));
             h->launches += 2;
+            if (dbg) {
+                std::vector<long long> hd(S2_DBG_STAGES * 16);
+                LDC_CUDA(cudaMemcpyAsync(hd.data(), dbg, hd.size() * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+                LDC_CUDA(cudaStreamSynchronize(h->stream));
+                if (FILE* f = fopen(dbg_path, "w")) {
+                    for (int st = 0; st < S2_DBG_STAGES; ++st) {
+                        for (int q = 0; q < 16; ++q) fprintf(f, "%lld ", hd[st * 16 + q]);
+                        fprintf(f, "\n");
+                    }
+                    fclose(f);
+                }
+                cudaFree(dbg);
+                dbg = nullptr;
+                P.dbg = nullptr;
+            }
             if (done + per_launch < stop) {
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
                 if (na == 0) break;
             }
         }
+        if (dbg) cudaFree(dbg);
         // every cavity's record back into buffer 0
         k_s2_normalise<<<dim3(64, h->B), 256, 0, h->stream>>>(h->t_state, bs, h->status);
         k_stream_clear_pad<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);

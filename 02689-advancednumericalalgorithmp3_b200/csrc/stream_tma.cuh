@@ -25,36 +25,38 @@ namespace ldc {
 constexpr int S2_HP = ST_HP;                 // padded parity-block edge (64)
 constexpr int S2_NK4 = S2_HP / 4;            // k4-steps per block row
 constexpr int S2_KC4 = 2;                    // k4-steps per chunk (K-chunk of 8)
-constexpr int S2_SLOTS = 5;                  // chunk slots in flight
+constexpr int S2_SLOTS = 4;                  // chunk slots in flight
 constexpr int S2_CONSUMERS = 256;            // 8 warps: (k-group) x (u | v equation) x (row half)
 constexpr int S2_THREADS = S2_CONSUMERS + 128;   // + the producer's warpgroup (setmaxnreg works on warpgroups)
 constexpr int S2_ME = 2 * S2_HP;
-// global record of one cavity (doubles): UV_R | UV_C | P_R | P_C | boundary lines (8 x ME) | 8 corners
-//   X_R[rt][kk][blk][r][kq] = X_blk[16 rt + r][4 kk + kq]      (row-type)
-//   X_C[ct][kk][blk][c][kq] = X_blk[4 kk + kq][16 ct + c]      (column-type: the transpose, row-type)
-constexpr size_t S2_UV = (size_t)4 * S2_NK4 * 8 * 64;
-constexpr size_t S2_P = (size_t)4 * S2_NK4 * 4 * 64;
-constexpr size_t S2_OPS = (size_t)4 * S2_NK4 * 6 * 64;   // per-cavity operators D_SA D_AS nuDD_SS nuDD_AA -G_SA -G_AS, row-type
-constexpr size_t S2_EDGE_OFF = 2 * S2_UV + 2 * S2_P;
+// global record of one cavity (doubles): row side | column side | boundary lines (8 x ME) | 8 corners.  A side holds, for
+// each 16-line tile and k4-step, S2_NB = 18 blocks of 16 x 4 doubles back to back -- the six operator blocks of the cavity
+// (D_SA D_AS nuDD_SS nuDD_AA -G_SA -G_AS; both sides carry the same copy) and the twelve state blocks u(4) v(4) p(4):
+//   row side    [rt][kk][blk][r][kq] = X_blk[16 rt + r][4 kk + kq]
+//   column side [ct][kk][blk][c][kq] = X_blk[4 kk + kq][16 ct + c]   (state: the transpose; operators: rows 16 ct + c)
+// so that ONE bulk copy per side brings everything a K-chunk needs (the TMA unit takes ~350 cycles per copy whatever its
+// size: scripts/tma_bw.cu, profiles/r02_tma_bw.txt).
+constexpr int S2_NB = 18, S2_BU = 6, S2_BV = 10, S2_BP = 14;
+constexpr size_t S2_SIDE = (size_t)4 * S2_NK4 * S2_NB * 64;
+constexpr size_t S2_EDGE_OFF = 2 * S2_SIDE;
 constexpr size_t S2_STRIDE = S2_EDGE_OFF + 8 * S2_ME + 8;
-// one chunk slot (doubles): O at tile rows | O at tile columns | UV rows | UV columns | P rows | P columns
-constexpr int S2_SL_OA = 0, S2_SL_OB = S2_KC4 * 6 * 64, S2_SL_FA = 2 * S2_KC4 * 6 * 64, S2_SL_FB = S2_SL_FA + S2_KC4 * 8 * 64,
-              S2_SL_PA = S2_SL_FB + S2_KC4 * 8 * 64, S2_SL_PB = S2_SL_PA + S2_KC4 * 4 * 64, S2_SLOT = S2_SL_PB + S2_KC4 * 4 * 64;
+// one chunk slot (doubles): row side [kk][blk][16][4] | column side
+constexpr int S2_SL_A = 0, S2_SL_B = S2_KC4 * S2_NB * 64, S2_SLOT = 2 * S2_KC4 * S2_NB * 64;
+constexpr unsigned S2_SIDE_BYTES = S2_KC4 * S2_NB * 64 * sizeof(double);
 constexpr unsigned S2_SLOT_BYTES = S2_SLOT * sizeof(double);
 constexpr size_t S2_SMEM_DOUBLES = (size_t)S2_SLOTS * S2_SLOT   // chunk ring
-                                   + 8 * 256                    // stage input u, v at the tile's own elements
+                                   + 8 * 256 + 12 * 256         // stage input u, v and phi^n (u, v, p) at the tile's own elements
                                    + 8 * S2_HP + 16 * S2_HP     // boundary-column vectors, boundary lines in parity form
                                    + 4 * 8 * 32                 // dv/dy hand-over v warps -> u warps
                                    + 16 * 8 + 80 + 16           // tile partials, reduction scratch, step info
                                    + 2 * S2_SLOTS + 2;          // mbarriers
 
-__host__ __device__ inline size_t s2_off(int nblk, int tile, int kk, int blk, int r, int kq) {
-    return (((size_t)tile * S2_NK4 + kk) * nblk + blk) * 64 + r * 4 + kq;
+__host__ __device__ inline size_t s2_off(int tile, int kk, int blk, int r, int kq) {
+    return (((size_t)tile * S2_NK4 + kk) * S2_NB + blk) * 64 + r * 4 + kq;
 }
 
 struct S2Params {
     const double* ops;            // eo packed operators (HP = 64): only the 8 boundary-column vectors are read here
-    const double* opsc;           // [B][S2_OPS]
     double* rec;                  // [3][B][S2_STRIDE] rotating records
     size_t buf_stride;            // B * S2_STRIDE
     const double *Re, *beta2, *CFL, *lidvel, *ulid, *vlid;
@@ -68,7 +70,9 @@ struct S2Params {
     int* q_data; unsigned* q_seq; unsigned* q_ctl; int B;   // cavity work queue (resident.cuh)
     unsigned* team_bar;           // [teams] arrivals at the team's stage barriers (zero at launch)
     unsigned long long* team_mail;// [teams] (visit number << 32) | (cavity + 1), written by the team's leader
+    long long* dbg;               // optional [S2_DBG_STAGES][16] clock samples of CTA 0 (LDC_S2_DEBUG), else null
 };
+constexpr int S2_DBG_STAGES = 256;
 
 // ---- PTX wrappers ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned s2_smem(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -94,6 +98,21 @@ __device__ __forceinline__ void bulk_g2s(double* dst, const double* src, unsigne
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(s2_smem(dst)), "l"(src), "r"(bytes), "r"(s2_smem(bar)) : "memory");
 }
+// the same with shared-memory addresses already converted (the producer keeps them in registers)
+__device__ __forceinline__ void mbar_expect_tx_a(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s_a(unsigned dst, const double* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -114,7 +133,7 @@ __device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned l
 }
 
 // ---- layout conversion kernels -----------------------------------------------------------------------------------------
-// canonical (u, v, p) -> record (row-type and column-type copies of the twelve parity blocks + boundary lines)
+// canonical (u, v, p) -> record (row-side and column-side copies of the twelve parity blocks + boundary lines)
 __global__ void k_s2_pack_state(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ p,
                                 double* __restrict__ rec, int n1) {
     const int b = blockIdx.y, HP = S2_HP, m = n1 - 2, h = eo_half(m), N = n1 - 1;
@@ -139,13 +158,11 @@ __global__ void k_s2_pack_state(const double* __restrict__ u, const double* __re
             }
             const double blk4[4] = {0.25 * ((q0 + q1) + (q2 + q3)), 0.25 * ((q0 + q1) - (q2 + q3)),
                                     0.25 * ((q0 - q1) + (q2 - q3)), 0.25 * ((q0 - q1) - (q2 - q3))};   // SS SA AS AA
-            const int nblk = f < 2 ? 8 : 4, b0 = f == 1 ? 4 : 0;
-            double* R = s + (f < 2 ? 0 : 2 * S2_UV);
-            double* C = R + (f < 2 ? S2_UV : S2_P);
+            const int b0 = S2_BU + 4 * f;
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                R[s2_off(nblk, i / 16, k / 4, b0 + q, i % 16, k % 4)] = blk4[q];
-                C[s2_off(nblk, k / 16, i / 4, b0 + q, k % 16, i % 4)] = blk4[q];
+                s[s2_off(i / 16, k / 4, b0 + q, i % 16, k % 4)] = blk4[q];
+                s[S2_SIDE + s2_off(k / 16, i / 4, b0 + q, k % 16, i % 4)] = blk4[q];
             }
         }
     }
@@ -205,12 +222,11 @@ __global__ void k_s2_unpack_state(double* __restrict__ u, double* __restrict__ v
         double f[3];
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
-            const int nblk = q < 2 ? 8 : 4, b0 = q == 1 ? 4 : 0;
-            const double* R = s + (q < 2 ? 0 : 2 * S2_UV);
-            const double ss = R[s2_off(nblk, r / 16, c / 4, b0 + 0, r % 16, c % 4)];
-            const double sA = R[s2_off(nblk, r / 16, c / 4, b0 + 1, r % 16, c % 4)];
-            const double as = R[s2_off(nblk, r / 16, c / 4, b0 + 2, r % 16, c % 4)];
-            const double aa = R[s2_off(nblk, r / 16, c / 4, b0 + 3, r % 16, c % 4)];
+            const int b0 = S2_BU + 4 * q;
+            const double ss = s[s2_off(r / 16, c / 4, b0 + 0, r % 16, c % 4)];
+            const double sA = s[s2_off(r / 16, c / 4, b0 + 1, r % 16, c % 4)];
+            const double as = s[s2_off(r / 16, c / 4, b0 + 2, r % 16, c % 4)];
+            const double aa = s[s2_off(r / 16, c / 4, b0 + 3, r % 16, c % 4)];
             f[q] = (ss + sb * sA) + sa * (as + sb * aa);
         }
         uu = f[0];
@@ -221,15 +237,22 @@ __global__ void k_s2_unpack_state(double* __restrict__ u, double* __restrict__ v
     v[(size_t)b * n1 * n1 + e] = vv;
 }
 
-// per-cavity operator panels: D as is, DD scaled by nu = 1 / Re, G negated; row-type k4-interleaved layout
-__global__ void k_s2_pack_ops(const double* __restrict__ ops, const double* __restrict__ Re, double* __restrict__ opsc) {
+// the cavity's operator blocks into both sides of its three records: D as is, DD scaled by nu = 1 / Re, G negated
+__global__ void k_s2_pack_ops(const double* __restrict__ ops, const double* __restrict__ Re, double* __restrict__ rec,
+                              size_t buf_stride) {
     const int b = blockIdx.y;
     const double nu = 1.0 / Re[b];
-    double* dst = opsc + (size_t)b * S2_OPS;
+    double* dst = rec + (size_t)b * S2_STRIDE;
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 6 * S2_HP * S2_HP; e += gridDim.x * blockDim.x) {
         const int blk = e / (S2_HP * S2_HP), i = (e / S2_HP) % S2_HP, k = e % S2_HP;
         const double sc = blk < 2 ? 1.0 : (blk < 4 ? nu : -1.0);
-        dst[s2_off(6, i / 16, k / 4, blk, i % 16, k % 4)] = sc * ops[(size_t)blk * ST_BLK + i * ST_LD + k];
+        const double val = sc * ops[(size_t)blk * ST_BLK + i * ST_LD + k];
+        const size_t o = s2_off(i / 16, k / 4, blk, i % 16, k % 4);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            dst[q * buf_stride + o] = val;
+            dst[q * buf_stride + S2_SIDE + o] = val;
+        }
     }
 }
 
@@ -245,8 +268,8 @@ __global__ void __launch_bounds__(256) k_s2_begin(const double* __restrict__ buf
 #pragma unroll
         for (int f = 0; f < 2; ++f) {
             double r[4];
-            eo_to_points(rec[s2_off(8, i / 16, k / 4, 4 * f + 0, i % 16, k % 4)], rec[s2_off(8, i / 16, k / 4, 4 * f + 1, i % 16, k % 4)],
-                         rec[s2_off(8, i / 16, k / 4, 4 * f + 2, i % 16, k % 4)], rec[s2_off(8, i / 16, k / 4, 4 * f + 3, i % 16, k % 4)], r);
+            const size_t o = s2_off(i / 16, k / 4, S2_BU + 4 * f, i % 16, k % 4);
+            eo_to_points(rec[o], rec[o + 64], rec[o + 128], rec[o + 192], r);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 isnan_[f] |= (r[q] != r[q]);
@@ -279,27 +302,28 @@ template <bool P_LEFT>
 __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int ksteps, int ro, int co, int fld,
                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int NT = 2;
-    const double* sOa = sl + S2_SL_OA + ro;
-    const double* sOb = sl + S2_SL_OB + co;
-    const double* sFa = sl + S2_SL_FA + fld * 256 + ro;
-    const double* sFb = sl + S2_SL_FB + fld * 256 + co;
-    const double* sPa = sl + S2_SL_PA + ro;
-    const double* sPb = sl + S2_SL_PB + co;
+    // every operand of a k4-step sits in one 18-block group of its side: [kk][blk][16][4]
+    const double* sOa = sl + S2_SL_A + ro;
+    const double* sOb = sl + S2_SL_B + co;
+    const double* sFa = sl + S2_SL_A + (S2_BU + 4 * fld) * 64 + ro;
+    const double* sFb = sl + S2_SL_B + (S2_BU + 4 * fld) * 64 + co;
+    const double* sPa = sl + S2_SL_A + S2_BP * 64 + ro;
+    const double* sPb = sl + S2_SL_B + S2_BP * 64 + co;
 #pragma unroll 1
     for (int kk = 0; kk < ksteps; ++kk) {
         double FA[4], FB[4][NT];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            FA[q] = sFa[(kk * 8 + q) * 64];
+            FA[q] = sFa[(kk * S2_NB + q) * 64];
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) FB[q][nt] = sFb[(kk * 8 + q) * 64 + nt * 32];
+            for (int nt = 0; nt < NT; ++nt) FB[q][nt] = sFb[(kk * S2_NB + q) * 64 + nt * 32];
         }
         {
             double dA[2], ddA[2];
 #pragma unroll
             for (int a = 0; a < 2; ++a) {
-                dA[a] = sOa[(kk * 6 + a) * 64];
-                ddA[a] = sOa[(kk * 6 + 2 + a) * 64];
+                dA[a] = sOa[(kk * S2_NB + a) * 64];
+                ddA[a] = sOa[(kk * S2_NB + 2 + a) * 64];
             }
 #pragma unroll
             for (int a = 0; a < 2; ++a)
@@ -317,8 +341,8 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kste
             for (int b = 0; b < 2; ++b)
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt) {
-                    dB[b][nt] = sOb[(kk * 6 + b) * 64 + nt * 32];
-                    ddB[b][nt] = sOb[(kk * 6 + 2 + b) * 64 + nt * 32];
+                    dB[b][nt] = sOb[(kk * S2_NB + b) * 64 + nt * 32];
+                    ddB[b][nt] = sOb[(kk * S2_NB + 2 + b) * 64 + nt * 32];
                 }
 #pragma unroll
             for (int a = 0; a < 2; ++a)
@@ -333,11 +357,11 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kste
         if (P_LEFT) {
             double gA[2], PB[4][NT];
 #pragma unroll
-            for (int a = 0; a < 2; ++a) gA[a] = sOa[(kk * 6 + 4 + a) * 64];
+            for (int a = 0; a < 2; ++a) gA[a] = sOa[(kk * S2_NB + 4 + a) * 64];
 #pragma unroll
             for (int q = 0; q < 4; ++q)
 #pragma unroll
-                for (int nt = 0; nt < NT; ++nt) PB[q][nt] = sPb[(kk * 4 + q) * 64 + nt * 32];
+                for (int nt = 0; nt < NT; ++nt) PB[q][nt] = sPb[(kk * S2_NB + q) * 64 + nt * 32];
 #pragma unroll
             for (int a = 0; a < 2; ++a)
 #pragma unroll
@@ -348,11 +372,11 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kste
         } else {
             double PA[4], gB[2][NT];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) PA[q] = sPa[(kk * 4 + q) * 64];
+            for (int q = 0; q < 4; ++q) PA[q] = sPa[(kk * S2_NB + q) * 64];
 #pragma unroll
             for (int b = 0; b < 2; ++b)
 #pragma unroll
-                for (int nt = 0; nt < NT; ++nt) gB[b][nt] = sOb[(kk * 6 + 4 + b) * 64 + nt * 32];
+                for (int nt = 0; nt < NT; ++nt) gB[b][nt] = sOb[(kk * S2_NB + 4 + b) * 64 + nt * 32];
 #pragma unroll
             for (int a = 0; a < 2; ++a)
 #pragma unroll
@@ -451,30 +475,23 @@ struct S2Visit {
 template <int X>
 __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, double* __restrict__ exch_own,
                                           const double* __restrict__ exch_other, unsigned long long* empty_other,
-                                          const double* __restrict__ sUV, const double* __restrict__ sVec,
+                                          const double* __restrict__ sUV, const double* __restrict__ sPhi,
+                                          const double* __restrict__ sVec,
                                           double* __restrict__ sEdgeP, double* __restrict__ sX, double* __restrict__ sRed,
                                           const double* __restrict__ recN, double* __restrict__ recO, int tile, int b,
                                           int r0, int c0, int stage, bool bc_lines, double dt, int fld, int tw, int lane,
-                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2],
+                                          long long* __restrict__ tdbg) {
     const int g = lane >> 2, t = lane & 3;
     const int tid128 = threadIdx.x & 127;
     const int m = P.m, h = eo_half(m), centre = (m & 1) ? h - 1 : -1;
     const int i = r0 + 8 * tw + g, j0 = c0 + 8 * X + 2 * t;
     const int rt = r0 >> 4, ct = c0 >> 4, ir = i & 15;
-    // phi^n of the warp's field (and p^n for the u warps) at the thread's elements: issued now, used after the swap
-    const size_t offR = s2_off(8, rt, j0 >> 2, 4 * fld, ir, j0 & 3);    // + q * 64
-    const size_t offPR = s2_off(4, rt, j0 >> 2, 0, ir, j0 & 3);
-    double2 f0[4], p0[4];
-    if (stage != 0) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) f0[q] = __ldcg(reinterpret_cast<const double2*>(recN + offR + q * 64));
-    }
-    if (fld == 0) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) p0[q] = __ldcg(reinterpret_cast<const double2*>(recN + 2 * S2_UV + offPR + q * 64));
-    }
+    const size_t offR = s2_off(rt, j0 >> 2, S2_BU + 4 * fld, ir, j0 & 3);    // + q * 64
+    const size_t offPR = s2_off(rt, j0 >> 2, S2_BP, ir, j0 & 3);
     // ---- split-K hand-over: give away the other half, take the partner's contribution to this half ----
     consumer_sync();   // both groups are done reading their last chunk slots
+    if (tdbg) tdbg[0] = clock64();
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
@@ -484,8 +501,8 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
             exch_own[(8 + idx) * 128 + tid128] = a2[q][1 - X][hh];
             exch_own[(16 + idx) * 128 + tid128] = aL[q][1 - X][hh];
         }
-    fence_proxy_async();   // these generic writes land in a slot the TMA refills later
     consumer_sync();
+    if (tdbg) tdbg[1] = clock64();
     double b1[4][2], b2[4][2], bL[4][2];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
@@ -499,8 +516,7 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
             b2[q][hh] = X == 0 ? a2[q][X][hh] + o2 : o2 + a2[q][X][hh];
             bL[q][hh] = X == 0 ? aL[q][X][hh] + oL : oL + aL[q][X][hh];
         }
-    // the partner's slot has been read: hand it back to the producer (generic reads/writes before the async refill)
-    fence_proxy_async();
+    // the partner's slot has been read -- its generic writes are therefore performed --: hand it back to the producer
     __syncwarp();
     if (lane == 0) mbar_arrive(empty_other);
 
@@ -510,8 +526,10 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
         const int pos = (X * 2 + tw) * 32 + lane;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double2 a = *reinterpret_cast<const double2*>(sUV + ((0 + q) * 128 + pos) * 2);
-            const double2 c = *reinterpret_cast<const double2*>(sUV + ((4 + q) * 128 + pos) * 2);
+            // stage 0: the stage input is phi^n itself (picked into sPhi during the K loop)
+            const double* uvsrc = stage == 0 ? sPhi : sUV;
+            const double2 a = *reinterpret_cast<const double2*>(uvsrc + ((0 + q) * 128 + pos) * 2);
+            const double2 c = *reinterpret_cast<const double2*>(uvsrc + ((4 + q) * 128 + pos) * 2);
             uo[q][0] = a.x; uo[q][1] = a.y;
             vo[q][0] = c.x; vo[q][1] = c.y;
         }
@@ -527,11 +545,12 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
         const double w0 = 4.0 * wi * (j0 == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j0 + 1 == centre ? 0.5 : 1.0);
         double fn[4][2];
         double* outR = recO + offR;
-        double* outC = recO + S2_UV + s2_off(8, ct, i >> 2, 4 * fld, j0 & 15, i & 3);   // + q * 64; second column + 4
+        double* outC = recO + S2_SIDE + s2_off(ct, i >> 2, S2_BU + 4 * fld, j0 & 15, i & 3);   // + q * 64; second column + 4
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double fx = stage == 0 ? (fld == 0 ? uo[q][0] : vo[q][0]) : f0[q].x;
-            const double fy = stage == 0 ? (fld == 0 ? uo[q][1] : vo[q][1]) : f0[q].y;
+            // phi^n of the warp's field at the thread's elements: kept in shared memory since stage 0 of this step
+            const double2 f0 = *reinterpret_cast<const double2*>(sPhi + ((4 * fld + q) * 128 + (X * 2 + tw) * 32 + lane) * 2);
+            const double fx = f0.x, fy = f0.y;
             fn[q][0] = fx + adt * bL[q][0];
             fn[q][1] = fy + adt * bL[q][1];
             if (last) {
@@ -571,15 +590,22 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
             sRed[w * 4 + 2] = mx;
         }
     }
+    if (tdbg) tdbg[2] = clock64();
     consumer_sync();   // dv/dy of the v warps is in sX (and the warps' partial sums in sRed)
     if (fld == 0) {
-        double* outR = recO + 2 * S2_UV + offPR;
-        double* outC = recO + 2 * S2_UV + S2_P + s2_off(4, ct, i >> 2, 0, j0 & 15, i & 3);
+        double* outR = recO + offPR;
+        double* outC = recO + S2_SIDE + s2_off(ct, i >> 2, S2_BP, j0 & 15, i & 3);
+        // frozen pressure (SGSolver): every stage takes grad(p^n), and a low-storage stage never reads the
+        // previous stage's p, so stages 0..2 pass p^n on as the next stage's pressure operand and only the last stage
+        // stores the new p; staged pressure (MultigridSmoother): every stage stores its own
+        const bool keep_pn = P.freeze && stage != 3;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const double dv0 = b1[q][0] + sX[((X * 2 + tw) * 8 + q * 2 + 0) * 32 + lane];
             const double dv1 = b1[q][1] + sX[((X * 2 + tw) * 8 + q * 2 + 1) * 32 + lane];
-            const double pn0 = p0[q].x + adt * (-V.beta2 * dv0), pn1 = p0[q].y + adt * (-V.beta2 * dv1);
+            const double2 p0 = *reinterpret_cast<const double2*>(sPhi + ((8 + q) * 128 + (X * 2 + tw) * 32 + lane) * 2);
+            const double pn0 = keep_pn ? p0.x : p0.x + adt * (-V.beta2 * dv0);
+            const double pn1 = keep_pn ? p0.y : p0.y + adt * (-V.beta2 * dv1);
             __stcg(reinterpret_cast<double2*>(outR + q * 64), make_double2(pn0, pn1));
             __stcg(outC + q * 64, pn0);
             __stcg(outC + q * 64 + 4, pn1);
@@ -642,13 +668,14 @@ __device__ __forceinline__ void s2_consumer_reduce(double (&s)[4], double (&mx)[
 
 // shared-memory carve-up of k_stream_tma
 struct S2Smem {
-    double *slot, *uv, *vec, *edgep, *x, *part, *red, *step;
+    double *slot, *uv, *phin, *vec, *edgep, *x, *part, *red, *step;
     unsigned long long *full, *empty, *stepbar;
     int* cavity;
     __device__ explicit S2Smem(double* smem) {
         slot = smem;
         uv = slot + (size_t)S2_SLOTS * S2_SLOT;
-        vec = uv + 8 * 256;
+        phin = uv + 8 * 256;
+        vec = phin + 12 * 256;
         edgep = vec + 8 * S2_HP;
         x = edgep + 16 * S2_HP;
         part = x + 4 * 8 * 32;             // [16 tiles][8]
@@ -674,9 +701,9 @@ struct S2Geo {
     }
 };
 
-// named barriers: 1 = the eight consumer warps (consumer_sync); 2 = consumers + producer warp, start of a visit;
+// named barriers: 1 = the eight consumer warps (consumer_sync); 2 = consumers + the four producer warps, start of a visit;
 // 3 = consumers arrive / producer waits: the visit's boundary-line sums are in shared memory
-__device__ __forceinline__ void visit_sync() { asm volatile("bar.sync 2, 288;" ::: "memory"); }
+__device__ __forceinline__ void visit_sync() { asm volatile("bar.sync 2, 384;" ::: "memory"); }
 __device__ __forceinline__ void sums_arrive() { asm volatile("bar.arrive 3, 288;" ::: "memory"); }
 __device__ __forceinline__ void sums_wait() { asm volatile("bar.sync 3, 288;" ::: "memory"); }
 
@@ -691,6 +718,8 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
     const int clast_other = ((nch - 1 - (1 - X)) & ~1) + (1 - X);
     unsigned gcb = 0;        // chunks consumed before the current stage (ring position)
     unsigned nstepinfo = 0;  // step-info hand-overs consumed so far
+    const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && (tid & 127) == 0;   // warp 0 (group 0) and warp 4 (group 1)
+    int dbg_stage = 0;
 
     for (;;) {
         visit_sync();   // the producer warp has the team's next cavity
@@ -786,24 +815,43 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                     for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
                         for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+                // Stage 0 picks phi^n (the warp's field; the u warps also p^n) out of the passing row panels into S.phin,
+                // where it stays for the four stages; stages 1..3 pick the stage input of the warp's field into S.uv.
+                double* grab_dst = stage == 0 ? S.phin : S.uv;
                 if (cgrab >= nch) {   // the group's columns lie in the zero padding
                     const int pos = (X * 2 + tw) * 32 + lane;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        *reinterpret_cast<double2*>(S.uv + ((4 * fld + q) * 128 + pos) * 2) = make_double2(0.0, 0.0);
+                    for (int q = 0; q < 4; ++q) {
+                        *reinterpret_cast<double2*>(grab_dst + ((4 * fld + q) * 128 + pos) * 2) = make_double2(0.0, 0.0);
+                        if (stage == 0 && fld == 0)
+                            *reinterpret_cast<double2*>(S.phin + ((8 + q) * 128 + pos) * 2) = make_double2(0.0, 0.0);
+                    }
                 }
+                long long t_start = 0, t_wait = 0;
+                if (dbg_on) t_start = clock64();
                 for (int c = X; c < nch; c += 2) {
                     const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
+                    long long tw0 = 0;
+                    if (dbg_on) tw0 = clock64();
                     mbar_wait(S.full + slot, (gc / S2_SLOTS) & 1);
+                    if (dbg_on) {
+                        const long long tw1 = clock64();
+                        t_wait += tw1 - tw0;
+                        if (c == X && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + X * 4 + 1] = tw1 - t_start;
+                    }
                     const double* sl = S.slot + (size_t)slot * S2_SLOT;
                     if (c == cgrab) {
                         // the thread's own elements of its field's stage input: columns 8 X + 2 t, + 1 of the tile
                         const int pos = (X * 2 + tw) * 32 + lane;
-                        const double* src = sl + S2_SL_FA + ((t >> 1) * 8 + 4 * fld) * 64 + (8 * tw + g) * 4 + 2 * (t & 1);
+                        const double* src = sl + S2_SL_A + ((t >> 1) * S2_NB + S2_BU + 4 * fld) * 64 + (8 * tw + g) * 4 + 2 * (t & 1);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                            *reinterpret_cast<double2*>(S.uv + ((4 * fld + q) * 128 + pos) * 2) =
+                        for (int q = 0; q < 4; ++q) {
+                            *reinterpret_cast<double2*>(grab_dst + ((4 * fld + q) * 128 + pos) * 2) =
                                 *reinterpret_cast<const double2*>(src + q * 64);
+                            if (stage == 0 && fld == 0)   // p^n: the pressure blocks sit (S2_BP - S2_BU) blocks further on
+                                *reinterpret_cast<double2*>(S.phin + ((8 + q) * 128 + pos) * 2) =
+                                    *reinterpret_cast<const double2*>(src + (S2_BP - S2_BU + q) * 64);
+                        }
                     }
                     const int ksteps = min(S2_KC4, G.nk4 - c * S2_KC4);
                     if (fld == 0) s2_chunk<true>(sl, ksteps, ro, co, fld, a1, a2, aL);
@@ -815,6 +863,8 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                 }
                 const unsigned slot_own = (gcb + clast_own) % S2_SLOTS, slot_other = (gcb + clast_other) % S2_SLOTS;
                 gcb += nch;
+                long long t_loop = 0;
+                if (dbg_on) t_loop = clock64();
                 if (stage == 0 && step > 0) {
                     // the reduction of the previous step (producer warp): dt of this step, and whether there is one
                     mbar_wait(S.stepbar, nstepinfo & 1);
@@ -828,54 +878,87 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                         break;
                     }
                 }
+                long long tfin[4] = {0, 0, 0, 0};
                 double* exch_own = S.slot + (size_t)slot_own * S2_SLOT;
                 const double* exch_other = S.slot + (size_t)slot_other * S2_SLOT;
                 if (X == 0)
-                    s2_finish<0>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.vec, S.edgep, S.x, S.red, recN, recO,
-                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL);
+                    s2_finish<0>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
+                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL,
+                                 (dbg_on && dbg_stage < S2_DBG_STAGES) ? tfin : nullptr);
                 else
-                    s2_finish<1>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.vec, S.edgep, S.x, S.red, recN, recO,
-                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL);
+                    s2_finish<1>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
+                                 G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL, nullptr);
                 bc_lines = true;
-                // ---- arrive at the team's stage barrier: this CTA's stage output is complete ----
-                fence_proxy_async();   // the stage output is read by the team's TMA copies (async proxy)
+                long long t_fin = 0;
+                if (dbg_on) t_fin = clock64();
+                // ---- arrive at the team's stage barrier: this CTA's stage output is complete.  The release of the counter
+                // update (cumulative over the CTA barrier) publishes every consumer's stores; the readers are TMA copies,
+                // whose issuing thread crosses to the async proxy after its acquire (s2_producer_main) ----
                 consumer_sync();
-                if (tid == 0) {
-                    __threadfence();
-                    red_release_add(P.team_bar + G.team, 1u);
+                if (tid == 0) red_release_add(P.team_bar + G.team, 1u);
+                if (dbg_on && dbg_stage < S2_DBG_STAGES) {
+                    // per group X: [0] stage start (absolute), [1] wait for the first chunk, [2] K loop incl. waits,
+                    // [3] all waits inside the K loop; group 0 also: [8] exchange + epilogue, [9] arrive,
+                    // [13] wait for the other group, [14] accumulator swap, [15] assembly + momentum stores
+                    long long* d = P.dbg + dbg_stage * 16 + X * 4;
+                    d[0] = t_start;
+                    d[2] = t_loop - t_start;
+                    d[3] = t_wait;
+                    if (X == 0) {
+                        P.dbg[dbg_stage * 16 + 8] = t_fin - t_loop;
+                        P.dbg[dbg_stage * 16 + 9] = clock64() - t_fin;
+                        P.dbg[dbg_stage * 16 + 13] = tfin[0] - t_loop;
+                        P.dbg[dbg_stage * 16 + 14] = tfin[1] - tfin[0];
+                        P.dbg[dbg_stage * 16 + 15] = tfin[2] - tfin[1];
+                    }
                 }
+                ++dbg_stage;
                 if (stage == 3) cur = (cur + 2) % 3;
             }
         }
     }
 }
 
-// ============================================ producer / reducer warp ============================================
-__device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem& S, const S2Geo& G) {
+// ======================================= producer warps (8: leader, 9..11: helpers) =======================================
+// One thread's bulk copies are served one after the other, ~360 cycles each whatever their size, while copies issued by
+// different warps proceed side by side (scripts/tma_bw.cu, profiles/r02_tma_bw.txt).  So the four warps of the producer
+// warpgroup each issue ONE side of every other chunk: warp 8 + pw issues side (pw & 1) of the chunks c = (pw >> 1) mod 2.
+// Warp 8 is also the team's link to the cavity queue and the reducer of the end-of-step sums.
+__device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem& S, const S2Geo& G, int pw) {
     const int lane = threadIdx.x & 31;
+    const bool leader = pw == 0;
+    const int side = pw & 1, cpar = pw >> 1;
     const int m = G.m, n1 = G.n1, nch = G.nch, team_size = G.team_size;
-    const int npre = nch < S2_SLOTS ? nch : S2_SLOTS;
     unsigned gcb = 0;        // chunks issued before the current stage (ring position)
     unsigned nbar = 0;       // team barriers completed before the current stage
+    unsigned nstepinfo = 0;  // step-info hand-overs seen so far (helpers)
     unsigned visit = 0;
+    const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && lane == 0 && leader;
+    int dbg_stage = 0;
+    const unsigned slot0 = s2_smem(S.slot), full0 = s2_smem(S.full), empty0 = s2_smem(S.empty);
+    // this warp's side of chunk c of a record: c chunk-strides after the tile's first k4-step (s2_off)
+    const size_t off_side = side == 0 ? (size_t)G.trow * (S2_NK4 * S2_NB * 64) : S2_SIDE + (size_t)G.tcol * (S2_NK4 * S2_NB * 64);
+    const unsigned sl_side = (side == 0 ? S2_SL_A : S2_SL_B) * 8;
 
     for (;;) {
         // ---- the team's next cavity ----
-        int b = 0;
-        if (lane == 0) {
-            if (G.tin == 0) {
-                b = CavityQueue::pop(P);
-                st_release_u64(P.team_mail + G.team, ((unsigned long long)(visit + 1) << 32) | (unsigned)(b + 1));
-            } else {
-                unsigned long long mail;
-                while (((mail = ld_acquire_u64(P.team_mail + G.team)) >> 32) != visit + 1) __nanosleep(100);
-                b = (int)(unsigned)(mail & 0xffffffffu) - 1;
+        if (leader) {
+            int bq = 0;
+            if (lane == 0) {
+                if (G.tin == 0) {
+                    bq = CavityQueue::pop(P);
+                    st_release_u64(P.team_mail + G.team, ((unsigned long long)(visit + 1) << 32) | (unsigned)(bq + 1));
+                } else {
+                    unsigned long long mail;
+                    while (((mail = ld_acquire_u64(P.team_mail + G.team)) >> 32) != visit + 1) __nanosleep(100);
+                    bq = (int)(unsigned)(mail & 0xffffffffu) - 1;
+                }
+                *S.cavity = bq;
+                __threadfence_block();
             }
-            *S.cavity = b;
         }
-        b = __shfl_sync(0xffffffffu, b, 0);
-        __threadfence_block();
         visit_sync();
+        const int b = *S.cavity;
         if (b < 0) return;
         ++visit;
         fence_proxy_async();   // the record was written through the generic proxy (another team, or the pack kernel)
@@ -889,24 +972,9 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
         if (nsteps > P.chunk) nsteps = P.chunk;
         const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
         double* rec0 = P.rec + (size_t)b * S2_STRIDE;
-        const double* opsc = P.opsc + (size_t)b * S2_OPS;
         bool active = true, sums_ready = false;
 
-        auto issue_ops = [&](int c, unsigned slot) {
-            double* sl = S.slot + (size_t)slot * S2_SLOT;
-            mbar_expect_tx(S.full + slot, S2_SLOT_BYTES);
-            bulk_g2s(sl + S2_SL_OA, opsc + s2_off(6, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 6 * 64 * 8, S.full + slot);
-            bulk_g2s(sl + S2_SL_OB, opsc + s2_off(6, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 6 * 64 * 8, S.full + slot);
-        };
-        auto issue_state = [&](int c, unsigned slot, const double* recI, const double* recP) {
-            double* sl = S.slot + (size_t)slot * S2_SLOT;
-            bulk_g2s(sl + S2_SL_FA, recI + s2_off(8, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 8 * 64 * 8, S.full + slot);
-            bulk_g2s(sl + S2_SL_FB, recI + S2_UV + s2_off(8, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 8 * 64 * 8, S.full + slot);
-            bulk_g2s(sl + S2_SL_PA, recP + 2 * S2_UV + s2_off(4, G.trow, c * S2_KC4, 0, 0, 0), S2_KC4 * 4 * 64 * 8, S.full + slot);
-            bulk_g2s(sl + S2_SL_PB, recP + 2 * S2_UV + S2_P + s2_off(4, G.tcol, c * S2_KC4, 0, 0, 0), S2_KC4 * 4 * 64 * 8,
-                     S.full + slot);
-        };
-        // end-of-step reduction: tile partials in fixed order + boundary lines, convergence bookkeeping
+        // end-of-step reduction (leader): tile partials in fixed order + boundary lines, convergence bookkeeping
         auto reduce_step = [&](bool first_step) {
             if (!sums_ready) {
                 sums_wait();   // the consumers' boundary-line sums of this visit
@@ -942,24 +1010,49 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
 
         for (long long step = 0; step < nsteps && active; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
-                const double* recN = rec0 + (size_t)cur * P.buf_stride;
-                const double* recI = rec0 + (size_t)st_in(cur, stage) * P.buf_stride;
-                const double* recP = P.freeze ? recN : recI;   // pressure operand
+                // the stage input: its pressure blocks are p^n in every stage when the pressure is frozen (s2_finish)
+                const double* src = rec0 + (size_t)st_in(cur, stage) * P.buf_stride + off_side;
                 const bool need_bar = !(step == 0 && stage == 0);
+                const bool reduce_now = stage == 0 && step > 0;
                 if (lane == 0) {
-                    for (int c = 0; c < npre; ++c) {
-                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
-                        mbar_wait(S.empty + slot, ((gc / S2_SLOTS) & 1) ^ 1);
-                        issue_ops(c, slot);
-                    }
+                    long long tp0 = 0, tp1 = 0;
+                    if (dbg_on) tp0 = clock64();
                     if (need_bar) {
                         wait_team();
                         fence_proxy_async();
                     }
-                    for (int c = 0; c < npre; ++c) issue_state(c, (gcb + c) % S2_SLOTS, recI, recP);
+                    if (dbg_on) tp1 = clock64();
+                    int c = cpar;
+                    // the chunks whose slots are free at the start of a stage first; the leader then reduces
+                    for (; c < nch && c < S2_SLOTS; c += 2) {
+                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
+                        mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                        mbar_expect_tx_a(fb, S2_SIDE_BYTES);
+                        bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + sl_side, src + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
+                    }
+                    if (dbg_on && dbg_stage < S2_DBG_STAGES) {
+                        // [10] start of the wait (absolute), [11] wait at the team barrier, [12] issue of the first chunks
+                        P.dbg[dbg_stage * 16 + 10] = tp0;
+                        P.dbg[dbg_stage * 16 + 11] = tp1 - tp0;
+                        P.dbg[dbg_stage * 16 + 12] = clock64() - tp1;
+                    }
+                    ++dbg_stage;
                 }
                 __syncwarp();
-                if (stage == 0 && step > 0) {
+                if (lane == 0) {
+                    int c = cpar;
+                    while (c < nch && c < S2_SLOTS) c += 2;
+                    for (; c < nch; c += 2) {
+                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
+                        mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                        mbar_expect_tx_a(fb, S2_SIDE_BYTES);
+                        bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + sl_side, src + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
+                    }
+                }
+                __syncwarp();
+                gcb += nch;
+                if (reduce_now && leader) {
+                    // the previous step's sums (needed by the consumers only at this stage's epilogue)
                     reduce_step(first && step == 1);
                     if (lane == 0) {
                         active = st.active != 0;
@@ -970,21 +1063,18 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
                     }
                     active = __shfl_sync(0xffffffffu, (int)active, 0) != 0;
                 }
-                if (lane == 0) {
-                    for (int c = npre; c < nch; ++c) {
-                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
-                        mbar_wait(S.empty + slot, ((gc / S2_SLOTS) & 1) ^ 1);
-                        issue_ops(c, slot);
-                        issue_state(c, slot, recI, recP);
-                    }
+                if (reduce_now && !leader) {
+                    // the leader's verdict on the previous step: is this stage a real one or was it speculative?
+                    mbar_wait(S.stepbar, nstepinfo & 1);
+                    ++nstepinfo;
+                    active = S.step[1] != 0.0;
                 }
-                __syncwarp();
-                gcb += nch;
                 if (!active) break;   // the consumers drop this (speculative) stage as well: no barrier follows it
                 ++nbar;
                 if (stage == 3) cur = (cur + 2) % 3;
             }
         }
+        if (!leader) continue;
         if (active) {
             // the last step of the visit: wait for the team, then its reduction
             if (lane == 0) wait_team();
@@ -1025,8 +1115,8 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
 }
 
 // The persistent kernel.  grid = teams x (tiles per cavity), cooperative launch (every CTA co-resident: the team barriers
-// and the queue spin).  384 threads: warps 0..7 consume (232 registers each after setmaxnreg), warp 8 produces and
-// reduces (40 registers), warps 9..11 exist only because setmaxnreg works on whole warpgroups and leave at once.
+// and the queue spin).  384 threads: warps 0..7 consume (224 registers each after setmaxnreg), warp 8 produces and
+// reduces (56 registers), warps 9..11 exist only because setmaxnreg works on whole warpgroups and leave at once.
 __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) {
     extern __shared__ __align__(16) double smem[];
     const S2Smem S(smem);
@@ -1034,7 +1124,7 @@ __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) 
     const int tid = threadIdx.x, warp = tid >> 5;
     if (tid == 0) {
         for (int s = 0; s < S2_SLOTS; ++s) {
-            mbar_init(S.full + s, 1);
+            mbar_init(S.full + s, 2);   // one arrival (with its byte count) per side
             mbar_init(S.empty + s, 4);
         }
         mbar_init(S.stepbar, 1);
@@ -1043,10 +1133,10 @@ __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) 
     for (int e = tid; e < 8 * S2_HP; e += S2_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
     __syncthreads();
     if (warp >= 8) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == 8) s2_producer_main(P, S, G);
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        s2_producer_main(P, S, G, warp - 8);
     } else {
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
         s2_consumer_main(P, S, G);
     }
 }

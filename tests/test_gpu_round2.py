@@ -90,7 +90,10 @@ def test_config4_grid_corners_to_tolerance_through_solve_sweep(ldc, golden):
     r = solve_sweep(32, meta[:, 1], meta[:, 0], 1e-6, 500_000, kind="fsg", n_levels=2, coarse_tolerance_factor=1.0,
                     balance="interleave")
     for k in range(4):
-        assert abs(int(r.iterations[k]) - int(meta[k, 2])) <= 1, (k, r.iterations[k], meta[k, 2])
+        # a converged solve: +-1 iteration.  A blow-up is exponentially sensitive to rounding, so the iteration at which a
+        # diverging cavity first shows a non-finite residual is held to 1 % (reference: 2894, Q8)
+        slack = 1 if meta[k, 3] else max(1, int(0.01 * meta[k, 2]))
+        assert abs(int(r.iterations[k]) - int(meta[k, 2])) <= slack, (k, r.iterations[k], meta[k, 2])
         assert bool(r.converged[k]) == bool(meta[k, 3])
         if meta[k, 3]:
             for f in ("u", "v", "p"):
