@@ -120,6 +120,12 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -296,10 +302,10 @@ __global__ void __launch_bounds__(256) k_s2_begin(const double* __restrict__ buf
 }
 
 // ---- the K loop of one chunk -------------------------------------------------------------------------------------------
-// Contractions of the warp's field for `ksteps` k4-steps of one chunk slot (cf. st_chunk / eo_field_pass).
+// Contractions of the warp's field for the k4-steps [kbeg, kend) of one chunk slot (cf. st_chunk / eo_field_pass).
 //   ro = (8 tw + g) * 4 + t : the thread's A-fragment offset inside a 16 x 4 block;  co = g * 4 + t : B-fragment offset
 template <bool P_LEFT>
-__device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int ksteps, int ro, int co, int fld,
+__device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kbeg, int kend, int ro, int co, int fld,
                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int NT = 2;
     // every operand of a k4-step sits in one 18-block group of its side: [kk][blk][16][4]
@@ -310,7 +316,7 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kste
     const double* sPa = sl + S2_SL_A + S2_BP * 64 + ro;
     const double* sPb = sl + S2_SL_B + S2_BP * 64 + co;
 #pragma unroll 1
-    for (int kk = 0; kk < ksteps; ++kk) {
+    for (int kk = kbeg; kk < kend; ++kk) {
         double FA[4], FB[4][NT];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -474,7 +480,8 @@ struct S2Visit {
 // tile), then the epilogue of that half.  Returns nothing; writes the stage output, and at the last stage the tile partials.
 template <int X>
 __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, double* __restrict__ exch_own,
-                                          const double* __restrict__ exch_other, unsigned long long* empty_other,
+                                          const double* __restrict__ exch_other, unsigned long long* empty_own,
+                                          unsigned long long* empty_other,
                                           const double* __restrict__ sUV, const double* __restrict__ sPhi,
                                           const double* __restrict__ sVec,
                                           double* __restrict__ sEdgeP, double* __restrict__ sX, double* __restrict__ sRed,
@@ -516,9 +523,13 @@ __device__ __forceinline__ void s2_finish(const S2Params& P, const S2Visit& V, d
             b2[q][hh] = X == 0 ? a2[q][X][hh] + o2 : o2 + a2[q][X][hh];
             bL[q][hh] = X == 0 ? aL[q][X][hh] + oL : oL + aL[q][X][hh];
         }
-    // the partner's slot has been read -- its generic writes are therefore performed --: hand it back to the producer
+    // the partner's slot has been read -- its generic writes are therefore performed --: hand both slots back to the
+    // producers (each slot is refilled once all eight warps have let go of it)
     __syncwarp();
-    if (lane == 0) mbar_arrive(empty_other);
+    if (lane == 0) {
+        mbar_arrive(empty_own);
+        mbar_arrive(empty_other);
+    }
 
     // ---- stage input u, v at the thread's elements (picked out of the row panels during the K loop) ----
     double uo[4][2], vo[4][2];
@@ -669,7 +680,7 @@ __device__ __forceinline__ void s2_consumer_reduce(double (&s)[4], double (&mx)[
 // shared-memory carve-up of k_stream_tma
 struct S2Smem {
     double *slot, *uv, *phin, *vec, *edgep, *x, *part, *red, *step;
-    unsigned long long *full, *empty, *stepbar;
+    unsigned long long *full, *empty, *stepbar, *teambar;
     int* cavity;
     __device__ explicit S2Smem(double* smem) {
         slot = smem;
@@ -684,6 +695,7 @@ struct S2Smem {
         full = reinterpret_cast<unsigned long long*>(step + 16);
         empty = full + S2_SLOTS;
         stepbar = empty + S2_SLOTS;
+        teambar = stepbar + 1;
         cavity = reinterpret_cast<int*>(step + 15);
     }
 };
@@ -714,8 +726,8 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
     const int ro = (8 * tw + g) * 4 + t, co = g * 4 + t;
     const int m = G.m, h = G.h, n1 = G.n1, nch = G.nch;
     const int cgrab = (G.c0 >> 3) + X;                       // the chunk holding this group's 8 columns of the tile
-    const int clast_own = ((nch - 1 - X) & ~1) + X;          // the group's last chunk
-    const int clast_other = ((nch - 1 - (1 - X)) & ~1) + (1 - X);
+    // Split K: both k-groups visit every chunk, group X takes the chunk's k4-step X.  The slots of the last two chunks
+    // are kept after the loop: the groups swap accumulator halves through them (s2_finish).
     unsigned gcb = 0;        // chunks consumed before the current stage (ring position)
     unsigned nstepinfo = 0;  // step-info hand-overs consumed so far
     const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && (tid & 127) == 0;   // warp 0 (group 0) and warp 4 (group 1)
@@ -829,7 +841,7 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                 }
                 long long t_start = 0, t_wait = 0;
                 if (dbg_on) t_start = clock64();
-                for (int c = X; c < nch; c += 2) {
+                for (int c = 0; c < nch; ++c) {
                     const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
                     long long tw0 = 0;
                     if (dbg_on) tw0 = clock64();
@@ -837,7 +849,7 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                     if (dbg_on) {
                         const long long tw1 = clock64();
                         t_wait += tw1 - tw0;
-                        if (c == X && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + X * 4 + 1] = tw1 - t_start;
+                        if (c == 0 && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + X * 4 + 1] = tw1 - t_start;
                     }
                     const double* sl = S.slot + (size_t)slot * S2_SLOT;
                     if (c == cgrab) {
@@ -854,14 +866,15 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                         }
                     }
                     const int ksteps = min(S2_KC4, G.nk4 - c * S2_KC4);
-                    if (fld == 0) s2_chunk<true>(sl, ksteps, ro, co, fld, a1, a2, aL);
-                    else s2_chunk<false>(sl, ksteps, ro, co, fld, a1, a2, aL);
-                    if (c != clast_own) {
+                    const int kend = ksteps < X + 1 ? ksteps : X + 1;
+                    if (fld == 0) s2_chunk<true>(sl, X, kend, ro, co, fld, a1, a2, aL);
+                    else s2_chunk<false>(sl, X, kend, ro, co, fld, a1, a2, aL);
+                    if (c < nch - 2) {
                         __syncwarp();
                         if (lane == 0) mbar_arrive(S.empty + slot);
                     }
                 }
-                const unsigned slot_own = (gcb + clast_own) % S2_SLOTS, slot_other = (gcb + clast_other) % S2_SLOTS;
+                const unsigned slot_own = (gcb + nch - 2 + X) % S2_SLOTS, slot_other = (gcb + nch - 1 - X) % S2_SLOTS;
                 gcb += nch;
                 long long t_loop = 0;
                 if (dbg_on) t_loop = clock64();
@@ -873,7 +886,10 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                     if (S.step[1] == 0.0) {
                         // the cavity went inactive with the previous step: this stage was speculative
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(S.empty + slot_own);
+                        if (lane == 0) {
+                            mbar_arrive(S.empty + slot_own);
+                            mbar_arrive(S.empty + slot_other);
+                        }
                         aborted = true;
                         break;
                     }
@@ -882,11 +898,11 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                 double* exch_own = S.slot + (size_t)slot_own * S2_SLOT;
                 const double* exch_other = S.slot + (size_t)slot_other * S2_SLOT;
                 if (X == 0)
-                    s2_finish<0>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
+                    s2_finish<0>(P, V, exch_own, exch_other, S.empty + slot_own, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
                                  G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL,
                                  (dbg_on && dbg_stage < S2_DBG_STAGES) ? tfin : nullptr);
                 else
-                    s2_finish<1>(P, V, exch_own, exch_other, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
+                    s2_finish<1>(P, V, exch_own, exch_other, S.empty + slot_own, S.empty + slot_other, S.uv, S.phin, S.vec, S.edgep, S.x, S.red, recN, recO,
                                  G.tile, b, G.r0, G.c0, stage, bc_lines, dt, fld, tw, lane, a1, a2, aL, nullptr);
                 bc_lines = true;
                 long long t_fin = 0;
@@ -932,13 +948,14 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
     unsigned gcb = 0;        // chunks issued before the current stage (ring position)
     unsigned nbar = 0;       // team barriers completed before the current stage
     unsigned nstepinfo = 0;  // step-info hand-overs seen so far (helpers)
+    unsigned nteam = 0;      // team-barrier hand-overs seen so far (helpers)
     unsigned visit = 0;
     const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && lane == 0 && leader;
     int dbg_stage = 0;
     const unsigned slot0 = s2_smem(S.slot), full0 = s2_smem(S.full), empty0 = s2_smem(S.empty);
-    // this warp's side of chunk c of a record: c chunk-strides after the tile's first k4-step (s2_off)
-    const size_t off_side = side == 0 ? (size_t)G.trow * (S2_NK4 * S2_NB * 64) : S2_SIDE + (size_t)G.tcol * (S2_NK4 * S2_NB * 64);
-    const unsigned sl_side = (side == 0 ? S2_SL_A : S2_SL_B) * 8;
+    // side s of chunk c of a record: c chunk-strides after the tile's first k4-step (s2_off)
+    const size_t offA = (size_t)G.trow * (S2_NK4 * S2_NB * 64), offB = S2_SIDE + (size_t)G.tcol * (S2_NK4 * S2_NB * 64);
+    const unsigned teambar = s2_smem(S.teambar);
 
     for (;;) {
         // ---- the team's next cavity ----
@@ -1005,49 +1022,53 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
         };
         auto wait_team = [&]() {
             const unsigned target = nbar * (unsigned)team_size;
-            while ((int)(ld_acquire_u32(P.team_bar + G.team) - target) < 0) {}
+            // relaxed polls (an acquire load invalidates L1 on every turn), one acquire fence once the count is there
+            while ((int)(ld_relaxed_u32(P.team_bar + G.team) - target) < 0) {}
+            fence_acq_rel_gpu();
         };
 
         for (long long step = 0; step < nsteps && active; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
                 // the stage input: its pressure blocks are p^n in every stage when the pressure is frozen (s2_finish)
-                const double* src = rec0 + (size_t)st_in(cur, stage) * P.buf_stride + off_side;
+                const double* rec_in = rec0 + (size_t)st_in(cur, stage) * P.buf_stride;
                 const bool need_bar = !(step == 0 && stage == 0);
+                // In a stage that starts with the previous step's reduction the leader warp only reduces: warp 9 then
+                // issues both sides of the even chunks.
                 const bool reduce_now = stage == 0 && step > 0;
+                const int s_lo = (reduce_now && pw == 1) ? 0 : side, s_hi = (reduce_now && pw == 1) ? 2 : side + 1;
                 if (lane == 0) {
                     long long tp0 = 0, tp1 = 0;
                     if (dbg_on) tp0 = clock64();
                     if (need_bar) {
-                        wait_team();
+                        // the leader polls the team's counter in global memory and passes the news on in shared memory
+                        if (leader) {
+                            wait_team();
+                            mbar_arrive(S.teambar);
+                        } else {
+                            mbar_wait_a(teambar, nteam & 1);
+                            ++nteam;
+                        }
                         fence_proxy_async();
                     }
                     if (dbg_on) tp1 = clock64();
-                    int c = cpar;
-                    // the chunks whose slots are free at the start of a stage first; the leader then reduces
-                    for (; c < nch && c < S2_SLOTS; c += 2) {
-                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
-                        mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
-                        mbar_expect_tx_a(fb, S2_SIDE_BYTES);
-                        bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + sl_side, src + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
-                    }
-                    if (dbg_on && dbg_stage < S2_DBG_STAGES) {
-                        // [10] start of the wait (absolute), [11] wait at the team barrier, [12] issue of the first chunks
-                        P.dbg[dbg_stage * 16 + 10] = tp0;
-                        P.dbg[dbg_stage * 16 + 11] = tp1 - tp0;
-                        P.dbg[dbg_stage * 16 + 12] = clock64() - tp1;
+                    if (!(reduce_now && leader)) {
+                        for (int c = cpar; c < nch; c += 2) {
+                            const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
+                            mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                            for (int sd = s_lo; sd < s_hi; ++sd) {
+                                mbar_expect_tx_a(fb, S2_SIDE_BYTES);
+                                bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + (sd ? S2_SL_B : S2_SL_A) * 8,
+                                           rec_in + (sd ? offB : offA) + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
+                            }
+                            if (dbg_on && c == cpar && dbg_stage < S2_DBG_STAGES) {
+                                // [10] start of the wait (absolute), [11] wait at the team barrier, [12] first chunk issued
+                                P.dbg[dbg_stage * 16 + 10] = tp0;
+                                P.dbg[dbg_stage * 16 + 11] = tp1 - tp0;
+                                P.dbg[dbg_stage * 16 + 12] = clock64() - tp1;
+                            }
+                        }
                     }
                     ++dbg_stage;
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    int c = cpar;
-                    while (c < nch && c < S2_SLOTS) c += 2;
-                    for (; c < nch; c += 2) {
-                        const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
-                        mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
-                        mbar_expect_tx_a(fb, S2_SIDE_BYTES);
-                        bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + sl_side, src + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
-                    }
                 }
                 __syncwarp();
                 gcb += nch;
@@ -1125,9 +1146,10 @@ __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) 
     if (tid == 0) {
         for (int s = 0; s < S2_SLOTS; ++s) {
             mbar_init(S.full + s, 2);   // one arrival (with its byte count) per side
-            mbar_init(S.empty + s, 4);
+            mbar_init(S.empty + s, 8);   // the eight consumer warps
         }
         mbar_init(S.stepbar, 1);
+        mbar_init(S.teambar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int e = tid; e < 8 * S2_HP; e += S2_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);

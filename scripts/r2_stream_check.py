@@ -53,6 +53,7 @@ if what in ("parity", "all"):
             for a, o in zip((res["stream_tma"][0][b], res["stream_tma"][1][b], res["stream_tma"][2][b]), (uo, vo, po)):
                 worst = max(worst, rel(a, o))
         vs_old = max(rel(a, o) for a, o in zip(res["stream_tma"], res["stream_eo"]))
+        assert vs_old < 1e-11
         out[f"parity_N{N}_B{B}_K{K}_fz{int(freeze)}"] = dict(vs_oracle=worst, vs_stream_eo=vs_old, kernel=kn)
         print(N, B, K, freeze, "vs oracle", worst, "vs stream_eo", vs_old, kn, flush=True)
         assert worst < 1e-10, "parity"
