@@ -15,6 +15,7 @@
 #include "stream_tma.cuh"
 #include "tiled.cuh"
 #include "validate.cuh"
+#include "vortex.cuh"
 #include "history_fused.cuh"
 
 namespace ldc {
@@ -1211,6 +1212,69 @@ int ldc_diagnostics(ldc_t* h, const double* W, double* out) {
         cudaStreamSynchronize(h->stream);
         cudaFree(tmpW);
     }
+    return rc;
+}
+
+int ldc_vortex_metrics(ldc_t* h, const double* Vai, const double* VbiT, const double* Va, const double* VbT,
+                       const double* inv_lam, const double* x, const double* y, double* out, double* psi) {
+    int rc = check_ready(h, "ldc_vortex_metrics");
+    if (rc) return rc;
+    if (!Vai || !VbiT || !Va || !VbT || !inv_lam || !x || !y || !out) return fail(LDC_ERR_INVALID, "ldc_vortex_metrics: null argument");
+    LDC_CUDA(cudaSetDevice(h->device));
+    if ((rc = ensure_canonical(h))) return rc;
+    const int n1x = h->n1x, n1y = h->n1y, mx = h->mx, my = h->my, B = h->B;
+    const size_t nf = (size_t)n1x * n1y, mm = (size_t)mx * my;
+    // shared inputs: Vai Va (mx x mx) | VbiT VbT (my x my) | inv_lam A BT | x y | out
+    double* M = nullptr;
+    const size_t nM = 2 * (size_t)mx * mx + 2 * (size_t)my * my + mm + (size_t)mx * mx + (size_t)my * my + n1x + n1y + (size_t)B * VM_OUT;
+    LDC_CUDA(cudaMalloc((void**)&M, nM * sizeof(double)));
+    double *dVai = M, *dVa = dVai + (size_t)mx * mx, *dVbiT = dVa + (size_t)mx * mx, *dVbT = dVbiT + (size_t)my * my,
+           *dInv = dVbT + (size_t)my * my, *dA = dInv + mm, *dBT = dA + (size_t)mx * mx, *dx = dBT + (size_t)my * my, *dy = dx + n1x,
+           *dOut = dy + n1y;
+    rc = copy_in(h, dVai, Vai, (size_t)mx * mx);
+    if (!rc) rc = copy_in(h, dVa, Va, (size_t)mx * mx);
+    if (!rc) rc = copy_in(h, dVbiT, VbiT, (size_t)my * my);
+    if (!rc) rc = copy_in(h, dVbT, VbT, (size_t)my * my);
+    if (!rc) rc = copy_in(h, dInv, inv_lam, mm);
+    if (!rc) rc = copy_in(h, dx, x, n1x);
+    if (!rc) rc = copy_in(h, dy, y, n1y);
+    if (rc) { cudaFree(M); return rc; }
+    // A = Dxx[1:-1,1:-1] (left operand), BT = Dyy[1:-1,1:-1]^T = DyyT[1:-1,1:-1] (right operand of psi B^T)
+    LDC_CUDA(cudaMemcpy2DAsync(dA, mx * sizeof(double), h->Dxx + n1x + 1, n1x * sizeof(double), mx * sizeof(double), mx,
+                               cudaMemcpyDeviceToDevice, h->stream));
+    LDC_CUDA(cudaMemcpy2DAsync(dBT, my * sizeof(double), h->DyyT + n1y + 1, n1y * sizeof(double), my * sizeof(double), my,
+                               cudaMemcpyDeviceToDevice, h->stream));
+    // scratch of the tiled path, free outside a step: omega -> pfull, F -> Ru, T -> Rv, G / corrections -> u0, psi_int -> v0,
+    // A psi -> Rp, psi B^T -> ptmp, R -> p0; psi on all nodes goes to Ru once F is no longer needed
+    double *om = h->pfull, *F = h->Ru, *T = h->Rv, *G = h->u0, *P0 = h->v0, *AP = h->Rp, *PB = h->ptmp, *R = h->p0;
+    const int TB = 256;
+    const dim3 gm((unsigned)((mm + TB - 1) / TB), B), gf((unsigned)((nf + TB - 1) / TB), B);
+    auto solve = [&](const double* rhs, double* dst) {   // dst = Va ((Vai rhs VbiT) * inv) VbT
+        k_left_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(dVai, rhs, T, mx, mx, my, nullptr);
+        k_right_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(T, dVbiT, dst, mx, my, my, nullptr);
+        k_vm_scale<<<gm, TB, 0, h->stream>>>(dst, dInv, (int)mm);
+        k_left_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(dVa, dst, T, mx, mx, my, nullptr);
+        k_right_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(T, dVbT, dst, mx, my, my, nullptr);
+        h->launches += 5;
+    };
+    k_vorticity<<<grid2d(n1x, n1y, B), kBlock2d, 0, h->stream>>>(h->u, h->v, h->Dx, h->DyT, om, n1x, n1y);
+    k_vm_interior_neg<<<gm, TB, 0, h->stream>>>(om, F, n1x, n1y);
+    solve(F, P0);
+    // one step of iterative refinement against the (non-normal) interior operator: R = F - (A psi + psi B^T)
+    k_left_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(dA, P0, AP, mx, mx, my, nullptr);
+    k_right_mul<<<grid2d(mx, my, B), kBlock2d, 0, h->stream>>>(P0, dBT, PB, mx, my, my, nullptr);
+    k_vm_residual<<<gm, TB, 0, h->stream>>>(F, AP, PB, R, (int)mm);
+    solve(R, G);
+    double* psi_full = h->Ru;   // F is dead
+    k_vm_embed<<<gf, TB, 0, h->stream>>>(P0, G, psi_full, n1x, n1y);
+    k_vm_scan<<<B, VM_THREADS, 0, h->stream>>>(psi_full, om, dx, dy, n1x, n1y, dOut);
+    h->launches += 7;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) rc = copy_out(h, out, dOut, (size_t)B * VM_OUT * sizeof(double));
+    if (e == cudaSuccess && !rc && psi) rc = copy_out(h, psi, psi_full, (size_t)B * nf * sizeof(double));
+    cudaStreamSynchronize(h->stream);
+    cudaFree(M);
+    if (e != cudaSuccess) return fail(LDC_ERR_CUDA, std::string("ldc_vortex_metrics: ") + cudaGetErrorString(e));
     return rc;
 }
 

@@ -42,6 +42,7 @@ SIGNATURES = {
     "ldc_solve_sampled": (C.c_int, [_vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int, _vp, C.c_int64, _vp, _vp, _vp, _vp, _vp,
                                     _vp]),
     "ldc_diagnostics": (C.c_int, [_vp, _vp, _vp]),
+    "ldc_vortex_metrics": (C.c_int, [_vp] + [_vp] * 9),
     "ldc_validation_errors": (C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ldc_prolongate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "ldc_restrict": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),

@@ -392,6 +392,15 @@ class BatchedSpectralLDC:
         _lib.check(self.lib.ldc_diagnostics(self._h, _lib.ptr(W), _lib.ptr(out)), "ldc_diagnostics")
         return out
 
+    def vortex_metrics(self, operands, want_psi: bool = False):
+        """[B, 19] vortex metrics (order: `postprocess.VORTEX_KEYS`) of the state on the device, psi [B, n, n] if asked;
+        `operands` = `postprocess.diagonalisation_operands(level)`."""
+        out = np.empty((self.B, 19))
+        psi = np.empty(self.shape_full) if want_psi else None
+        _lib.check(self.lib.ldc_vortex_metrics(self._h, *[_lib.ptr(a) for a in operands], _lib.ptr(out), _lib.ptr(psi)),
+                   "ldc_vortex_metrics")
+        return out, psi
+
     def validation_errors(self, plan, ref_u, ref_v):
         """[B,3] = (u_L2_error, v_L2_error, n_valid) against a stored solution at scattered points
         (compute_validation_errors, base.py:970-1054); `plan` is a `validation.BilinearPlan` for this grid."""

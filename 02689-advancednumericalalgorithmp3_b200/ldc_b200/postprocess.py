@@ -33,6 +33,28 @@ def _diagonalisation(nx: int, ny: int, Lx: float, Ly: float, basis: str):
     return la, Va, Vai, lb, Vb, Vbi
 
 
+VORTEX_KEYS = ("psi_min", "psi_min_x", "psi_min_y", "omega_center", "omega_max", "omega_max_x", "omega_max_y",
+               "psi_BR", "omega_BR", "psi_BR_x", "psi_BR_y", "psi_BL", "omega_BL", "psi_BL_x", "psi_BL_y",
+               "psi_TL", "omega_TL", "psi_TL_x", "psi_TL_y")
+
+
+def diagonalisation_operands(level):
+    """The shared operands of `ldc_vortex_metrics` for this level: (Vai, VbiT, Va, VbT, inv_lam, x, y), C-contiguous."""
+    la, Va, Vai, lb, Vb, Vbi = _diagonalisation(level.nx, level.ny, level.Lx, level.Ly, level.basis)
+    c = np.ascontiguousarray
+    return (c(Vai), c(Vbi.T), c(Va), c(Vb.T), c(1.0 / (la[:, None] + lb[None, :])), c(level.x, dtype=np.float64),
+            c(level.y, dtype=np.float64))
+
+
+def vortex_metrics_device(batch, want_psi: bool = False):
+    """The 19 vortex entries of `Metrics` for EVERY cavity of a `BatchedSpectralLDC` handle, computed on the device from
+    the state it holds (`ldc_vortex_metrics`: batched fast-diagonalisation solve + one fixed-order scan per cavity).
+    Returns a list of dicts (and psi [B, n, n] when asked).  Same quantities as `streamfunction_vortex_metrics`."""
+    vals, psi = batch.vortex_metrics(diagonalisation_operands(batch.level), want_psi)
+    out = [{k: float(v) for k, v in zip(VORTEX_KEYS, row)} for row in vals]
+    return (out, psi) if want_psi else out
+
+
 def vorticity(level, u, v):
     """omega = dv/dx - du/dy on all nodes (spectral/sg.py:510-522); u, v are [..., n, n]."""
     return level.Dx @ v - u @ level.Dy.T

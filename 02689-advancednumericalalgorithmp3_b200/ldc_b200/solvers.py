@@ -149,8 +149,11 @@ class SGSolver:
         return self._batch().diagnostics()[0]
 
     def compute_vortex_metrics(self) -> dict:
-        """Streamfunction-based vortex metrics (sg.py:556-743) by tensor-product fast diagonalisation."""
-        return streamfunction_vortex_metrics(self.level, self.u_2d, self.v_2d)
+        """Streamfunction-based vortex metrics (sg.py:556-743) by tensor-product fast diagonalisation, on the device."""
+        from .postprocess import vortex_metrics_device
+
+        self._push_state()
+        return vortex_metrics_device(self._batch())[0]
 
     def compute_validation_errors(self, reference_dir: str = "data/validation/fv", save_plots: bool = True) -> dict:
         """L2 errors against the stored FV solutions (base.py:970-1054) -- PyVista-free: the .vts files are parsed by

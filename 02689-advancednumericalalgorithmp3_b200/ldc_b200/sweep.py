@@ -219,8 +219,6 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
     Returns one TrialResult per trial, in trial order, on every rank (the sharded solve all-gathers its results).
     `root` is the directory holding data/validation/...; `solve` overrides `sharded.solve_sweep` (tests)."""
     from .sharded import solve_sweep
-    from .postprocess import streamfunction_vortex_metrics
-    from . import operators as ops
 
     kws = [solver_kwargs(t) for t in trials]
     results = [None] * len(trials)
@@ -247,16 +245,14 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
         lo, hi = _my_block(r.bounds, len(idx))
         verr_loc = _group_validation_errors(N, k0, {k: v[lo:hi] for k, v in per.items()}, r.u[lo:hi], r.v[lo:hi], r.p[lo:hi],
                                             root, device) if hi > lo else []
-        lv = ops.build_level(N, N, k0["Lx"], k0["Ly"], str(k0["basis_type"]).lower())
-        vm_loc = []
-        for j in range(lo, hi):
-            vm = {}
-            if vortex_metrics and not r.diverged[j]:
-                try:
-                    vm = streamfunction_vortex_metrics(lv, r.u[j], r.v[j])
-                except Exception:   # base.py:156-160 swallows these too
-                    vm = {}
-            vm_loc.append({k: float(v) for k, v in vm.items()})
+        # streamfunction / vortex metrics of the whole block in one batched device call (`ldc_vortex_metrics`)
+        vm_loc = [{} for _ in range(lo, hi)]
+        if vortex_metrics and hi > lo:
+            try:
+                vm_all = _block_vortex_metrics(N, k0, r.u[lo:hi], r.v[lo:hi], device)
+                vm_loc = [{} if r.diverged[j] else vm_all[j - lo] for j in range(lo, hi)]
+            except Exception:   # base.py:156-160 swallows these too
+                pass
         verrs, vms = _gather_records(verr_loc, vm_loc, r.bounds, len(idx))
         for j, i in enumerate(idx):
             vm = vms[j]
@@ -268,6 +264,21 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
                                      objective_value(objective, verrs[j], m, params["Re"], root), gi,
                                      dict(diverged=bool(r.diverged[j]), batch=len(idx), batch_wall_s=wall))
     return results
+
+
+def _block_vortex_metrics(N, k0, u, v, device):
+    """Vortex metrics of a block of cavities [b, n, n] on the device: one handle for the block, one call."""
+    import torch
+
+    from .batched import BatchedSpectralLDC
+    from .postprocess import vortex_metrics_device
+
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    with BatchedSpectralLDC(N, N, len(u), k0["Lx"], k0["Ly"], str(k0["basis_type"]).lower(), device) as s:
+        s.set_cases(100.0)          # (the streamfunction does not depend on the physics; the ABI wants the cases set)
+        s.set_state(np.nan_to_num(u), np.nan_to_num(v), None)
+        return vortex_metrics_device(s)
 
 
 def _my_block(bounds, n):

@@ -150,6 +150,19 @@ int ldc_solve_sampled(ldc_t* h, const double* tol, int64_t max_iter, int warmup,
  * (spectral/sg.py:495-550); out is [batch][3]. */
 int ldc_diagnostics(ldc_t* h, const double* W, double* out);
 
+/* Streamfunction + vortex metrics of every cavity of the handle (SGSolver._compute_streamfunction / compute_vortex_metrics,
+ * spectral/sg.py:556-743; the reference assembles a sparse Kronecker Laplacian and calls SuperLU once per cavity).  Here the
+ * interior system A psi + psi B^T = -omega (A = Dxx[1:-1,1:-1], B = Dyy[1:-1,1:-1]) is solved for the whole batch by
+ * tensor-product fast diagonalisation with one step of iterative refinement; the caller supplies the eigen-decompositions
+ * A = Va diag(la) Va^-1, B = Vb diag(lb) Vb^-1 (mx = nx - 1, my = ny - 1; all matrices row-major):
+ *   Vai [mx][mx] = Va^-1, VbiT [my][my] = (Vb^-1)^T, Va [mx][mx], VbT [my][my] = Vb^T, inv_lam [mx][my] = 1 / (la_i + lb_j),
+ *   x [nx+1], y [ny+1] the collocation nodes.
+ * out [batch][19] = psi_min, psi_min_x, psi_min_y, omega_center, omega_max, omega_max_x, omega_max_y, then (psi, omega, x, y)
+ * of the BR, BL, TL corner vortices (zeros where the quadrant's maximum of psi is not positive) -- the vortex fields of
+ * `Metrics` (datastructures.py:73-95) in that order.  psi (optional) receives the streamfunction [batch][nx+1][ny+1]. */
+int ldc_vortex_metrics(ldc_t* h, const double* Vai, const double* VbiT, const double* Va, const double* VbT,
+                       const double* inv_lam, const double* x, const double* y, double* out, double* psi);
+
 /* compute_validation_errors (base.py:970-1054) for every cavity of the handle: u, v are evaluated at nq scattered points by
  * bilinear interpolation on the collocation grid (_evaluate_at_points base.py:1122-1160: SciPy RegularGridInterpolator,
  * method="linear") and compared with a stored solution (ref_u, ref_v) [nq]:

@@ -213,3 +213,31 @@ def test_mro_recipe_of_integration_md_against_the_reference_base(ldc):
     assert s.fields.u.shape == (17 * 17,) or s.fields.u.size == 17 * 17
     d = s.metrics.to_mlflow()
     assert "iterations" in d
+
+
+@pytest.mark.parametrize("tag,N", [("sg_Re100_N16", 16), ("fsg_Re100_N24", 24), ("fsg_Re100_N32", 32), ("fsg_Re1000_N30_cs015", 30),
+                                   ("fsg_Re400_N64", 64)])
+def test_vortex_metrics_on_the_device(ldc, golden, tag, N):
+    """streamfunction + vortex metrics for a whole batch on the device (`ldc_vortex_metrics`) against the
+    reference's sparse SuperLU values (spectral/sg.py:556-743; tests/golden/make_golden_vortex.py), at the tolerance the host
+    version meets, and against the host version itself."""
+    from ldc_b200 import operators as ops
+    from ldc_b200 import postprocess as pp
+
+    g, gv = golden.solves, golden.vortex
+    u, v = g[f"{tag}_u"], g[f"{tag}_v"]
+    with ldc.BatchedSpectralLDC(N, batch=3) as s:
+        s.set_cases(100.0)
+        s.set_state(np.stack([u, 2 * u, u[::-1] * 0 + u]), np.stack([v, 2 * v, v]), None)
+        vm, psi = pp.vortex_metrics_device(s, want_psi=True)
+    ref_psi = gv[f"{tag}_psi"]
+    assert rel(psi[0], ref_psi) < 1e-9 and rel(psi[1], 2 * ref_psi) < 1e-9
+    assert not psi[0][0].any() and not psi[0][:, -1].any()
+    for k, ref in zip(gv[f"{tag}_keys"], gv[f"{tag}_vals"]):
+        assert vm[0][str(k)] == pytest.approx(ref, rel=1e-8, abs=1e-12), k
+    host = pp.streamfunction_vortex_metrics(ops.build_level(N, N), u, v)
+    for k in pp.VORTEX_KEYS:
+        assert vm[0][k] == pytest.approx(host[k], rel=1e-9, abs=1e-13), k
+        assert vm[2][k] == vm[0][k]
+    # psi is linear in (u, v): the positions stay, the values double
+    assert vm[1]["psi_min"] == pytest.approx(2 * vm[0]["psi_min"], rel=1e-12) and vm[1]["psi_min_x"] == vm[0]["psi_min_x"]
