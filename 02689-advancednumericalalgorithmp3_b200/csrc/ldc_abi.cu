@@ -13,6 +13,7 @@
 #include "resident_main.cuh"
 #include "stream_eo.cuh"
 #include "stream_tma.cuh"
+#include "stream_tma_wide.cuh"
 #include "tiled.cuh"
 #include "validate.cuh"
 #include "vortex.cuh"
@@ -731,11 +732,21 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
     if (kernel == 5) {
         // persistent TMA-fed streamed path (stream_tma.cuh): teams of ntile^2 co-resident CTAs, one cooperative launch per
         // batch of steps
-        const int ntile = (eo_half(h->mx) + ST_T - 1) / ST_T, team_size = ntile * ntile;
-        const size_t smem = S2_SMEM_DOUBLES * sizeof(double);
-        LDC_CUDA(cudaFuncSetAttribute(k_stream_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int ntile = (eo_half(h->mx) + ST_T - 1) / ST_T;
+        // Tile shape: 16 x 16 per CTA (k_stream_tma: a cavity over ntile^2 SMs, lowest latency per step) for few cavities;
+        // 16 x 32 per CTA (k_stream_tma_wide: half the CTAs per cavity, the per-stage synchronisation paid once per twice
+        // the DMMA work) once the batch would queue up behind the larger teams.  LDC_STREAM_CW=1 / 2 forces a shape.
+        // (measured, B200: N = 128 B = 64 196 k -> 247 k steps/s; with an odd number of 16-wide tiles per block edge the wide
+        // tiles of the last column are half padding: N = 96 B = 64 399 k -> 384 k, so those grids keep the 16 x 16 shape)
+        bool wide = ntile % 2 == 0 && (long long)h->B * 10 >= 16LL * (h->num_sms / (ntile * ntile));
+        if (const char* e = getenv("LDC_STREAM_CW")) wide = atoi(e) == 2;
+        const int team_size = wide ? ntile * ((ntile + 1) / 2) : ntile * ntile;
+        const size_t smem = (wide ? S2W_SMEM_DOUBLES : S2_SMEM_DOUBLES) * sizeof(double);
+        const void* kfun = wide ? (const void*)k_stream_tma_wide : (const void*)k_stream_tma;
+        LDC_CUDA(cudaFuncSetAttribute(kfun, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
-        LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma, S2_THREADS, smem));
+        if (wide) LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma_wide, S2_THREADS, smem));
+        else LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma, S2_THREADS, smem));
         int teams = std::min(h->B, per_sm * h->num_sms / team_size);
         if (const char* e = getenv("LDC_STREAM_TEAMS")) teams = std::max(1, std::min(teams, atoi(e)));   // A / B measurements
         if (teams < 1) return fail(LDC_ERR_UNSUPPORTED, "streamed TMA path: a team of CTAs does not fit the device");
@@ -789,7 +800,7 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
             LDC_CUDA(cudaMemsetAsync(h->t_team, 0, 2 * (size_t)h->num_sms * sizeof(double), h->stream));
             void* args[] = {(void*)&P};
-            LDC_CUDA(cudaLaunchCooperativeKernel((const void*)k_stream_tma, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
+            LDC_CUDA(cudaLaunchCooperativeKernel(kfun, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
                                                  h->stream));
             h->launches += 2;
             if (dbg) {

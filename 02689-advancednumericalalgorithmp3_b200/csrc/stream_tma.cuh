@@ -305,16 +305,16 @@ __global__ void __launch_bounds__(256) k_s2_begin(const double* __restrict__ buf
 // Contractions of the warp's field for the k4-steps [kbeg, kend) of one chunk slot (cf. st_chunk / eo_field_pass).
 //   ro = (8 tw + g) * 4 + t : the thread's A-fragment offset inside a 16 x 4 block;  co = g * 4 + t : B-fragment offset
 template <bool P_LEFT>
-__device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int kbeg, int kend, int ro, int co, int fld,
+__device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff, int kbeg, int kend, int ro, int co, int fld,
                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int NT = 2;
     // every operand of a k4-step sits in one 18-block group of its side: [kk][blk][16][4]
     const double* sOa = sl + S2_SL_A + ro;
-    const double* sOb = sl + S2_SL_B + co;
+    const double* sOb = sl + boff + co;
     const double* sFa = sl + S2_SL_A + (S2_BU + 4 * fld) * 64 + ro;
-    const double* sFb = sl + S2_SL_B + (S2_BU + 4 * fld) * 64 + co;
+    const double* sFb = sl + boff + (S2_BU + 4 * fld) * 64 + co;
     const double* sPa = sl + S2_SL_A + S2_BP * 64 + ro;
-    const double* sPb = sl + S2_SL_B + S2_BP * 64 + co;
+    const double* sPb = sl + boff + S2_BP * 64 + co;
 #pragma unroll 1
     for (int kk = kbeg; kk < kend; ++kk) {
         double FA[4], FB[4][NT];
@@ -702,11 +702,12 @@ struct S2Smem {
 
 // CTA geometry inside its team
 struct S2Geo {
-    int ntile, team_size, team, tin, trow, tcol, tile, r0, c0, m, h, n1, nk4, nch;
-    __device__ explicit S2Geo(const S2Params& P) {
-        ntile = P.ntile; team_size = ntile * ntile;
+    int ntile, ntc, team_size, team, tin, trow, tcol, tile, r0, c0, m, h, n1, nk4, nch;
+    // cw = 16-column tiles per CTA: 1 (k_stream_tma) or 2 (k_stream_tma_wide); tcol = the CTA's first column tile
+    __device__ S2Geo(const S2Params& P, int cw) {
+        ntile = P.ntile; ntc = (ntile + cw - 1) / cw; team_size = ntile * ntc;
         team = blockIdx.x / team_size; tin = blockIdx.x % team_size;
-        trow = tin / ntile; tcol = tin % ntile; tile = trow * (S2_HP / 16) + tcol;
+        trow = tin / ntc; tcol = (tin % ntc) * cw; tile = trow * (S2_HP / 16) + tin % ntc;
         r0 = trow * 16; c0 = tcol * 16;
         m = P.m; h = eo_half(m); n1 = P.n1;
         nk4 = P.K4 / 4; nch = (nk4 + S2_KC4 - 1) / S2_KC4;
@@ -718,6 +719,76 @@ struct S2Geo {
 __device__ __forceinline__ void visit_sync() { asm volatile("bar.sync 2, 384;" ::: "memory"); }
 __device__ __forceinline__ void sums_arrive() { asm volatile("bar.arrive 3, 288;" ::: "memory"); }
 __device__ __forceinline__ void sums_wait() { asm volatile("bar.sync 3, 288;" ::: "memory"); }
+
+// Start of a visit (consumer warps): the boundary lines in parity form for the first stage, and the boundary-line parts
+// of the convergence sums into S.step for the producer warp's reductions.
+template <class SM>
+__device__ __forceinline__ void s2_visit_prepare(const S2Params& P, const SM& S, const S2Visit& V, const double* __restrict__ rec0,
+                                                 int cur, const double* __restrict__ ul, const double* __restrict__ vl, int m, int h,
+                                                 int n1) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+        const double* ed = rec0 + (size_t)cur * P.buf_stride + S2_EDGE_OFF;
+        for (int e = tid; e < 8 * S2_HP; e += S2_CONSUMERS) {
+            const int line = e / S2_HP, k = e % S2_HP;
+            double x = 0.0, y = 0.0;
+            if (k < h) {
+                if (V.first) {
+                    x = __ldcg(ed + line * S2_ME + k);
+                    y = __ldcg(ed + line * S2_ME + m - 1 - k);
+                } else if ((line & 3) == 3) {
+                    const double* lid = (line < 4 ? ul : vl) + 1;
+                    x = lid[k];
+                    y = lid[m - 1 - k];
+                }
+            }
+            S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
+            S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
+        }
+        // sums over the boundary lines of ||phi^{n+1} - phi^n||^2, ||phi^n||^2 and max |lid|: with the lines as stored
+        // (first step after a load) and with the boundary-condition lines (every later step)
+        double sf[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, bm[2] = {0, 0}, dummy[2] = {0, 0};
+        for (int e = tid; e < m; e += S2_CONSUMERS) {
+#pragma unroll
+            for (int f = 0; f < 2; ++f) {
+                const double lid = (f ? vl : ul)[e + 1];
+                const double* L = ed + f * 4 * S2_ME;
+                const double w = __ldcg(L + e), ea = __ldcg(L + S2_ME + e), so = __ldcg(L + 2 * S2_ME + e),
+                             no = __ldcg(L + 3 * S2_ME + e);
+                const double dn = lid - no;
+                sf[2 * f] += w * w + ea * ea + so * so + dn * dn;
+                sf[2 * f + 1] += w * w + ea * ea + so * so + no * no;
+                sb[2 * f + 1] += lid * lid;
+                bm[f] = nanmax(bm[f], fabs(lid));
+            }
+        }
+        if (tid == 0) {
+#pragma unroll
+            for (int f = 0; f < 2; ++f) {
+                const double* c = ed + 8 * S2_ME + 4 * f;   // c00 c0N cN0 cNN
+                const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
+                const double q0 = __ldcg(c), q1 = __ldcg(c + 1), q2 = __ldcg(c + 2), q3 = __ldcg(c + 3);
+                const double d1 = l0 - q1, d3 = lN - q3;
+                sf[2 * f] += q0 * q0 + d1 * d1 + q2 * q2 + d3 * d3;
+                sf[2 * f + 1] += q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3;
+                sb[2 * f + 1] += l0 * l0 + lN * lN;
+                bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
+            }
+        }
+        s2_consumer_reduce(sf, bm, S.red, warp, lane);
+        s2_consumer_reduce(sb, dummy, S.red, warp, lane);
+        if (tid == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                S.step[2 + q] = sf[q];
+                S.step[8 + q] = sb[q];
+            }
+            S.step[6] = bm[0];
+            S.step[7] = bm[1];
+        }
+        __threadfence_block();
+        sums_arrive();     // the producer warp reads them at its first reduction of the visit
+        consumer_sync();   // S.edgep complete
+}
 
 // ================================================ consumer warps ================================================
 __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem& S, const S2Geo& G) {
@@ -748,70 +819,7 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
         const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
         double* rec0 = P.rec + (size_t)b * S2_STRIDE;
 
-        // ---- boundary lines in parity form for the first stage; boundary-line parts of the convergence sums ----
-        {
-            const double* ed = rec0 + (size_t)cur * P.buf_stride + S2_EDGE_OFF;
-            for (int e = tid; e < 8 * S2_HP; e += S2_CONSUMERS) {
-                const int line = e / S2_HP, k = e % S2_HP;
-                double x = 0.0, y = 0.0;
-                if (k < h) {
-                    if (V.first) {
-                        x = __ldcg(ed + line * S2_ME + k);
-                        y = __ldcg(ed + line * S2_ME + m - 1 - k);
-                    } else if ((line & 3) == 3) {
-                        const double* lid = (line < 4 ? ul : vl) + 1;
-                        x = lid[k];
-                        y = lid[m - 1 - k];
-                    }
-                }
-                S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
-                S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
-            }
-            // sums over the boundary lines of ||phi^{n+1} - phi^n||^2, ||phi^n||^2 and max |lid|: with the lines as stored
-            // (first step after a load) and with the boundary-condition lines (every later step)
-            double sf[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, bm[2] = {0, 0}, dummy[2] = {0, 0};
-            for (int e = tid; e < m; e += S2_CONSUMERS) {
-#pragma unroll
-                for (int f = 0; f < 2; ++f) {
-                    const double lid = (f ? vl : ul)[e + 1];
-                    const double* L = ed + f * 4 * S2_ME;
-                    const double w = __ldcg(L + e), ea = __ldcg(L + S2_ME + e), so = __ldcg(L + 2 * S2_ME + e),
-                                 no = __ldcg(L + 3 * S2_ME + e);
-                    const double dn = lid - no;
-                    sf[2 * f] += w * w + ea * ea + so * so + dn * dn;
-                    sf[2 * f + 1] += w * w + ea * ea + so * so + no * no;
-                    sb[2 * f + 1] += lid * lid;
-                    bm[f] = nanmax(bm[f], fabs(lid));
-                }
-            }
-            if (tid == 0) {
-#pragma unroll
-                for (int f = 0; f < 2; ++f) {
-                    const double* c = ed + 8 * S2_ME + 4 * f;   // c00 c0N cN0 cNN
-                    const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
-                    const double q0 = __ldcg(c), q1 = __ldcg(c + 1), q2 = __ldcg(c + 2), q3 = __ldcg(c + 3);
-                    const double d1 = l0 - q1, d3 = lN - q3;
-                    sf[2 * f] += q0 * q0 + d1 * d1 + q2 * q2 + d3 * d3;
-                    sf[2 * f + 1] += q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3;
-                    sb[2 * f + 1] += l0 * l0 + lN * lN;
-                    bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
-                }
-            }
-            s2_consumer_reduce(sf, bm, S.red, warp, lane);
-            s2_consumer_reduce(sb, dummy, S.red, warp, lane);
-            if (tid == 0) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    S.step[2 + q] = sf[q];
-                    S.step[8 + q] = sb[q];
-                }
-                S.step[6] = bm[0];
-                S.step[7] = bm[1];
-            }
-            __threadfence_block();
-            sums_arrive();     // the producer warp reads them at its first reduction of the visit
-            consumer_sync();   // S.edgep complete
-        }
+        s2_visit_prepare(P, S, V, rec0, cur, ul, vl, m, h, n1);
         // dt of the first step of the visit from the status (spectral/sg.py:387-408)
         double dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
         bool bc_lines = !V.first;
@@ -867,8 +875,8 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                     }
                     const int ksteps = min(S2_KC4, G.nk4 - c * S2_KC4);
                     const int kend = ksteps < X + 1 ? ksteps : X + 1;
-                    if (fld == 0) s2_chunk<true>(sl, X, kend, ro, co, fld, a1, a2, aL);
-                    else s2_chunk<false>(sl, X, kend, ro, co, fld, a1, a2, aL);
+                    if (fld == 0) s2_chunk<true>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
+                    else s2_chunk<false>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
                     if (c < nch - 2) {
                         __syncwarp();
                         if (lane == 0) mbar_arrive(S.empty + slot);
@@ -940,10 +948,15 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
 // different warps proceed side by side (scripts/tma_bw.cu, profiles/r02_tma_bw.txt).  So the four warps of the producer
 // warpgroup each issue ONE side of every other chunk: warp 8 + pw issues side (pw & 1) of the chunks c = (pw >> 1) mod 2.
 // Warp 8 is also the team's link to the cavity queue and the reducer of the end-of-step sums.
-__device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem& S, const S2Geo& G, int pw) {
+// WIDE (k_stream_tma_wide: a chunk has three sides A, B0, B1): warps 8, 9, 10 issue one side of EVERY chunk each; warp 11
+// stands in for warp 8 on side A in the stages the leader spends reducing.
+template <bool WIDE, class SM>
+__device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S, const S2Geo& G, int pw) {
+    constexpr int SLOTS = WIDE ? 3 : S2_SLOTS;
+    constexpr unsigned SLOT_BYTES = (WIDE ? 3 : 2) * S2_SIDE_BYTES;
     const int lane = threadIdx.x & 31;
     const bool leader = pw == 0;
-    const int side = pw & 1, cpar = pw >> 1;
+    const int side = WIDE ? (pw == 3 ? 0 : pw) : (pw & 1), cpar = WIDE ? 0 : (pw >> 1), cstep = WIDE ? 1 : 2;
     const int m = G.m, n1 = G.n1, nch = G.nch, team_size = G.team_size;
     unsigned gcb = 0;        // chunks issued before the current stage (ring position)
     unsigned nbar = 0;       // team barriers completed before the current stage
@@ -955,6 +968,7 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
     const unsigned slot0 = s2_smem(S.slot), full0 = s2_smem(S.full), empty0 = s2_smem(S.empty);
     // side s of chunk c of a record: c chunk-strides after the tile's first k4-step (s2_off)
     const size_t offA = (size_t)G.trow * (S2_NK4 * S2_NB * 64), offB = S2_SIDE + (size_t)G.tcol * (S2_NK4 * S2_NB * 64);
+    const size_t offB1 = offB + (size_t)(S2_NK4 * S2_NB * 64);   // the second column tile (WIDE)
     const unsigned teambar = s2_smem(S.teambar);
 
     for (;;) {
@@ -998,7 +1012,7 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
                 sums_ready = true;
             }
             if (lane < team_size) {
-                const int tl = (lane / G.ntile) * (S2_HP / 16) + lane % G.ntile;
+                const int tl = (lane / G.ntc) * (S2_HP / 16) + lane % G.ntc;
                 const double* part = P.partials + ((size_t)b * ST_TILES + tl) * 8;
 #pragma unroll
                 for (int q = 0; q < 6; ++q) S.part[lane * 8 + q] = __ldcg(part + q);
@@ -1035,7 +1049,8 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
                 // In a stage that starts with the previous step's reduction the leader warp only reduces: warp 9 then
                 // issues both sides of the even chunks.
                 const bool reduce_now = stage == 0 && step > 0;
-                const int s_lo = (reduce_now && pw == 1) ? 0 : side, s_hi = (reduce_now && pw == 1) ? 2 : side + 1;
+                const int s_lo = (!WIDE && reduce_now && pw == 1) ? 0 : side, s_hi = (!WIDE && reduce_now && pw == 1) ? 2 : side + 1;
+                const bool idle = WIDE ? (pw == 3 ? !reduce_now : (reduce_now && leader)) : (reduce_now && leader);
                 if (lane == 0) {
                     long long tp0 = 0, tp1 = 0;
                     if (dbg_on) tp0 = clock64();
@@ -1051,14 +1066,15 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
                         fence_proxy_async();
                     }
                     if (dbg_on) tp1 = clock64();
-                    if (!(reduce_now && leader)) {
-                        for (int c = cpar; c < nch; c += 2) {
-                            const unsigned gc = gcb + c, slot = gc % S2_SLOTS, fb = full0 + 8 * slot;
-                            mbar_wait_a(empty0 + 8 * slot, ((gc / S2_SLOTS) & 1) ^ 1);
+                    if (!idle) {
+                        for (int c = cpar; c < nch; c += cstep) {
+                            const unsigned gc = gcb + c, slot = gc % SLOTS, fb = full0 + 8 * slot;
+                            mbar_wait_a(empty0 + 8 * slot, ((gc / SLOTS) & 1) ^ 1);
                             for (int sd = s_lo; sd < s_hi; ++sd) {
                                 mbar_expect_tx_a(fb, S2_SIDE_BYTES);
-                                bulk_g2s_a(slot0 + slot * S2_SLOT_BYTES + (sd ? S2_SL_B : S2_SL_A) * 8,
-                                           rec_in + (sd ? offB : offA) + (size_t)c * (S2_KC4 * S2_NB * 64), S2_SIDE_BYTES, fb);
+                                bulk_g2s_a(slot0 + slot * SLOT_BYTES + sd * S2_SIDE_BYTES,
+                                           rec_in + (sd == 0 ? offA : (sd == 1 ? offB : offB1)) + (size_t)c * (S2_KC4 * S2_NB * 64),
+                                           S2_SIDE_BYTES, fb);
                             }
                             if (dbg_on && c == cpar && dbg_stage < S2_DBG_STAGES) {
                                 // [10] start of the wait (absolute), [11] wait at the team barrier, [12] first chunk issued
@@ -1141,7 +1157,7 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const S2Smem
 __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) {
     extern __shared__ __align__(16) double smem[];
     const S2Smem S(smem);
-    const S2Geo G(P);
+    const S2Geo G(P, 1);
     const int tid = threadIdx.x, warp = tid >> 5;
     if (tid == 0) {
         for (int s = 0; s < S2_SLOTS; ++s) {
@@ -1156,7 +1172,7 @@ __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) 
     __syncthreads();
     if (warp >= 8) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-        s2_producer_main(P, S, G, warp - 8);
+        s2_producer_main<false>(P, S, G, warp - 8);
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
         s2_consumer_main(P, S, G);

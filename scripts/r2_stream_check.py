@@ -4,6 +4,7 @@ launch-per-stage streamed kernels (`stream_eo`), a to-tolerance solve, then timi
     python scripts/r2_stream_check.py [parity|time|all]
 """
 import json
+import os
 import sys
 import time
 
@@ -19,6 +20,8 @@ from oracle import ldc_oracle as orc
 
 what = sys.argv[1] if len(sys.argv) > 1 else "all"
 out = {}
+CW = os.environ.get("LDC_STREAM_CW", "auto")   # 1: 16 x 16 tiles (k_stream_tma), 2: 16 x 32 (k_stream_tma_wide)
+print("tile shape LDC_STREAM_CW =", CW, flush=True)
 
 
 def rel(a, o):
@@ -114,5 +117,5 @@ if what in ("time", "all"):
             out[f"{path}_N{N}_B{B}"] = dict(steps_per_s=rate, us_per_step=best * 1e3 / K, alg_tflops=rate * fstep(N) / 1e12,
                                             pipe_frac=rate * issued / 1e12 / peak, ms=ms)
             print(path, N, B, out[f"{path}_N{N}_B{B}"], flush=True)
-json.dump(out, open("gpurun_out/r2_stream_check.json", "w"), indent=1)
+json.dump(out, open(f"gpurun_out/r2_stream_check_cw{CW}.json", "w"), indent=1)
 print("OK")

@@ -241,3 +241,37 @@ def test_vortex_metrics_on_the_device(ldc, golden, tag, N):
         assert vm[2][k] == vm[0][k]
     # psi is linear in (u, v): the positions stay, the values double
     assert vm[1]["psi_min"] == pytest.approx(2 * vm[0]["psi_min"], rel=1e-12) and vm[1]["psi_min_x"] == vm[0]["psi_min_x"]
+
+
+@pytest.mark.parametrize("N,B", [(128, 2), (66, 3), (40, 41)])
+def test_wide_tile_shape_of_the_streamed_kernel(ldc, golden, monkeypatch, N, B):
+    """k_stream_tma_wide (16 x 32 tiles, LDC_STREAM_CW=2; AUTO takes it for large batches at N >= 98): against the tiled FMA
+    path from a BC-violating random state with both pressure semantics, bitwise reproducible, and -- B = 41 at N = 40: more
+    cavities than teams -- independent of the batch-mates while cavities migrate between teams."""
+    rng = np.random.default_rng(N)
+    u, v = 0.1 * rng.standard_normal((2, B, N + 1, N + 1))
+    p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
+    Re = np.linspace(300.0, 2000.0, B)
+    out = {}
+    for path, cw in (("tiled", None), ("stream_tma", "2"), ("stream_tma", "2"), ("stream_tma", "1")):
+        if cw:
+            monkeypatch.setenv("LDC_STREAM_CW", cw)
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            s.set_cases(Re, corner_smoothing=0.1).set_state(u, v, p)
+            s.step(2, freeze_pressure=(N % 4 == 0))
+            r = s.step(4 if B < 10 else 9, freeze_pressure=(N % 4 == 0))
+            res = (*s.get_state(), r)
+        key = path + (cw or "")
+        if key in out:
+            assert all(np.array_equal(a, c) for a, c in zip(out[key], res)), "not bitwise reproducible"
+        out[key] = res
+    for key in ("stream_tma2", "stream_tma1"):
+        for a, c in zip(out[key][:3], out["tiled"][:3]):
+            assert rel(a, c) < 1e-10, key
+        assert np.allclose(out[key][3], out["tiled"][3], rtol=1e-8), key
+
+
+def test_config5_on_the_wide_tiles(ldc, golden, monkeypatch):
+    """The config-5 pin (N = 128, Re = 5000, 200 steps from the prolongated state) on the 16 x 32 tile shape."""
+    monkeypatch.setenv("LDC_STREAM_CW", "2")
+    test_config5_n128_re5000_from_the_prolongated_state(ldc, golden, "stream_tma")
