@@ -9,7 +9,7 @@
 // the residual becomes two h x h ones per output block: half the DMMA work of the plain resident kernel
 //     (Dx F)_ab = D_{a,1-a} F_{1-a,b}       (F Dy^T)_ab = F_{a,1-b} D_{b,1-b}^T
 //     (Dxx F)_ab = DD_{aa} F_ab             (F Dyy^T)_ab = F_ab DD_{bb}^T
-// The host-side statement of the same algebra (pinned by tests/test_parity.py) is ldc_b200/parity.py.
+// The host-side statement of the same algebra (pinned by tests/test_parity.py) is tests/parity_model.py (test infrastructure, not shipped).
 #pragma once
 #include "resident.cuh"
 

@@ -182,6 +182,8 @@ class SGSolver:
         ref = pd.read_csv(reference_csv, comment="#").iloc[0].to_dict()
         rows = []
 
+        # Row format restated from the reference's own table builder (solvers/base.py:924-958): the column names, the
+        # number formats and the `reference and reference != 0` rule ARE the contract of `mlflow.log_table`'s consumers.
         def add_row(vortex, metric, computed, reference, fmt=".6f"):
             if reference and reference != 0:
                 error_pct = abs(abs(computed) - abs(reference)) / abs(reference) * 100

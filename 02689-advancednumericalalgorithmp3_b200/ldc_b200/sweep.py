@@ -260,8 +260,10 @@ def run_trials(trials, objective: str = "fv_l2_error", root: str = ".", device=N
                         final_residual=float(r.rel_residual[j]), wall_time_seconds=wall / len(idx),
                         **{k: float(v) for k, v in vm.items() if k in Metrics.__dataclass_fields__})
             params = {k: v for k, v in kws[i].items() if not k.startswith("_")}
-            results[i] = TrialResult(i, dict(trials[i]), params, m.to_mlflow(), verrs[j],
-                                     objective_value(objective, verrs[j], m, params["Re"], root), gi,
+            # a diverged trial has no solution: its objective is +inf (an optimiser must not mistake the error of an
+            # all-zero or non-finite field for a poor but valid one)
+            obj = float("inf") if r.diverged[j] else objective_value(objective, verrs[j], m, params["Re"], root)
+            results[i] = TrialResult(i, dict(trials[i]), params, m.to_mlflow(), verrs[j], obj, gi,
                                      dict(diverged=bool(r.diverged[j]), batch=len(idx), batch_wall_s=wall))
     return results
 

@@ -1,10 +1,10 @@
-"""Even-odd (parity) algebra of the `eo` kernel (ldc_b200/parity.py) against the oracle residual and the
+"""Even-odd (parity) algebra of the `eo` kernel (tests/parity_model.py) against the oracle residual and the
 reference-minted residual fixture: the formulation is pinned on the CPU before the CUDA kernel is trusted."""
 import numpy as np
 import pytest
 
 from ldc_b200 import operators as ops
-from ldc_b200 import parity as par
+import parity_model as par
 from oracle import ldc_oracle as orc
 
 rel = lambda a, b: np.linalg.norm(a - b) / np.linalg.norm(b)
