@@ -209,7 +209,8 @@ static int pick_kernel(const ldc_handle* h) {
     if (eo_split_ok(h) && h->HP <= 16 && h->B <= h->num_sms) return 4;   // measured: no gain at HP = 24
     // few cavities on the largest resident grids (50 <= N <= 65): four SMs per cavity on the streamed path beat one
     // (N = 64: 28.0 k against 16.7 k steps/s for one cavity, 822 k against 614 k for 37; 74 cavities: 1.02 M against 1.23 M)
-    if (stream_ok(h) && eo_half(h->mx) > 24 && eo_half(h->mx) <= 32 && 4LL * h->B <= h->num_sms) return stream_auto(h);
+    if (stream_ok(h) && eo_half(h->mx) > 24 && eo_half(h->mx) <= 32 &&
+        (stream_auto(h) == 5 ? 2LL : 4LL) * h->B <= h->num_sms) return stream_auto(h);
     if (eo_ok(h)) return 2;
     if (resident_ok(h)) return 1;
     return stream_ok(h) ? stream_auto(h) : 0;
@@ -717,8 +718,9 @@ static cudaError_t launch_chain(bool pdl, K kernel, dim3 grid, int threads, size
 // Shared driver of ldc_step / ldc_solve / ldc_solve_sampled: iterations [start, stop) of a solve whose limit is max_iter,
 // until every cavity is inactive.  start = 0 starts a solve (status reset); start > 0 continues from the status the
 // previous call left (every active cavity has taken exactly `start` iterations).
+// n_active: cavities known to be still iterating (a hand-over from another kernel in mid-solve), else -1 = the whole batch.
 static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long long stop, long long max_iter, int warmup,
-                     int freeze, int nan_exit) {
+                     int freeze, int nan_exit, int n_active = -1) {
     if (start == 0) {
         k_reset_status<<<(h->B + 127) / 128, 128, 0, h->stream>>>(h->status, h->B);
         h->launches += 1;
@@ -738,18 +740,28 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         // the DMMA work) once the batch would queue up behind the larger teams.  LDC_STREAM_CW=1 / 2 forces a shape.
         // (measured, B200: N = 128 B = 64 196 k -> 247 k steps/s; with an odd number of 16-wide tiles per block edge the wide
         // tiles of the last column are half padding: N = 96 B = 64 399 k -> 384 k, so those grids keep the 16 x 16 shape)
-        bool wide = ntile % 2 == 0 && (long long)h->B * 10 >= 16LL * (h->num_sms / (ntile * ntile));
-        if (const char* e = getenv("LDC_STREAM_CW")) wide = atoi(e) == 2;
-        const int team_size = wide ? ntile * ((ntile + 1) / 2) : ntile * ntile;
-        const size_t smem = (wide ? S2W_SMEM_DOUBLES : S2_SMEM_DOUBLES) * sizeof(double);
-        const void* kfun = wide ? (const void*)k_stream_tma_wide : (const void*)k_stream_tma;
-        LDC_CUDA(cudaFuncSetAttribute(kfun, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int per_sm = 0;
-        if (wide) LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma_wide, S2_THREADS, smem));
-        else LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma, S2_THREADS, smem));
-        int teams = std::min(h->B, per_sm * h->num_sms / team_size);
-        if (const char* e = getenv("LDC_STREAM_TEAMS")) teams = std::max(1, std::min(teams, atoi(e)));   // A / B measurements
-        if (teams < 1) return fail(LDC_ERR_UNSUPPORTED, "streamed TMA path: a team of CTAs does not fit the device");
+        // The shape is chosen per launch from the number of cavities still iterating (both shapes work on the same records).
+        bool wide = false;
+        int team_size = 0, teams = 0;
+        size_t smem = 0;
+        const void* kfun = nullptr;
+        auto pick_shape = [&](int nact) -> int {
+            wide = ntile % 2 == 0 && (long long)nact * 10 >= 16LL * (h->num_sms / (ntile * ntile));
+            if (const char* e = getenv("LDC_STREAM_CW")) wide = atoi(e) == 2;
+            team_size = wide ? ntile * ((ntile + 1) / 2) : ntile * ntile;
+            smem = (wide ? S2W_SMEM_DOUBLES : S2_SMEM_DOUBLES) * sizeof(double);
+            kfun = wide ? (const void*)k_stream_tma_wide : (const void*)k_stream_tma;
+            LDC_CUDA(cudaFuncSetAttribute(kfun, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            int per_sm = 0;
+            if (wide) LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma_wide, S2_THREADS, smem));
+            else LDC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_stream_tma, S2_THREADS, smem));
+            teams = std::min(nact, per_sm * h->num_sms / team_size);
+            if (const char* e = getenv("LDC_STREAM_TEAMS")) teams = std::max(1, std::min(teams, atoi(e)));   // A / B measurements
+            if (teams < 1) return fail(LDC_ERR_UNSUPPORTED, "streamed TMA path: a team of CTAs does not fit the device");
+            return LDC_OK;
+        };
+        int nact = (n_active > 0 && n_active <= h->B) ? n_active : h->B;
+        if ((rc = pick_shape(nact))) return rc;
         const size_t bs = (size_t)h->B * S2_STRIDE;
         if (!h->t_state) {
             if ((rc = dalloc(h, &h->t_state, 3 * bs))) return rc;
@@ -793,8 +805,8 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             // steps per queue visit: the whole launch when every cavity has a team, else ~32 visits per team so that the
             // tail of the launch (teams idling while the last visits finish) stays small
             P.chunk = L;
-            if (h->B > teams) {
-                const long long c = (L * h->B + 32LL * teams - 1) / (32LL * teams);
+            if (nact > teams) {
+                const long long c = (L * nact + 32LL * teams - 1) / (32LL * teams);
                 P.chunk = std::min(L, std::max(4LL, c));
             }
             k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
@@ -822,6 +834,10 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
                 if (na == 0) break;
+                if (na != nact) {
+                    nact = na;
+                    if ((rc = pick_shape(nact))) return rc;
+                }
             }
         }
         if (dbg) cudaFree(dbg);
@@ -905,6 +921,9 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         if ((rc = split ? eo_split_slots(h) : (eo ? eo_slots(h) : resident_slots(h)))) return rc;
         // steps per launch (the host looks at the active count between launches)
         const long long chunk = h->mx >= 49 ? 1024 : (h->mx >= 33 ? 2048 : (h->mx >= 17 ? 4096 : 16384));
+        const char* env_tail = getenv("LDC_TAIL_SWITCH");
+        const bool tail_switch = kernel == 2 && h->path == LDC_PATH_AUTO && h->HP == 32 && eo_half(h->mx) > 24 && stream_tma_ok(h) &&
+                                 !(env_tail && atoi(env_tail) == 0) && stream_auto(h) == 5;
         h->canon_valid = false;
         for (long long done = start; done < stop; done += chunk) {
             const long long L = std::min(chunk, stop - done);
@@ -921,6 +940,22 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
                 int na = 0;
                 if ((rc = count_active(h, &na))) return rc;
                 if (na == 0) break;
+                // The tail of a to-tolerance solve: once every cavity still iterating can have two (then four) SMs, the
+                // streamed kernel takes over -- a cavity's chain of dependent steps is what is left, and on the largest
+                // resident grids it runs 1.2 x (two SMs) to 1.9 x (four) faster there.  AUTO only (a forced path stays put,
+                // so that runs which must agree bit for bit can); LDC_TAIL_SWITCH=0 turns it off.
+                if (tail_switch && 2 * na <= h->num_sms) {
+                    LDC_CUDA(cudaEventRecord(h->ev1, h->stream));
+                    LDC_CUDA(cudaEventSynchronize(h->ev1));
+                    float ms1 = 0;
+                    LDC_CUDA(cudaEventElapsedTime(&ms1, h->ev0, h->ev1));
+                    const int saved = h->path;
+                    h->path = LDC_PATH_STREAM_TMA;
+                    rc = run_steps(h, tol_dev, done + L, stop, max_iter, warmup, freeze, nan_exit, na);
+                    h->path = saved;
+                    h->last_ms += ms1;
+                    return rc;
+                }
             }
         }
     } else {
