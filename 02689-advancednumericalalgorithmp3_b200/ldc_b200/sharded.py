@@ -97,6 +97,21 @@ def _gather_fields(tensors, counts, dst_all: bool):
     return out
 
 
+def warm_up_gather():
+    """Bring up NCCL's point-to-point connections to rank 0 (they are made lazily, ~0.1-0.2 s per peer, on the first
+    `dist.gather`): call once before a timed sweep so that the sweep's clock does not include communicator set-up."""
+    import torch
+
+    dist = _dist()
+    if dist is None or dist.get_world_size() == 1:
+        return
+    t = torch.zeros(8, dtype=torch.float64, device=_comm_device())
+    recv = [torch.empty_like(t) for _ in range(dist.get_world_size())] if dist.get_rank() == 0 else None
+    dist.gather(t, recv, dst=0)
+    if t.is_cuda:
+        torch.cuda.synchronize()
+
+
 def interleave_permutation(n_cases: int, world: int) -> np.ndarray:
     """Order in which the cavities are laid out before the contiguous split so that rank r gets cavities r, r + world,
     r + 2 world, ...: a sweep ordered by Re or corner_smoothing then hands every rank the same mix of short and long solves

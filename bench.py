@@ -467,7 +467,9 @@ def gpu_arm(args):
     # IN TOTAL, dealt round-robin over the ranks (strong scaling: the work is fixed as N grows) ----
     sweep = None
     if not args.no_sweep:
-        from ldc_b200.sharded import solve_sweep
+        from ldc_b200.sharded import solve_sweep, warm_up_gather
+
+        warm_up_gather()     # NCCL's lazy point-to-point set-up to rank 0 is not part of the sweep
 
         g = args.sweep_grid
         cs_g, re_g = np.meshgrid(np.linspace(0.02, 0.35, g), np.linspace(100.0, 1000.0, g), indexing="ij")
