@@ -5,18 +5,22 @@
 //   * ONE cooperative launch runs many RK4 steps: a team of (tiles per cavity) co-resident CTAs pops a cavity from the
 //     work queue, advances it `chunk` steps and hands it back.  The stages of a step are separated by a team barrier in
 //     global memory (release / acquire counter) instead of a kernel boundary, and the end-of-step reduction (convergence
-//     norms, next dt) is done redundantly, in fixed order, by the idle producer warp of every CTA of the team.
+//     norms, next dt) is done redundantly, in fixed order, by a producer warp of every CTA of the team.
 //   * operand panels arrive by TMA bulk copies (cp.async.bulk, SASS UBLKCP) with mbarrier completion into a ring of
-//     S2_SLOTS chunk slots: a producer warp issues, eight consumer warps wait on the slot's "full" barrier and hand the
-//     slot back through its "empty" barrier -- no CTA-wide barrier and no cp.async wait inside the K loop.
-//   * state and operators live in global memory in a k4-interleaved tile layout: for a 16-row tile and one k4-step (four
-//     consecutive k) the 16 x 4 doubles of a block are contiguous, [row][k % 4].  Every chunk panel is then ONE contiguous
-//     bulk copy, and a DMMA fragment load (lane (g, t) -> row g, k t) reads 256 contiguous bytes: conflict-free with no
-//     padding.  Every field is stored twice, row-type (A operands) and column-type (its transpose, B operands).
-//   * the two warp groups split K by chunk parity (even chunks: group 0, odd: group 1), swap half of their accumulators
-//     through the two last chunk slots, and EACH runs the epilogue of one 8-column half of the tile.
-//   * the stage input u, v at the thread's own elements are picked out of the row panels as they pass through shared
-//     memory (no global re-read); phi^n comes from the CTA's own earlier stores.
+//     S2_SLOTS chunk slots: four producer warps issue (one thread's copies are served one after the other, ~360 cycles
+//     each whatever their size, copies of different warps side by side: scripts/tma_bw.cu), eight consumer warps wait
+//     on the slot's "full" barrier and hand the slot back through its "empty" barrier -- no CTA-wide barrier and no
+//     cp.async wait inside the K loop.  setmaxnreg gives the consumers 224 registers and the producers 56.
+//   * state and operators live in global memory in a k4-interleaved tile layout: for a 16-line tile and one k4-step (four
+//     consecutive k) the 16 x 4 doubles of a block are contiguous, [line][k % 4], and the 18 blocks a side needs (six
+//     operator blocks, u, v, p) sit back to back.  A chunk is then ONE contiguous bulk copy per side, and a DMMA fragment
+//     load (lane (g, t) -> line g, k t) reads 256 contiguous bytes: conflict-free with no padding.  Every field is stored
+//     twice, row side (A operands) and column side (its transpose, B operands).
+//   * the two warp groups split K inside every chunk (k4-step 0: group 0, k4-step 1: group 1), swap half of their
+//     accumulators through the two last chunk slots, and EACH runs the epilogue of one 8-column half of the tile.
+//   * the stage input u, v at the thread's own elements -- at stage 0 also phi^n and p^n, kept for the four stages -- are
+//     picked out of the row panels as they pass through shared memory: the epilogue reads nothing from global memory.
+// The 16 x 32 shape for large batches is stream_tma_wide.cuh; measurements and the design history are in DESIGN.md 4.6.
 #pragma once
 #include "stream_eo.cuh"
 
@@ -1152,8 +1156,8 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S,
 }
 
 // The persistent kernel.  grid = teams x (tiles per cavity), cooperative launch (every CTA co-resident: the team barriers
-// and the queue spin).  384 threads: warps 0..7 consume (224 registers each after setmaxnreg), warp 8 produces and
-// reduces (56 registers), warps 9..11 exist only because setmaxnreg works on whole warpgroups and leave at once.
+// and the queue spin).  384 threads: warps 0..7 consume (224 registers each after setmaxnreg), warps 8..11 issue the bulk
+// copies (56 registers; setmaxnreg works on whole warpgroups), warp 8 also polls the team barrier and reduces.
 __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) {
     extern __shared__ __align__(16) double smem[];
     const S2Smem S(smem);
