@@ -105,3 +105,50 @@ def test_sweep_without_process_group_runs_locally():
     r = solve_sweep(6, Re, 0.15, 1e-6, 100, local_solver=_fake_solver)
     assert r.bounds == [(0, 3)] and list(r.iterations) == [1000, 4000, 9500] and list(r.diverged) == [False, False, True]
     assert r.u.shape == (3, 7, 7)
+
+
+def _gather_worker(rank, world, port, q):
+    """The device-side gather route of solve_sweep (`_gather_fields`, used with NCCL) on gloo / CPU tensors: padded blocks of
+    different sizes to rank 0 (`dist.gather`) and to every rank, the point-to-point warm-up, per-rank kernel times."""
+    import torch
+    import torch.distributed as dist
+
+    from ldc_b200.sharded import _gather_fields, solve_sweep, warm_up_gather
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        warm_up_gather()
+        counts = [3, 2]
+        pad = max(counts)
+        t = torch.zeros((pad, 4, 4), dtype=torch.float64)
+        t[:counts[rank]] = torch.arange(counts[rank] * 16, dtype=torch.float64).reshape(counts[rank], 4, 4) + 100 * rank
+        to0 = _gather_fields([t], counts, dst_all=False)[0]
+        toall = _gather_fields([t], counts, dst_all=True)[0]
+        r = solve_sweep(6, np.linspace(100, 800, 5), 0.1, 1e-6, 100, fields="none", local_solver=_fake_solver,
+                        per_rank_kernel_ms=True)
+        q.put((rank, None if to0 is None else to0.copy(), toall.copy(), r.per_rank_kernel_ms.copy(), r.u))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_route_and_per_rank_kernel_times_over_gloo():
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gather_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted((q.get(timeout=120) for _ in procs), key=lambda t: t[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    want = np.concatenate([np.arange(48.0).reshape(3, 4, 4), np.arange(32.0).reshape(2, 4, 4) + 100])
+    for rank, to0, toall, kms, u in got:
+        assert np.array_equal(toall, want)
+        assert (to0 is None) == (rank != 0) and (rank != 0 or np.array_equal(to0, want))
+        assert kms.tolist() == [3.0, 2.0] and u is None   # the stand-in reports its block size as kernel time
