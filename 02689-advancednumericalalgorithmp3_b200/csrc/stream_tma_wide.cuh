@@ -65,21 +65,18 @@ __device__ __forceinline__ void s2w_finish(const S2Params& P, const S2Visit& V, 
     const double adt = rk_alpha(stage) * dt;
     const bool last = (stage == 3);
     const double wi = (i == centre) ? 0.5 : 1.0;
-    // phi^n of the warp's field at the thread's elements (stage 0: it is the stage input, already in sUV)
-    double2 f0[4][2];
-    if (stage != 0) {
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-            const int j0 = c0w + 8 * nt + 2 * t;
-            const size_t offR = s2_off(rt, j0 >> 2, S2_BU + 4 * fld, ir, j0 & 3);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) f0[q][nt] = __ldcg(reinterpret_cast<const double2*>(recN + offR + q * 64));
-        }
-    }
     double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
         const int j0 = c0w + 8 * nt + 2 * t;
+        // phi^n of the warp's field at the thread's elements of this half (stage 0: it is the stage input, already in
+        // sUV): issued here, used after the assembly
+        double2 f0[4];
+        if (stage != 0) {
+            const size_t offR = s2_off(rt, j0 >> 2, S2_BU + 4 * fld, ir, j0 & 3);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) f0[q] = __ldcg(reinterpret_cast<const double2*>(recN + offR + q * 64));
+        }
         double uo[4][2], vo[4][2], b1[4][2], b2[4][2], bL[4][2];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -102,8 +99,8 @@ __device__ __forceinline__ void s2w_finish(const S2Params& P, const S2Visit& V, 
         double* outC = recO + S2_SIDE + s2_off(ct, i >> 2, S2_BU + 4 * fld, j0 & 15, i & 3);   // + q * 64; second column + 4
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double fx = stage == 0 ? (fld == 0 ? uo[q][0] : vo[q][0]) : f0[q][nt].x;
-            const double fy = stage == 0 ? (fld == 0 ? uo[q][1] : vo[q][1]) : f0[q][nt].y;
+            const double fx = stage == 0 ? (fld == 0 ? uo[q][0] : vo[q][0]) : f0[q].x;
+            const double fy = stage == 0 ? (fld == 0 ? uo[q][1] : vo[q][1]) : f0[q].y;
             fn[q][0] = fx + adt * bL[q][0];
             fn[q][1] = fy + adt * bL[q][1];
             if (last) {
