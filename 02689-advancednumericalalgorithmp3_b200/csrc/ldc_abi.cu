@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1463,3 +1464,54 @@ double ldc_last_kernel_ms(const ldc_t* h) { return h ? h->last_ms : 0.0; }
 int ldc_fp64_peak(int device, int which, double* tflops) { return measure_fp64_peak(device, which, tflops); }
 
 }  // extern "C"
+
+// ---- allocation-free diagnostics ------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that may not allocate device
+// memory (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two kernels as
+// ldc_diagnostics (k_vorticity, k_diagnostics); the vorticity field they hand over lives in the file-scope array below
+// instead of in a handle's buffers.  Every GPU that loads the library holds the array (4 MiB) until the process exits.
+constexpr size_t NOALLOC_MAX_DOUBLES = (size_t)LDC_NOALLOC_MAX_DOUBLES;
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_MAX_DOUBLES];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address is looked up once per device, with
+// that device current, and it is that address the kernels are given.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch(int device, double** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(LDC_ERR_INVALID, "ldc_diagnostics_noalloc: device index out of range");
+    LDC_CUDA(cudaSetDevice(device));
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        double* p = nullptr;
+        LDC_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) return fail(LDC_ERR_CUDA, "ldc_diagnostics_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return LDC_OK;
+}
+
+extern "C" int ldc_diagnostics_noalloc(int device, void* cuda_stream, int nx, int ny, int batch, const double* d_u,
+                                       const double* d_v, const double* d_Dx, const double* d_DyT, const double* d_W,
+                                       double* d_out) {
+    if (nx < 2 || ny < 2 || batch < 1) return fail(LDC_ERR_INVALID, "ldc_diagnostics_noalloc: nx, ny >= 2 and batch >= 1 required");
+    if (!d_u || !d_v || !d_Dx || !d_DyT || !d_W || !d_out) return fail(LDC_ERR_INVALID, "ldc_diagnostics_noalloc: null argument");
+    const size_t n1x = (size_t)nx + 1, n1y = (size_t)ny + 1, need = (size_t)batch * n1x * n1y;
+    if (batch > 65535 || need > NOALLOC_MAX_DOUBLES)
+        return fail(LDC_ERR_INVALID, "ldc_diagnostics_noalloc: batch * (nx+1) * (ny+1) = " + std::to_string(need) +
+                                         " doubles exceeds the static scratch of " + std::to_string(NOALLOC_MAX_DOUBLES) +
+                                         " (LDC_NOALLOC_MAX_DOUBLES); use ldc_diagnostics, which allocates");
+    double* om = nullptr;
+    int rc = noalloc_scratch(device, &om);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // The array keeps the previous call's vorticity.  k_vorticity writes every element that k_diagnostics reads, so nothing
+    // here depends on a zero start; the part in use is cleared all the same, so that a stale value cannot be read by accident.
+    LDC_CUDA(cudaMemsetAsync(om, 0, need * sizeof(double), st));
+    k_vorticity<<<grid2d((int)n1x, (int)n1y, batch), kBlock2d, 0, st>>>(d_u, d_v, d_Dx, d_DyT, om, (int)n1x, (int)n1y);
+    k_diagnostics<<<batch, RED_THREADS, 0, st>>>(d_u, d_v, om, d_Dx, d_DyT, d_W, d_out, (int)n1x, (int)n1y);
+    LDC_CUDA(cudaGetLastError());
+    return LDC_OK;
+}

@@ -49,6 +49,7 @@ SIGNATURES = {
     "ldc_launch_count": (C.c_int64, [_vp]),
     "ldc_last_kernel_ms": (C.c_double, [_vp]),
     "ldc_fp64_peak": (C.c_int, [C.c_int, C.c_int, _dp]),
+    "ldc_diagnostics_noalloc": (C.c_int, [C.c_int, _vp, C.c_int, C.c_int, C.c_int] + [_vp] * 6),
 }
 
 _lib = None

@@ -195,6 +195,22 @@ double ldc_last_kernel_ms(const ldc_t* h);
  * DMMA (mma.sync m8n8k4 f64), 1 register-resident DFMA, 2 both pipes mixed.  TFLOP/s in *tflops. */
 int ldc_fp64_peak(int device, int which, double* tflops);
 
+/* Allocation-free variant of ldc_diagnostics.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It needs no handle and calls no cudaMalloc / cudaFree or allocating library routine: the vorticity field the two kernels
+ * hand over lives in a file-scope static __device__ array of LDC_NOALLOC_MAX_DOUBLES doubles (4 MiB), which every GPU that
+ * loads the library holds until the process exits.  All pointers are DEVICE pointers on `device`, row-major:
+ *   d_u, d_v [batch][nx+1][ny+1]; d_Dx [nx+1][nx+1]; d_DyT [ny+1][ny+1] = Dy^T; d_W [nx+1][ny+1] quadrature weights;
+ *   d_out [batch][3] = energy, enstrophy, palinstrophy (as ldc_diagnostics).
+ * The launches go to `cuda_stream` (NULL: the default stream) and the call returns without synchronising.
+ * batch * (nx+1) * (ny+1) > LDC_NOALLOC_MAX_DOUBLES (or batch > 65535) is refused with LDC_ERR_INVALID.
+ * All calls share the one array per GPU, which keeps the last call's contents (the part in use is cleared first): two calls
+ * that overlap on the same GPU (different streams or threads) RACE -- keep them on one stream or order them with events.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress) and should be made outside a capture. */
+#define LDC_NOALLOC_MAX_DOUBLES 524288
+int ldc_diagnostics_noalloc(int device, void* cuda_stream, int nx, int ny, int batch, const double* d_u, const double* d_v,
+                            const double* d_Dx, const double* d_DyT, const double* d_W, double* d_out);
+
 #ifdef __cplusplus
 }
 #endif
