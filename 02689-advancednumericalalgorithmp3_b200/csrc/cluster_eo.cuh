@@ -1,0 +1,603 @@
+// Cluster-resident even-odd path for few cavities on the largest resident grids (50 <= N <= 65, parity blocks of 32 x 32).
+//
+// A cavity is spread over a thread-block CLUSTER of 8 CTAs (4 row tiles x 2 column tiles; a CTA owns an 8 x 16 tile of all
+// four parity blocks of u, v and p).  Nothing of the stepping path goes through global memory:
+//   * every CTA keeps the operand panels of its tile in its own shared memory for the whole visit -- the row panel
+//     (operator rows and state rows of its 8 lines, all k) and the column panel (its 16 columns, all k), in the
+//     k4-interleaved block layout of stream_tma.cuh, so that the DMMA fragment loads are the same conflict-free 256-byte reads;
+//   * the output of an RK stage is written straight into the panels of the CTAs that need it -- the row panels of the two
+//     CTAs of the tile's row, the column panels of the four CTAs of its column -- with st.shared::cluster (distributed
+//     shared memory), and the stages are separated by the hardware cluster barrier (barrier.cluster arrive / wait,
+//     ~620 cycles: scripts/dsmem_bw.cu) instead of a counter in global memory plus a round of bulk copies out of L2;
+//   * the end-of-step sums (convergence norms, maxima for the next dt) are exchanged the same way and reduced redundantly,
+//     in fixed order, by every CTA; status and state go back to the record in L2 only at the end of a visit.
+// What bounds it: the SM-to-SM network takes ~20 B/clk out of an SM (scripts/dsmem_bw.cu, profiles/r02_dsmem_bw.txt), and
+// a stage sends 48 KB per CTA; the K loop of a stage is 160 DMMAs per warp, one warp per SM sub-partition.
+// Four warps per CTA: (k-group X: even | odd k4-steps) x (u | v equation), each over the whole 8 x 16 tile; the groups swap
+// accumulator halves and each runs the epilogue of one 8-column half (as k_stream_tma does).
+// Records, pack / unpack kernels, queue and host-side driver are those of stream_tma.cuh (ldc_abi.cu picks this kernel as a
+// third "shape" of the persistent streamed path when every cavity still iterating can have a cluster).
+#pragma once
+#include "stream_tma.cuh"
+
+namespace ldc {
+
+constexpr int CE_NK4 = 8;                        // k4-steps of a 32-wide parity block
+constexpr int CE_TR = 8, CE_TC = 16;             // tile of a CTA: rows x columns
+constexpr int CE_CR = 32 / CE_TR, CE_CC = 32 / CE_TC;
+constexpr int CE_CLUSTER = CE_CR * CE_CC;        // 8 CTAs per cavity; rank = row tile * CE_CC + column tile
+constexpr int CE_THREADS = 128;
+constexpr int CE_ABLK = CE_TR * 4, CE_BBLK = CE_TC * 4;      // doubles per block of the row / column panel
+constexpr int CE_RP = CE_NK4 * S2_NB * CE_ABLK;              // row panel    [kk][blk][8 r][4]
+constexpr int CE_CP = CE_NK4 * S2_NB * CE_BBLK;              // column panel [kk][blk][16 c][4]
+constexpr int CE_EXCH = 2 * 24 * 64;                         // accumulator swap: [group][24 values][64 threads]
+constexpr size_t CE_SMEM_DOUBLES = (size_t)CE_RP + CE_CP + CE_EXCH
+                                   + 8 * S2_HP + 16 * S2_HP  // boundary-column vectors, boundary lines in parity form
+                                   + 2 * 8 * 32              // dv/dy hand-over v warps -> u warps
+                                   + CE_CLUSTER * 8 + 64 + 16 + 2;   // partials of the 8 tiles, reduction scratch, step info, cavity
+
+struct CESmem {
+    double *rp, *cp, *exch, *vec, *edgep, *x, *part, *red, *step;
+    int* cavity;
+    __device__ explicit CESmem(double* smem) {
+        rp = smem;
+        cp = rp + CE_RP;
+        exch = cp + CE_CP;
+        vec = exch + CE_EXCH;
+        edgep = vec + 8 * S2_HP;
+        x = edgep + 16 * S2_HP;
+        part = x + 2 * 8 * 32;
+        red = part + CE_CLUSTER * 8;
+        step = red + 64;   // [2..5] boundary-line sums of a first step, [6..7] max |lid|, [8..11] sums of later steps
+        cavity = reinterpret_cast<int*>(step + 16);
+    }
+};
+
+// ---- cluster PTX ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned ce_rank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+// shared::cluster address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ unsigned ce_mapa(const void* p, unsigned rank) {
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(s2_smem(p)), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void ce_st(unsigned addr, double v) {
+    asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void ce_st2(unsigned addr, double v0, double v1) {
+    asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v0), "d"(v1) : "memory");
+}
+__device__ __forceinline__ void ce_st_s32(unsigned addr, int v) {
+    asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ce_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void ce_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+// ---- one k4-step of the warp's contractions (cf. s2_chunk) -------------------------------------------------------------
+//   A = row panel at this k4-step + the thread's A-fragment offset (g * 4 + t), block b at A + b * CE_ABLK
+//   Bp = column panel likewise,                                                  block b at Bp + b * CE_BBLK (+ 32: second half)
+template <bool P_LEFT>
+__device__ __forceinline__ void ce_kstep(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
+                                         double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    constexpr int NT = 2;
+    const int bf = S2_BU + 4 * fld;
+    double FA[4], FB[4][NT];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        FA[q] = A[(bf + q) * CE_ABLK];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) FB[q][nt] = Bp[(bf + q) * CE_BBLK + nt * 32];
+    }
+    {
+        double dA[2], ddA[2];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            dA[a] = A[a * CE_ABLK];
+            ddA[a] = A[(2 + a) * CE_ABLK];
+        }
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
+                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
+                }
+    }
+    {
+        double dB[2][NT], ddB[2][NT];
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                dB[b][nt] = Bp[b * CE_BBLK + nt * 32];
+                ddB[b][nt] = Bp[(2 + b) * CE_BBLK + nt * 32];
+            }
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
+                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
+                }
+    }
+    if (P_LEFT) {
+        double gA[2], PB[4][NT];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) gA[a] = A[(4 + a) * CE_ABLK];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) PB[q][nt] = Bp[(S2_BP + q) * CE_BBLK + nt * 32];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
+    } else {
+        double PA[4], gB[2][NT];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) PA[q] = A[(S2_BP + q) * CE_ABLK];
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) gB[b][nt] = Bp[(4 + b) * CE_BBLK + nt * 32];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], PA[2 * a + (1 - b)], gB[b][nt]);
+    }
+}
+
+// 4 sums + 2 NaN-propagating maxima across the four warps, fixed order, result in every thread.
+__device__ __forceinline__ void ce_block_reduce(double (&s)[4], double (&mx)[2], double* sRed, int warp, int lane) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s[q] += __shfl_xor_sync(0xffffffffu, s[q], o);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) mx[q] = nanmax(mx[q], __shfl_xor_sync(0xffffffffu, mx[q], o));
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sRed[warp * 8 + q] = s[q];
+        sRed[warp * 8 + 4] = mx[0];
+        sRed[warp * 8 + 5] = mx[1];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) s[q] = sRed[q];
+    mx[0] = sRed[4];
+    mx[1] = sRed[5];
+    for (int w = 1; w < CE_THREADS / 32; ++w) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s[q] += sRed[w * 8 + q];
+        mx[0] = nanmax(mx[0], sRed[w * 8 + 4]);
+        mx[1] = nanmax(mx[1], sRed[w * 8 + 5]);
+    }
+    __syncthreads();
+}
+
+// Start of a visit: the boundary lines in parity form for the first stage, and the boundary-line parts of the convergence
+// sums into S.step (every CTA of the cluster computes the same numbers in the same order).  cf. s2_visit_prepare.
+__device__ __forceinline__ void ce_visit_prepare(const CESmem& S, bool first, const double* __restrict__ ed,
+                                                 const double* __restrict__ ul, const double* __restrict__ vl, int m, int h, int n1) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) {
+        const int line = e / S2_HP, k = e % S2_HP;
+        double x = 0.0, y = 0.0;
+        if (k < h) {
+            if (first) {
+                x = __ldcg(ed + line * S2_ME + k);
+                y = __ldcg(ed + line * S2_ME + m - 1 - k);
+            } else if ((line & 3) == 3) {
+                const double* lid = (line < 4 ? ul : vl) + 1;
+                x = lid[k];
+                y = lid[m - 1 - k];
+            }
+        }
+        S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
+        S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
+    }
+    // sums over the boundary lines of ||phi^{n+1} - phi^n||^2, ||phi^n||^2 and max |lid|: with the lines as stored (first
+    // step after a load) and with the boundary-condition lines (every later step)
+    double sf[4] = {0, 0, 0, 0}, sb[4] = {0, 0, 0, 0}, bm[2] = {0, 0}, dummy[2] = {0, 0};
+    for (int e = tid; e < m; e += CE_THREADS) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double lid = (f ? vl : ul)[e + 1];
+            const double* L = ed + f * 4 * S2_ME;
+            const double w = __ldcg(L + e), ea = __ldcg(L + S2_ME + e), so = __ldcg(L + 2 * S2_ME + e),
+                         no = __ldcg(L + 3 * S2_ME + e);
+            const double dn = lid - no;
+            sf[2 * f] += w * w + ea * ea + so * so + dn * dn;
+            sf[2 * f + 1] += w * w + ea * ea + so * so + no * no;
+            sb[2 * f + 1] += lid * lid;
+            bm[f] = nanmax(bm[f], fabs(lid));
+        }
+    }
+    if (tid == 0) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const double* c = ed + 8 * S2_ME + 4 * f;   // c00 c0N cN0 cNN
+            const double l0 = (f ? vl : ul)[0], lN = (f ? vl : ul)[n1 - 1];
+            const double q0 = __ldcg(c), q1 = __ldcg(c + 1), q2 = __ldcg(c + 2), q3 = __ldcg(c + 3);
+            const double d1 = l0 - q1, d3 = lN - q3;
+            sf[2 * f] += q0 * q0 + d1 * d1 + q2 * q2 + d3 * d3;
+            sf[2 * f + 1] += q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3;
+            sb[2 * f + 1] += l0 * l0 + lN * lN;
+            bm[f] = nanmax(nanmax(bm[f], fabs(l0)), fabs(lN));
+        }
+    }
+    ce_block_reduce(sf, bm, S.red, warp, lane);
+    ce_block_reduce(sb, dummy, S.red, warp, lane);
+    if (tid == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            S.step[2 + q] = sf[q];
+            S.step[8 + q] = sb[q];
+        }
+        S.step[6] = bm[0];
+        S.step[7] = bm[1];
+    }
+    __syncthreads();
+}
+
+// geometry of a CTA inside its cluster and the shared::cluster addresses it stores to
+struct CEGeo {
+    int rank, trow, tcol, r0, c0, m, h, n1, nk4;
+    unsigned rrow[CE_CC];        // row panels of the CTAs of this tile row (all column tiles, this CTA included)
+    unsigned rcol[CE_CR];        // column panels of the CTAs of this tile column
+    __device__ CEGeo(const S2Params& P, const CESmem& S) {
+        rank = (int)ce_rank();
+        trow = rank / CE_CC; tcol = rank % CE_CC;
+        r0 = trow * CE_TR; c0 = tcol * CE_TC;
+        m = P.m; h = eo_half(m); n1 = P.n1; nk4 = P.K4 / 4;
+#pragma unroll
+        for (int c = 0; c < CE_CC; ++c) rrow[c] = ce_mapa(S.rp, trow * CE_CC + c);
+#pragma unroll
+        for (int r = 0; r < CE_CR; ++r) rcol[r] = ce_mapa(S.cp, r * CE_CC + tcol);
+    }
+};
+
+// one block value pair of the thread into every panel that holds it: columns j0, j0 + 1 of row i
+//   offR: double offset inside a row panel (a double2), offC: inside a column panel (second column 4 doubles further on)
+__device__ __forceinline__ void ce_publish(const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
+#pragma unroll
+    for (int c = 0; c < CE_CC; ++c) ce_st2(G.rrow[c] + offR * 8u, x0, x1);
+#pragma unroll
+    for (int r = 0; r < CE_CR; ++r) {
+        ce_st(G.rcol[r] + offC * 8u, x0);
+        ce_st(G.rcol[r] + offC * 8u + 32u, x1);
+    }
+}
+
+// After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): swap accumulator halves
+// with the other k-group, epilogue of this group's 8-column half, then -- once every CTA of the cluster has read its panels --
+// the stage output into the panels of the CTAs that need it, and the barrier that makes it visible.  cf. s2_finish.
+//   uo, vo: stage input at the thread's elements; fN, pN: phi^n of the warp's field and p^n there (u warps)
+template <int X>
+__device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, const CESmem& S, const CEGeo& G, int b, int stage,
+                                          bool bc_lines, double dt, int fld, int lane, const double (&uo)[4][2],
+                                          const double (&vo)[4][2], const double (&fN)[4][2], const double (&pN)[4][2],
+                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    const int g = lane >> 2, t = lane & 3, tid64 = fld * 32 + lane, warp = 2 * X + fld;
+    const int m = P.m, h = G.h, centre = (m & 1) ? h - 1 : -1;
+    const int i = G.r0 + g, j0 = G.c0 + 8 * X + 2 * t;
+    // ---- split-K hand-over: give away the other half, take the partner's contribution to this half ----
+    double* exch_own = S.exch + X * 24 * 64;
+    const double* exch_other = S.exch + (1 - X) * 24 * 64;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int idx = q * 2 + hh;
+            exch_own[(0 + idx) * 64 + tid64] = a1[q][1 - X][hh];
+            exch_own[(8 + idx) * 64 + tid64] = a2[q][1 - X][hh];
+            exch_own[(16 + idx) * 64 + tid64] = aL[q][1 - X][hh];
+        }
+    __syncthreads();
+    double b1[4][2], b2[4][2], bL[4][2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int idx = q * 2 + hh;
+            // group 0's sum first, whichever group does the addition (bitwise the same in both)
+            const double o1 = exch_other[(0 + idx) * 64 + tid64], o2 = exch_other[(8 + idx) * 64 + tid64],
+                         oL = exch_other[(16 + idx) * 64 + tid64];
+            b1[q][hh] = X == 0 ? a1[q][X][hh] + o1 : o1 + a1[q][X][hh];
+            b2[q][hh] = X == 0 ? a2[q][X][hh] + o2 : o2 + a2[q][X][hh];
+            bL[q][hh] = X == 0 ? aL[q][X][hh] + oL : oL + aL[q][X][hh];
+        }
+    if (fld == 0) s2_assemble<true>(S.vec, S.edgep, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
+    else s2_assemble<false>(S.vec, S.edgep + 8 * S2_HP, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
+
+    const double adt = rk_alpha(stage) * dt;
+    const bool last = (stage == 3);
+    double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
+    double fn[4][2];
+    {
+        const double wi = (i == centre) ? 0.5 : 1.0;
+        const double w0 = 4.0 * wi * (j0 == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j0 + 1 == centre ? 0.5 : 1.0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double fx = fN[q][0], fy = fN[q][1];
+            fn[q][0] = fx + adt * bL[q][0];
+            fn[q][1] = fy + adt * bL[q][1];
+            if (last) {
+                double d;
+                d = fn[q][0] - fx; s0 = fma(w0 * d, d, s0); s1 = fma(w0 * fx, fx, s1);
+                d = fn[q][1] - fy; s0 = fma(w1 * d, d, s0); s1 = fma(w1 * fy, fy, s1);
+            }
+            if (fld == 1) {   // dv/dy to the u warp of the same k-group
+                S.x[(X * 8 + q * 2 + 0) * 32 + lane] = b1[q][0];
+                S.x[(X * 8 + q * 2 + 1) * 32 + lane] = b1[q][1];
+            }
+        }
+        if (last) {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                double fr[4];
+                eo_to_points(fn[0][hh], fn[1][hh], fn[2][hh], fn[3][hh], fr);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) mx = nanmax(mx, fabs(fr[q]));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+                s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                mx = nanmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            }
+            if (lane == 0) {
+                S.red[warp * 4 + 0] = s0;
+                S.red[warp * 4 + 1] = s1;
+                S.red[warp * 4 + 2] = mx;
+            }
+        }
+    }
+    __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red; S.edgep has been read
+    // frozen pressure (SGSolver): every stage takes grad(p^n), so stages 0..2 leave the pressure blocks alone
+    const bool keep_pn = P.freeze && stage != 3;
+    double pn[4][2];
+    if (fld == 0 && !keep_pn) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double dv0 = b1[q][0] + S.x[(X * 8 + q * 2 + 0) * 32 + lane];
+            const double dv1 = b1[q][1] + S.x[(X * 8 + q * 2 + 1) * 32 + lane];
+            pn[q][0] = pN[q][0] + adt * (-V.beta2 * dv0);
+            pn[q][1] = pN[q][1] + adt * (-V.beta2 * dv1);
+        }
+    }
+    ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
+    {
+        const unsigned offR = (unsigned)(((j0 >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j0 & 3));
+        const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j0 & 15) * 4 + (i & 3));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) ce_publish(G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
+        if (fld == 0 && !keep_pn) {
+            const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) ce_publish(G, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
+        }
+    }
+    if (!bc_lines) {
+        // first stage after a load done: from now on the boundary lines are the boundary conditions (walls zero, lid line)
+        for (int e = threadIdx.x; e < 8 * S2_HP; e += CE_THREADS) {
+            const int line = e / S2_HP, k = e % S2_HP;
+            double x = 0.0, y = 0.0;
+            if (k < h && (line & 3) == 3) {
+                const double* lid = (line < 4 ? P.ulid : P.vlid) + (size_t)b * P.n1 + 1;
+                x = lid[k];
+                y = lid[m - 1 - k];
+            }
+            S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
+            S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
+        }
+    }
+    if (last && threadIdx.x < CE_CLUSTER) {
+        // this tile's partial sums to every CTA of the cluster.  warps: w = 2 X + fld; u: warps 0, 2; v: warps 1, 3
+        const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x);
+        ce_st(dst + 0, S.red[0 * 4 + 0] + S.red[2 * 4 + 0]);
+        ce_st(dst + 8, S.red[0 * 4 + 1] + S.red[2 * 4 + 1]);
+        ce_st(dst + 16, S.red[1 * 4 + 0] + S.red[3 * 4 + 0]);
+        ce_st(dst + 24, S.red[1 * 4 + 1] + S.red[3 * 4 + 1]);
+        ce_st(dst + 32, nanmax(S.red[0 * 4 + 2], S.red[2 * 4 + 2]));
+        ce_st(dst + 40, nanmax(S.red[1 * 4 + 2], S.red[3 * 4 + 2]));
+    }
+    ce_arrive();   // release: the stage output ...
+    ce_wait();     // ... is in every panel of the cluster
+}
+
+// The persistent kernel.  grid = clusters x 8 (cluster dimension 8 set at launch); a cluster pops a cavity from the queue,
+// advances it `chunk` steps and hands it back.  128 threads: warp w = 2 X + fld.
+__global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) {
+    extern __shared__ __align__(16) double smem[];
+    const CESmem S(smem);
+    const CEGeo G(P, S);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int X = warp >> 1, fld = warp & 1, g = lane >> 2, t = lane & 3;
+    const int fo = g * 4 + t;   // the thread's fragment offset inside a block (A: row g; B: column g; k = t)
+    const int m = G.m, h = G.h, n1 = G.n1;
+    for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    ce_arrive();
+    ce_wait();   // every CTA of the cluster is running: its shared memory may be written
+
+    for (;;) {
+        // ---- the cluster's next cavity ----
+        if (G.rank == 0 && tid == 0) {
+            const int bq = CavityQueue::pop(P);
+            for (unsigned r = 0; r < CE_CLUSTER; ++r) ce_st_s32(ce_mapa(S.cavity, r), bq);
+        }
+        ce_arrive();
+        ce_wait();
+        const int b = *reinterpret_cast<volatile int*>(S.cavity);
+        if (b < 0) return;
+
+        CavityStatus st = load_status(P.status + b);
+        const int cur = __ldcg(&P.status[b].pad);
+        S2Visit V;
+        V.nu = 1.0 / P.Re[b]; V.beta2 = P.beta2[b]; V.cfl = P.CFL[b]; V.lidv = P.lidvel[b];
+        V.tol = P.tol ? P.tol[b] : -1.0;
+        V.first = st.iters == 0 ? 1 : 0;
+        long long nsteps = P.launch_end - st.iters;
+        if (nsteps > P.chunk) nsteps = P.chunk;
+        const double *ul = P.ulid + (size_t)b * n1, *vl = P.vlid + (size_t)b * n1;
+        double* rec = P.rec + (size_t)cur * P.buf_stride + (size_t)b * S2_STRIDE;
+
+        // ---- the tile's panels out of the record (L2): operator blocks and state blocks, row side and column side ----
+        {
+            const double* srcA = rec + s2_off(G.trow >> 1, 0, 0, (G.trow & 1) * 8, 0);
+            for (int e = tid; e < CE_RP / 2; e += CE_THREADS) {
+                const int grp = e >> 4, w = e & 15;   // 16 double2 per 8 x 4 block
+                const int kk = grp / S2_NB, blk = grp % S2_NB;
+                reinterpret_cast<double2*>(S.rp)[e] =
+                    __ldcg(reinterpret_cast<const double2*>(srcA + ((size_t)kk * S2_NB + blk) * 64) + w);
+            }
+            const double* srcB = rec + S2_SIDE + s2_off(G.tcol, 0, 0, 0, 0);
+            for (int e = tid; e < CE_CP / 2; e += CE_THREADS)   // the 18 blocks of a k4-step are contiguous on both sides
+                reinterpret_cast<double2*>(S.cp)[e] = __ldcg(reinterpret_cast<const double2*>(srcB) + e);
+        }
+        ce_visit_prepare(S, V.first != 0, rec + S2_EDGE_OFF, ul, vl, m, h, n1);   // ends with a CTA barrier
+        double dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+        bool bc_lines = !V.first, active = true;
+        double fN[4][2], pN[4][2];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) fN[q][0] = fN[q][1] = pN[q][0] = pN[q][1] = 0.0;
+
+        for (long long step = 0; step < nsteps && active; ++step) {
+            for (int stage = 0; stage < 4; ++stage) {
+                double a1[4][2][2], a2[4][2][2], aL[4][2][2];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                        for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+                // K loop: group X takes the k4-steps X, X + 2, ...
+                // (unrolled: with one warp per SM sub-partition the next k4-step's fragment loads have to be in flight
+                // under this one's DMMAs)
+                if (fld == 0) {
+#pragma unroll
+                    for (int c = 0; c < CE_NK4 / 2; ++c) {
+                        const int kk = X + 2 * c;   // (k4-steps beyond the data are zero padding in both panels)
+                        ce_kstep<true>(S.rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, S.cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, 0,
+                                       a1, a2, aL);
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < CE_NK4 / 2; ++c) {
+                        const int kk = X + 2 * c;
+                        ce_kstep<false>(S.rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, S.cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, 1,
+                                        a1, a2, aL);
+                    }
+                }
+                // the stage input at the thread's own elements (columns 8 X + 2 t, + 1 of the tile), before anyone overwrites it
+                double uo[4][2], vo[4][2];
+                {
+                    const int j0 = G.c0 + 8 * X + 2 * t;
+                    const double* own = S.rp + (size_t)(j0 >> 2) * (S2_NB * CE_ABLK) + g * 4 + (j0 & 3);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const double2 a = *reinterpret_cast<const double2*>(own + (S2_BU + q) * CE_ABLK);
+                        const double2 c = *reinterpret_cast<const double2*>(own + (S2_BV + q) * CE_ABLK);
+                        uo[q][0] = a.x; uo[q][1] = a.y;
+                        vo[q][0] = c.x; vo[q][1] = c.y;
+                        if (stage == 0) {   // phi^n of the warp's field (u warps: also p^n), kept for the four stages
+                            fN[q][0] = fld == 0 ? a.x : c.x;
+                            fN[q][1] = fld == 0 ? a.y : c.y;
+                            if (fld == 0) {
+                                const double2 pp = *reinterpret_cast<const double2*>(own + (S2_BP + q) * CE_ABLK);
+                                pN[q][0] = pp.x; pN[q][1] = pp.y;
+                            }
+                        }
+                    }
+                }
+                ce_arrive();   // this CTA has read its panels (the wait is in ce_finish, behind the assembly)
+                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL);
+                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL);
+                bc_lines = true;
+            }
+            // ---- end of the step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread ----
+            {
+                const double* es = S.step + ((V.first && step == 0) ? 2 : 8);
+                double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0.0, 0.0};
+                for (int tl = 0; tl < CE_CLUSTER; ++tl) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
+                    mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
+                    mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
+                }
+                const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+                update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
+                st.umax = nanmax(mx[0], S.step[6]);
+                st.vmax = nanmax(mx[1], S.step[7]);
+                active = st.active != 0;
+                dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+            }
+        }
+
+        // ---- visit end: the state back into the record (rows by the CTAs of column tile 0, columns by those of row tile
+        // 0), boundary-condition lines and status by CTA 0, then the cavity goes back to the queue ----
+        if (G.tcol == 0) {
+            double* dstA = rec + s2_off(G.trow >> 1, 0, S2_BU, (G.trow & 1) * 8, 0);
+            for (int e = tid; e < CE_NK4 * 12 * 16; e += CE_THREADS) {
+                const int grp = e >> 4, w = e & 15;
+                const int kk = grp / 12, fb = grp % 12;
+                __stcg(reinterpret_cast<double2*>(dstA + ((size_t)kk * S2_NB + fb) * 64) + w,
+                       reinterpret_cast<const double2*>(S.rp + ((size_t)kk * S2_NB + S2_BU + fb) * CE_ABLK)[w]);
+            }
+        }
+        if (G.trow == 0) {
+            double* dstB = rec + S2_SIDE + s2_off(G.tcol, 0, S2_BU, 0, 0);
+            for (int e = tid; e < CE_NK4 * 12 * 32; e += CE_THREADS) {
+                const int kk = e / (12 * 32), w = e % (12 * 32);
+                __stcg(reinterpret_cast<double2*>(dstB + (size_t)kk * S2_NB * 64) + w,
+                       reinterpret_cast<const double2*>(S.cp + ((size_t)kk * S2_NB + S2_BU) * CE_BBLK)[w]);
+            }
+        }
+        if (G.rank == 0 && warp == 0) {
+            double* edn = rec + S2_EDGE_OFF;
+            for (int e = lane; e < S2_ME; e += 32) {
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    double* Ln = edn + f * 4 * S2_ME;
+                    __stcg(Ln + e, 0.0);
+                    __stcg(Ln + S2_ME + e, 0.0);
+                    __stcg(Ln + 2 * S2_ME + e, 0.0);
+                    __stcg(Ln + 3 * S2_ME + e, e < m ? (f ? vl : ul)[e + 1] : 0.0);
+                }
+            }
+            if (lane < 2) {
+                double* cn = edn + 8 * S2_ME + 4 * lane;
+                __stcg(cn + 0, 0.0);
+                __stcg(cn + 1, (lane ? vl : ul)[0]);
+                __stcg(cn + 2, 0.0);
+                __stcg(cn + 3, (lane ? vl : ul)[n1 - 1]);
+            }
+        }
+        __threadfence();
+        ce_arrive();
+        ce_wait();   // the whole record is written
+        if (G.rank == 0 && tid == 0) {
+            store_status(P.status + b, st);
+            __threadfence();
+            if (st.active && st.iters < P.launch_end) CavityQueue::push(P, b);
+            else CavityQueue::retire(P);
+        }
+    }
+}
+
+}  // namespace ldc

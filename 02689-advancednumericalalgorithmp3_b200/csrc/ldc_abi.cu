@@ -15,6 +15,7 @@
 #include "stream_eo.cuh"
 #include "stream_tma.cuh"
 #include "stream_tma_wide.cuh"
+#include "cluster_eo.cuh"
 #include "tiled.cuh"
 #include "validate.cuh"
 #include "vortex.cuh"
@@ -197,6 +198,50 @@ static int stream_auto(const ldc_handle* h) {
     return (stream_tma_ok(h) && !(e && atoi(e) == 0)) ? 5 : 3;
 }
 
+// Clusters of 8 CTAs of k_cluster_eo the device holds at once (0: the kernel cannot run here).
+static int cluster_eo_clusters(const ldc_handle* h) {
+    const size_t smem = CE_SMEM_DOUBLES * sizeof(double);
+    if (cudaFuncSetAttribute(k_cluster_eo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CE_CLUSTER;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3(CE_CLUSTER * std::max(1, h->num_sms / CE_CLUSTER));
+    cfg.blockDim = dim3(CE_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, k_cluster_eo, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+// Shape of the persistent streamed path for `nact` cavities still iterating: 0 = 16 x 16 tiles (k_stream_tma), 1 = 16 x 32
+// tiles (k_stream_tma_wide), 2 = a cluster of 8 CTAs per cavity with the state in distributed shared memory (k_cluster_eo:
+// parity blocks of 32 with all four 8-row tiles in use, i.e. 50 <= N <= 65, and a cluster for every cavity).
+// LDC_STREAM_CW = 1 | 2 | 3 forces a shape (3 = cluster, where the grid allows it).
+static int stream_tma_shape(const ldc_handle* h, int nact, int* clusters_out = nullptr) {
+    const int hh = eo_half(h->mx), ntile = (hh + ST_T - 1) / ST_T;
+    const char* e = getenv("LDC_STREAM_CW");
+    const int forced = e ? atoi(e) : 0;
+    if (ntile == 2 && hh > 24 && (forced == 0 || forced == 3)) {
+        const int nc = cluster_eo_clusters(h);
+        if (clusters_out) *clusters_out = nc;
+        if (nc > 0 && (forced == 3 || nact <= nc)) return 2;
+    }
+    if (forced == 1) return 0;
+    if (forced == 2) return ntile % 2 == 0 ? 1 : 0;
+    return (ntile % 2 == 0 && (long long)nact * 10 >= 16LL * (h->num_sms / (ntile * ntile))) ? 1 : 0;
+}
+
 // 0 tiled, 1 resident, 2 even-odd resident, 3 streamed even-odd, 4 even-odd resident split by equation,
 // 5 streamed even-odd, persistent + TMA
 static int pick_kernel(const ldc_handle* h) {
@@ -376,7 +421,10 @@ const char* ldc_kernel_name(const ldc_t* h) {
         case 2: return "k_resident_eo";
         case 3: return "k_stream_stage";
         case 4: return "k_resident_eo_split";
-        case 5: return "k_stream_tma";
+        case 5: {
+            const int shape = stream_tma_shape(h, h->B);
+            return shape == 2 ? "k_cluster_eo" : (shape == 1 ? "k_stream_tma_wide" : "k_stream_tma");
+        }
     }
     return "unsupported";
 }
@@ -742,13 +790,26 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
         // (measured, B200: N = 128 B = 64 196 k -> 247 k steps/s; with an odd number of 16-wide tiles per block edge the wide
         // tiles of the last column are half padding: N = 96 B = 64 399 k -> 384 k, so those grids keep the 16 x 16 shape)
         // The shape is chosen per launch from the number of cavities still iterating (both shapes work on the same records).
-        bool wide = false;
+        // Third shape (k_cluster_eo, cluster_eo.cuh): on the 32-wide parity blocks, once every cavity still iterating can
+        // have a cluster of 8 CTAs, the state stays in the cluster's shared memory and the stages exchange it there.
+        bool wide = false, cluster = false;
         int team_size = 0, teams = 0;
         size_t smem = 0;
         const void* kfun = nullptr;
         auto pick_shape = [&](int nact) -> int {
-            wide = ntile % 2 == 0 && (long long)nact * 10 >= 16LL * (h->num_sms / (ntile * ntile));
-            if (const char* e = getenv("LDC_STREAM_CW")) wide = atoi(e) == 2;
+            int nclusters = 0;
+            const int shape = stream_tma_shape(h, nact, &nclusters);
+            cluster = shape == 2;
+            if (cluster) {
+                wide = false;
+                team_size = CE_CLUSTER;
+                smem = CE_SMEM_DOUBLES * sizeof(double);
+                kfun = (const void*)k_cluster_eo;
+                teams = std::min(nact, nclusters);
+                if (const char* e = getenv("LDC_STREAM_TEAMS")) teams = std::max(1, std::min(teams, atoi(e)));
+                return LDC_OK;
+            }
+            wide = shape == 1;
             team_size = wide ? ntile * ((ntile + 1) / 2) : ntile * ntile;
             smem = (wide ? S2W_SMEM_DOUBLES : S2_SMEM_DOUBLES) * sizeof(double);
             kfun = wide ? (const void*)k_stream_tma_wide : (const void*)k_stream_tma;
@@ -813,8 +874,25 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             k_queue_init<<<1, 1024, 0, h->stream>>>(h->status, h->B, P.launch_end, h->q_data, h->q_seq, h->q_ctl);
             LDC_CUDA(cudaMemsetAsync(h->t_team, 0, 2 * (size_t)h->num_sms * sizeof(double), h->stream));
             void* args[] = {(void*)&P};
-            LDC_CUDA(cudaLaunchCooperativeKernel(kfun, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
-                                                 h->stream));
+            if (cluster) {
+                // clusters need no co-residency with each other (a cluster waiting at the queue only waits for running ones)
+                cudaLaunchConfig_t cfg = {};
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = CE_CLUSTER;
+                at[0].val.clusterDim.y = 1;
+                at[0].val.clusterDim.z = 1;
+                cfg.attrs = at;
+                cfg.numAttrs = 1;
+                cfg.gridDim = dim3(teams * CE_CLUSTER);
+                cfg.blockDim = dim3(CE_THREADS);
+                cfg.dynamicSmemBytes = smem;
+                cfg.stream = h->stream;
+                LDC_CUDA(cudaLaunchKernelExC(&cfg, kfun, args));
+            } else {
+                LDC_CUDA(cudaLaunchCooperativeKernel(kfun, dim3(teams * team_size), dim3(S2_THREADS), args, smem,
+                                                     h->stream));
+            }
             h->launches += 2;
             if (dbg) {
                 std::vector<long long> hd(S2_DBG_STAGES * 16);
