@@ -75,6 +75,8 @@ __device__ __forceinline__ void ce_st_s32(unsigned addr, int v) {
     asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 __device__ __forceinline__ void ce_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+// arrival that publishes nothing ("this CTA has read its panels"): no release fence
+__device__ __forceinline__ void ce_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void ce_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 // ---- one k4-step of the warp's contractions (cf. s2_chunk) -------------------------------------------------------------
@@ -258,30 +260,35 @@ __device__ __forceinline__ void ce_visit_prepare(const CESmem& S, bool first, co
 // geometry of a CTA inside its cluster and the shared::cluster addresses it stores to
 struct CEGeo {
     int rank, trow, tcol, r0, c0, m, h, n1, nk4;
-    unsigned rrow[CE_CC];        // row panels of the CTAs of this tile row (all column tiles, this CTA included)
+    unsigned rrow[CE_CC];        // row panels of the CTAs of this tile row
     unsigned rcol[CE_CR];        // column panels of the CTAs of this tile column
     __device__ CEGeo(const S2Params& P, const CESmem& S) {
         rank = (int)ce_rank();
         trow = rank / CE_CC; tcol = rank % CE_CC;
         r0 = trow * CE_TR; c0 = tcol * CE_TC;
         m = P.m; h = eo_half(m); n1 = P.n1; nk4 = P.K4 / 4;
+        // entry 0 is this CTA itself (stored to directly), entries 1.. the other CTAs of the row / column, starting with the next
 #pragma unroll
-        for (int c = 0; c < CE_CC; ++c) rrow[c] = ce_mapa(S.rp, trow * CE_CC + c);
+        for (int c = 0; c < CE_CC; ++c) rrow[c] = ce_mapa(S.rp, trow * CE_CC + (tcol + c) % CE_CC);
 #pragma unroll
-        for (int r = 0; r < CE_CR; ++r) rcol[r] = ce_mapa(S.cp, r * CE_CC + tcol);
+        for (int r = 0; r < CE_CR; ++r) rcol[r] = ce_mapa(S.cp, ((trow + r) % CE_CR) * CE_CC + tcol);
     }
 };
 
 // one block value pair of the thread into every panel that holds it: columns j0, j0 + 1 of row i
 //   offR: double offset inside a row panel (a double2), offC: inside a column panel (second column 4 doubles further on)
-__device__ __forceinline__ void ce_publish(const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
+__device__ __forceinline__ void ce_publish(const CESmem& S, const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
+    // remote panels first (the SM-to-SM network is the slow part), the CTA's own by plain shared-memory stores
 #pragma unroll
-    for (int c = 0; c < CE_CC; ++c) ce_st2(G.rrow[c] + offR * 8u, x0, x1);
-#pragma unroll
-    for (int r = 0; r < CE_CR; ++r) {
+    for (int r = 1; r < CE_CR; ++r) {
         ce_st(G.rcol[r] + offC * 8u, x0);
         ce_st(G.rcol[r] + offC * 8u + 32u, x1);
     }
+#pragma unroll
+    for (int c = 1; c < CE_CC; ++c) ce_st2(G.rrow[c] + offR * 8u, x0, x1);
+    *reinterpret_cast<double2*>(S.rp + offR) = make_double2(x0, x1);
+    S.cp[offC] = x0;
+    S.cp[offC + 4] = x1;
 }
 
 // After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): swap accumulator halves
@@ -292,7 +299,8 @@ template <int X>
 __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, const CESmem& S, const CEGeo& G, int b, int stage,
                                           bool bc_lines, double dt, int fld, int lane, const double (&uo)[4][2],
                                           const double (&vo)[4][2], const double (&fN)[4][2], const double (&pN)[4][2],
-                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2],
+                                          long long* __restrict__ tdbg) {
     const int g = lane >> 2, t = lane & 3, tid64 = fld * 32 + lane, warp = 2 * X + fld;
     const int m = P.m, h = G.h, centre = (m & 1) ? h - 1 : -1;
     const int i = G.r0 + g, j0 = G.c0 + 8 * X + 2 * t;
@@ -309,6 +317,7 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             exch_own[(16 + idx) * 64 + tid64] = aL[q][1 - X][hh];
         }
     __syncthreads();
+    if (tdbg) tdbg[3] = clock64();
     double b1[4][2], b2[4][2], bL[4][2];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
@@ -368,6 +377,7 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             }
         }
     }
+    if (tdbg) tdbg[4] = clock64();
     __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red; S.edgep has been read
     // frozen pressure (SGSolver): every stage takes grad(p^n), so stages 0..2 leave the pressure blocks alone
     const bool keep_pn = P.freeze && stage != 3;
@@ -381,16 +391,18 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             pn[q][1] = pN[q][1] + adt * (-V.beta2 * dv1);
         }
     }
+    if (tdbg) tdbg[5] = clock64();
     ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
+    if (tdbg) tdbg[6] = clock64();
     {
         const unsigned offR = (unsigned)(((j0 >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j0 & 3));
         const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j0 & 15) * 4 + (i & 3));
 #pragma unroll
-        for (int q = 0; q < 4; ++q) ce_publish(G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
+        for (int q = 0; q < 4; ++q) ce_publish(S, G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
         if (fld == 0 && !keep_pn) {
             const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) ce_publish(G, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
+            for (int q = 0; q < 4; ++q) ce_publish(S, G, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
         }
     }
     if (!bc_lines) {
@@ -417,8 +429,10 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
         ce_st(dst + 32, nanmax(S.red[0 * 4 + 2], S.red[2 * 4 + 2]));
         ce_st(dst + 40, nanmax(S.red[1 * 4 + 2], S.red[3 * 4 + 2]));
     }
+    if (tdbg) tdbg[7] = clock64();
     ce_arrive();   // release: the stage output ...
     ce_wait();     // ... is in every panel of the cluster
+    if (tdbg) tdbg[8] = clock64();
 }
 
 // The persistent kernel.  grid = clusters x 8 (cluster dimension 8 set at launch); a cluster pops a cavity from the queue,
@@ -431,6 +445,11 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
     const int X = warp >> 1, fld = warp & 1, g = lane >> 2, t = lane & 3;
     const int fo = g * 4 + t;   // the thread's fragment offset inside a block (A: row g; B: column g; k = t)
     const int m = G.m, h = G.h, n1 = G.n1;
+    // LDC_S2_DEBUG: clock samples of warp 0 of CTA 0 per stage -- [0] stage start, [1] K loop done, [2] own elements read,
+    // [3] accumulator swap done, [4] assembly done, [5] pressure update done, [6] every CTA has read its panels, [7] stage
+    // output stored, [8] stage output visible everywhere
+    const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && tid == 0;
+    int dbg_stage = 0;
     for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
     ce_arrive();
     ce_wait();   // every CTA of the cluster is running: its shared memory may be written
@@ -477,8 +496,30 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
 #pragma unroll
         for (int q = 0; q < 4; ++q) fN[q][0] = fN[q][1] = pN[q][0] = pN[q][1] = 0.0;
 
-        for (long long step = 0; step < nsteps && active; ++step) {
+        // end of a step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread (the same numbers
+        // everywhere): convergence bookkeeping, dt of the next step
+        auto reduce_step = [&](bool first_step) {
+            const double* es = S.step + (first_step ? 2 : 8);
+            double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0.0, 0.0};
+            for (int tl = 0; tl < CE_CLUSTER; ++tl) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
+                mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
+                mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
+            }
+            const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+            update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
+            st.umax = nanmax(mx[0], S.step[6]);
+            st.vmax = nanmax(mx[1], S.step[7]);
+            active = st.active != 0;
+            dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+        };
+        for (long long step = 0; step < nsteps; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
+                // The previous step's reduction sits in front of this stage's K loop, which does not depend on it: its
+                // square roots and divisions run under the DMMAs.  Should the cavity have gone inactive, the K loop was
+                // speculative (it only reads) and the visit ends before anything is published.
+                if (stage == 0 && step > 0) reduce_step(V.first && step == 1);
                 double a1[4][2][2], a2[4][2][2], aL[4][2][2];
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
@@ -486,6 +527,9 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                     for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
                         for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+                long long* tdbg = (dbg_on && dbg_stage < S2_DBG_STAGES) ? P.dbg + dbg_stage * 16 : nullptr;
+                ++dbg_stage;
+                if (tdbg) tdbg[0] = clock64();
                 // K loop: group X takes the k4-steps X, X + 2, ...
                 // (unrolled: with one warp per SM sub-partition the next k4-step's fragment loads have to be in flight
                 // under this one's DMMAs)
@@ -504,6 +548,8 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                                         a1, a2, aL);
                     }
                 }
+                if (tdbg) tdbg[1] = clock64();
+                if (stage == 0 && !active) break;
                 // the stage input at the thread's own elements (columns 8 X + 2 t, + 1 of the tile), before anyone overwrites it
                 double uo[4][2], vo[4][2];
                 {
@@ -525,29 +571,15 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                         }
                     }
                 }
-                ce_arrive();   // this CTA has read its panels (the wait is in ce_finish, behind the assembly)
-                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL);
-                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL);
+                ce_arrive_relaxed();   // this CTA has read its panels (the wait is in ce_finish, behind the assembly)
+                if (tdbg) tdbg[2] = clock64();
+                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
+                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
                 bc_lines = true;
             }
-            // ---- end of the step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread ----
-            {
-                const double* es = S.step + ((V.first && step == 0) ? 2 : 8);
-                double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0.0, 0.0};
-                for (int tl = 0; tl < CE_CLUSTER; ++tl) {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
-                    mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
-                    mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
-                }
-                const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
-                update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
-                st.umax = nanmax(mx[0], S.step[6]);
-                st.vmax = nanmax(mx[1], S.step[7]);
-                active = st.active != 0;
-                dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
-            }
+            if (!active) break;
         }
+        if (active && nsteps > 0) reduce_step(V.first && nsteps == 1);   // the last step of the visit
 
         // ---- visit end: the state back into the record (rows by the CTAs of column tile 0, columns by those of row tile
         // 0), boundary-condition lines and status by CTA 0, then the cavity goes back to the queue ----
