@@ -34,11 +34,12 @@ constexpr int CE_EXCH = 2 * 24 * 64;                         // accumulator swap
 constexpr size_t CE_SMEM_DOUBLES = (size_t)CE_RP + CE_CP + CE_EXCH
                                    + 8 * S2_HP + 16 * S2_HP  // boundary-column vectors, boundary lines in parity form
                                    + 2 * 8 * 32              // dv/dy hand-over v warps -> u warps
-                                   + CE_CLUSTER * 8 + 64 + 16 + 2;   // partials of the 8 tiles, reduction scratch, step info, cavity
+                                   + CE_CLUSTER * 8 + 64 + 16 + 2;   // partials of the 8 tiles, reduction scratch, step info, cavity + mbarrier
 
 struct CESmem {
     double *rp, *cp, *exch, *vec, *edgep, *x, *part, *red, *step;
     int* cavity;
+    unsigned long long* databar;   // mbarrier: the other CTAs' part of a stage output has arrived (byte count)
     __device__ explicit CESmem(double* smem) {
         rp = smem;
         cp = rp + CE_RP;
@@ -50,6 +51,7 @@ struct CESmem {
         red = part + CE_CLUSTER * 8;
         step = red + 64;   // [2..5] boundary-line sums of a first step, [6..7] max |lid|, [8..11] sums of later steps
         cavity = reinterpret_cast<int*>(step + 16);
+        databar = reinterpret_cast<unsigned long long*>(step + 17);
     }
 };
 
@@ -71,6 +73,15 @@ __device__ __forceinline__ void ce_st(unsigned addr, double v) {
 __device__ __forceinline__ void ce_st2(unsigned addr, double v0, double v1) {
     asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v0), "d"(v1) : "memory");
 }
+// stores into another CTA's shared memory that count their bytes on an mbarrier there once they have landed (STAS)
+__device__ __forceinline__ void ce_sta(unsigned addr, double v, unsigned bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(addr), "d"(v), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void ce_sta2(unsigned addr, double v0, double v1, unsigned bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];" ::"r"(addr), "d"(v0),
+                 "d"(v1), "r"(bar) : "memory");
+}
 __device__ __forceinline__ void ce_st_s32(unsigned addr, int v) {
     asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -79,57 +90,38 @@ __device__ __forceinline__ void ce_arrive() { asm volatile("barrier.cluster.arri
 __device__ __forceinline__ void ce_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void ce_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
-// ---- one k4-step of the warp's contractions (cf. s2_chunk) -------------------------------------------------------------
+// ---- one k4-step of the warp's contractions (cf. s2_chunk), in two halves ---------------------------------------------
 //   A = row panel at this k4-step + the thread's A-fragment offset (g * 4 + t), block b at A + b * CE_ABLK
 //   Bp = column panel likewise,                                                  block b at Bp + b * CE_BBLK (+ 32: second half)
+// ce_kstep_opsA: operator rows (row panel) x state columns (column panel) -- needs the state rows 4 kk .. 4 kk + 3, which
+//   the CTAs of row tile kk / 2 produce;
+// ce_kstep_opsB: state rows (row panel) x operator rows at the tile's columns (column panel) -- needs the state columns
+//   4 kk .. 4 kk + 3, which the CTAs of column tile kk / 4 produce.
+// So three of a warp's eight half-steps work on state this CTA has produced itself (ce_local_part).
 template <bool P_LEFT>
-__device__ __forceinline__ void ce_kstep(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
-                                         double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+__device__ __forceinline__ void ce_kstep_opsA(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
+                                              double (&a1)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int NT = 2;
     const int bf = S2_BU + 4 * fld;
-    double FA[4], FB[4][NT];
+    double FB[4][NT], dA[2], ddA[2];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        FA[q] = A[(bf + q) * CE_ABLK];
+    for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) FB[q][nt] = Bp[(bf + q) * CE_BBLK + nt * 32];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        dA[a] = A[a * CE_ABLK];
+        ddA[a] = A[(2 + a) * CE_ABLK];
     }
-    {
-        double dA[2], ddA[2];
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
-            dA[a] = A[a * CE_ABLK];
-            ddA[a] = A[(2 + a) * CE_ABLK];
-        }
-#pragma unroll
-        for (int a = 0; a < 2; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
-                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
-                }
-    }
-    {
-        double dB[2][NT], ddB[2][NT];
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b)
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-                dB[b][nt] = Bp[b * CE_BBLK + nt * 32];
-                ddB[b][nt] = Bp[(2 + b) * CE_BBLK + nt * 32];
+                dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
+                dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
             }
-#pragma unroll
-        for (int a = 0; a < 2; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
-                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
-                }
-    }
     if (P_LEFT) {
         double gA[2], PB[4][NT];
 #pragma unroll
@@ -145,7 +137,33 @@ __device__ __forceinline__ void ce_kstep(const double* __restrict__ A, const dou
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt)
                     dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
-    } else {
+    }
+}
+template <bool P_LEFT>
+__device__ __forceinline__ void ce_kstep_opsB(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
+                                              double (&a2)[4][2][2], double (&aL)[4][2][2]) {
+    constexpr int NT = 2;
+    const int bf = S2_BU + 4 * fld;
+    double FA[4], dB[2][NT], ddB[2][NT];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) FA[q] = A[(bf + q) * CE_ABLK];
+#pragma unroll
+    for (int b = 0; b < 2; ++b)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            dB[b][nt] = Bp[b * CE_BBLK + nt * 32];
+            ddB[b][nt] = Bp[(2 + b) * CE_BBLK + nt * 32];
+        }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
+                dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
+            }
+    if (!P_LEFT) {
         double PA[4], gB[2][NT];
 #pragma unroll
         for (int q = 0; q < 4; ++q) PA[q] = A[(S2_BP + q) * CE_ABLK];
@@ -160,6 +178,40 @@ __device__ __forceinline__ void ce_kstep(const double* __restrict__ A, const dou
 #pragma unroll
                 for (int nt = 0; nt < NT; ++nt)
                     dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], PA[2 * a + (1 - b)], gB[b][nt]);
+    }
+}
+// The K loop of a stage for k-group X (k4-steps X, X + 2, X + 4, X + 6) in two parts.  Local part: the half-steps whose state
+// operand this CTA produces itself -- opsA at k4-step 2 trow + X, opsB at 4 tcol + X and 4 tcol + 2 + X.  It runs right
+// after the CTA's own stores of the previous stage, while the other CTAs' stores are still crossing the SM-to-SM network.
+// Remote part: the other five half-steps, once the cluster barrier says that everything has arrived.  (The order of the
+// accumulation differs from tile to tile but is fixed for a tile.)
+template <bool P_LEFT>
+__device__ __forceinline__ void ce_local_part(const double* __restrict__ rp, const double* __restrict__ cp, int fo, int X, int trow,
+                                              int tcol, int fld, double (&a1)[4][2][2], double (&a2)[4][2][2],
+                                              double (&aL)[4][2][2]) {
+    {
+        const int kk = 2 * trow + X;
+        ce_kstep_opsA<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a1, aL);
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        const int kk = 4 * tcol + 2 * c + X;
+        ce_kstep_opsB<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a2, aL);
+    }
+}
+template <bool P_LEFT>
+__device__ __forceinline__ void ce_remote_part(const double* __restrict__ rp, const double* __restrict__ cp, int fo, int X, int trow,
+                                               int tcol, int fld, double (&a1)[4][2][2], double (&a2)[4][2][2],
+                                               double (&aL)[4][2][2]) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        const int kk = 4 * (1 - tcol) + 2 * c + X;
+        ce_kstep_opsB<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a2, aL);
+    }
+#pragma unroll
+    for (int c = 1; c < CE_CR; ++c) {
+        const int kk = 2 * ((trow + c) % CE_CR) + X;
+        ce_kstep_opsA<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a1, aL);
     }
 }
 
@@ -262,6 +314,7 @@ struct CEGeo {
     int rank, trow, tcol, r0, c0, m, h, n1, nk4;
     unsigned rrow[CE_CC];        // row panels of the CTAs of this tile row
     unsigned rcol[CE_CR];        // column panels of the CTAs of this tile column
+    unsigned bar_off;            // data barrier of a CTA = its panel address + bar_off (one window per CTA, same layout)
     __device__ CEGeo(const S2Params& P, const CESmem& S) {
         rank = (int)ce_rank();
         trow = rank / CE_CC; tcol = rank % CE_CC;
@@ -272,6 +325,7 @@ struct CEGeo {
         for (int c = 0; c < CE_CC; ++c) rrow[c] = ce_mapa(S.rp, trow * CE_CC + (tcol + c) % CE_CC);
 #pragma unroll
         for (int r = 0; r < CE_CR; ++r) rcol[r] = ce_mapa(S.cp, ((trow + r) % CE_CR) * CE_CC + tcol);
+        bar_off = ce_mapa(S.databar, 0) - ce_mapa(S.rp, 0);
     }
 };
 
@@ -279,13 +333,14 @@ struct CEGeo {
 //   offR: double offset inside a row panel (a double2), offC: inside a column panel (second column 4 doubles further on)
 __device__ __forceinline__ void ce_publish(const CESmem& S, const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
     // remote panels first (the SM-to-SM network is the slow part), the CTA's own by plain shared-memory stores
+    const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
 #pragma unroll
     for (int r = 1; r < CE_CR; ++r) {
-        ce_st(G.rcol[r] + offC * 8u, x0);
-        ce_st(G.rcol[r] + offC * 8u + 32u, x1);
+        ce_sta(G.rcol[r] + offC * 8u, x0, G.rcol[r] + cp_to_bar);
+        ce_sta(G.rcol[r] + offC * 8u + 32u, x1, G.rcol[r] + cp_to_bar);
     }
 #pragma unroll
-    for (int c = 1; c < CE_CC; ++c) ce_st2(G.rrow[c] + offR * 8u, x0, x1);
+    for (int c = 1; c < CE_CC; ++c) ce_sta2(G.rrow[c] + offR * 8u, x0, x1, G.rrow[c] + G.bar_off);
     *reinterpret_cast<double2*>(S.rp + offR) = make_double2(x0, x1);
     S.cp[offC] = x0;
     S.cp[offC + 4] = x1;
@@ -421,18 +476,20 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
     }
     if (last && threadIdx.x < CE_CLUSTER) {
         // this tile's partial sums to every CTA of the cluster.  warps: w = 2 X + fld; u: warps 0, 2; v: warps 1, 3
-        const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x);
-        ce_st(dst + 0, S.red[0 * 4 + 0] + S.red[2 * 4 + 0]);
-        ce_st(dst + 8, S.red[0 * 4 + 1] + S.red[2 * 4 + 1]);
-        ce_st(dst + 16, S.red[1 * 4 + 0] + S.red[3 * 4 + 0]);
-        ce_st(dst + 24, S.red[1 * 4 + 1] + S.red[3 * 4 + 1]);
-        ce_st(dst + 32, nanmax(S.red[0 * 4 + 2], S.red[2 * 4 + 2]));
-        ce_st(dst + 40, nanmax(S.red[1 * 4 + 2], S.red[3 * 4 + 2]));
+        const double o[6] = {S.red[0 * 4 + 0] + S.red[2 * 4 + 0], S.red[0 * 4 + 1] + S.red[2 * 4 + 1],
+                             S.red[1 * 4 + 0] + S.red[3 * 4 + 0], S.red[1 * 4 + 1] + S.red[3 * 4 + 1],
+                             nanmax(S.red[0 * 4 + 2], S.red[2 * 4 + 2]), nanmax(S.red[1 * 4 + 2], S.red[3 * 4 + 2])};
+        if ((int)threadIdx.x == G.rank) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) S.part[G.rank * 8 + q] = o[q];
+        } else {
+            const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x), bar = ce_mapa(S.databar, threadIdx.x);
+#pragma unroll
+            for (int q = 0; q < 6; ++q) ce_sta(dst + 8 * q, o[q], bar);
+        }
     }
     if (tdbg) tdbg[7] = clock64();
-    ce_arrive();   // release: the stage output ...
-    ce_wait();     // ... is in every panel of the cluster
-    if (tdbg) tdbg[8] = clock64();
+    __syncthreads();   // the CTA's own panels are complete: the caller runs the local part of the next K loop, then the barrier
 }
 
 // The persistent kernel.  grid = clusters x 8 (cluster dimension 8 set at launch); a cluster pops a cavity from the queue,
@@ -451,6 +508,11 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
     const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && tid == 0;
     int dbg_stage = 0;
     for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
+    if (tid == 0) {
+        mbar_init(S.databar, 1);   // one arrival per stage (with the byte count the other CTAs will deliver)
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    unsigned nphase = 0;   // stages whose output has been waited for (the data barrier's phase)
     ce_arrive();
     ce_wait();   // every CTA of the cluster is running: its shared memory may be written
 
@@ -507,49 +569,65 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
                 mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
             }
-            const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
-            update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
             st.umax = nanmax(mx[0], S.step[6]);
             st.vmax = nanmax(mx[1], S.step[7]);
+            // The six square roots and then the six divisions of the residuals and of s2_dt are independent of each other:
+            // lane l of every warp takes the l-th, so that their latencies (a couple of hundred cycles each) overlap.  Same
+            // operations on the same operands as the serial forms (s2_dt; sqrt(s0) / (sqrt(s1) + 1e-12)).
+            const double ua = (V.lidv > st.umax) ? V.lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
+            const double sq_arg = lane == 0 ? s[0] : (lane == 1 ? s[1] : (lane == 2 ? s[2] : (lane == 3 ? s[3] :
+                                  (lane == 4 ? ua * ua + V.beta2 : va * va + V.beta2))));
+            const double sq = sqrt(sq_arg);
+            const double r0 = __shfl_sync(0xffffffffu, sq, 0), r1 = __shfl_sync(0xffffffffu, sq, 1),
+                         r2 = __shfl_sync(0xffffffffu, sq, 2), r3 = __shfl_sync(0xffffffffu, sq, 3),
+                         r4 = __shfl_sync(0xffffffffu, sq, 4), r5 = __shfl_sync(0xffffffffu, sq, 5);
+            const double num = lane == 0 ? r0 : (lane == 1 ? r2 : (lane == 2 ? ua + r4 : (lane == 3 ? va + r5 : V.nu)));
+            const double den = lane == 0 ? r1 + 1e-12 : (lane == 1 ? r3 + 1e-12 : (lane == 2 ? P.dx_min : (lane == 3 ? P.dy_min :
+                               (lane == 4 ? P.dx_min * P.dx_min : P.dy_min * P.dy_min))));
+            const double qt = num / den;
+            const double ures = __shfl_sync(0xffffffffu, qt, 0), vres = __shfl_sync(0xffffffffu, qt, 1);
+            const double lam_x = __shfl_sync(0xffffffffu, qt, 2) + __shfl_sync(0xffffffffu, qt, 4);
+            const double lam_y = __shfl_sync(0xffffffffu, qt, 3) + __shfl_sync(0xffffffffu, qt, 5);
+            update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
             active = st.active != 0;
-            dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+            dt = V.cfl / (lam_x + lam_y);
         };
+        double a1[4][2][2], a2[4][2][2], aL[4][2][2];
+        auto start_stage = [&]() {   // accumulators to zero, then the part of the K loop that needs no one else's output
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+            if (fld == 0) ce_local_part<true>(S.rp, S.cp, fo, X, G.trow, G.tcol, 0, a1, a2, aL);
+            else ce_local_part<false>(S.rp, S.cp, fo, X, G.trow, G.tcol, 1, a1, a2, aL);
+        };
+        start_stage();
         for (long long step = 0; step < nsteps; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
-                // The previous step's reduction sits in front of this stage's K loop, which does not depend on it: its
-                // square roots and divisions run under the DMMAs.  Should the cavity have gone inactive, the K loop was
-                // speculative (it only reads) and the visit ends before anything is published.
+                // The previous step's reduction: convergence, dt.  Should the cavity have gone inactive, the K loop parts
+                // run so far were speculative (they only read) and the visit ends before anything is published.
+                const long long t_red0 = dbg_on ? clock64() : 0;
                 if (stage == 0 && step > 0) reduce_step(V.first && step == 1);
-                double a1[4][2][2], a2[4][2][2], aL[4][2][2];
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-#pragma unroll
-                    for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-                        for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
+                const long long t_red1 = dbg_on ? clock64() : 0;
+                if (stage == 0 && !active) break;
                 long long* tdbg = (dbg_on && dbg_stage < S2_DBG_STAGES) ? P.dbg + dbg_stage * 16 : nullptr;
                 ++dbg_stage;
-                if (tdbg) tdbg[0] = clock64();
-                // K loop: group X takes the k4-steps X, X + 2, ...
-                // (unrolled: with one warp per SM sub-partition the next k4-step's fragment loads have to be in flight
-                // under this one's DMMAs)
-                if (fld == 0) {
-#pragma unroll
-                    for (int c = 0; c < CE_NK4 / 2; ++c) {
-                        const int kk = X + 2 * c;   // (k4-steps beyond the data are zero padding in both panels)
-                        ce_kstep<true>(S.rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, S.cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, 0,
-                                       a1, a2, aL);
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < CE_NK4 / 2; ++c) {
-                        const int kk = X + 2 * c;
-                        ce_kstep<false>(S.rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, S.cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, 1,
-                                        a1, a2, aL);
-                    }
+                if (tdbg) {
+                    tdbg[9] = t_red1 - t_red0;   // the previous step's reduction (stage 0)
+                    tdbg[0] = clock64();
                 }
+                if (tid == 0) {
+                    // what the other CTAs will deliver for this stage: u, v (8 blocks) and, unless the pressure is frozen, p
+                    // (4 blocks) of one tile into the row panel and of three into the column panel; 6 sums from 7 CTAs
+                    const unsigned blocks = (P.freeze && stage != 3) ? 8u : 12u;
+                    mbar_expect_tx(S.databar, 4u * blocks * (CE_TR * CE_TC * 8u) + (stage == 3 ? 7u * 48u : 0u));
+                }
+                // the rest of the K loop: everything has arrived
+                if (fld == 0) ce_remote_part<true>(S.rp, S.cp, fo, X, G.trow, G.tcol, 0, a1, a2, aL);
+                else ce_remote_part<false>(S.rp, S.cp, fo, X, G.trow, G.tcol, 1, a1, a2, aL);
                 if (tdbg) tdbg[1] = clock64();
-                if (stage == 0 && !active) break;
                 // the stage input at the thread's own elements (columns 8 X + 2 t, + 1 of the tile), before anyone overwrites it
                 double uo[4][2], vo[4][2];
                 {
@@ -576,6 +654,13 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
                 else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
                 bc_lines = true;
+                // The local part of the next stage's K loop runs while the stores cross the SM-to-SM network.  They are
+                // st.async stores that count their bytes on the receiver's mbarrier: no release fence, no barrier round trip.
+                start_stage();
+                if (tdbg) tdbg[10] = clock64();
+                mbar_wait(S.databar, nphase & 1);   // everyone else's part of the stage output is in this CTA's panels
+                ++nphase;
+                if (tdbg) tdbg[8] = clock64();
             }
             if (!active) break;
         }

@@ -33,6 +33,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     } while (!ok);
 }
 
+// mode 4: st.async stores, time until the receiver's mbarrier completes (the trailing cluster barrier not counted);
 // mode 0: barrier only; 1: v2.f64 remote stores; 2: scalar f64 remote stores (pairs 32 B apart, the column-side pattern);
 // 3: bulk copies smem -> peer smem.  `bytes` leave every CTA per iteration, spread over `npeers` peers.
 __global__ void __launch_bounds__(384, 1) k_x(int mode, int cs, unsigned bytes, int npeers, int issuers, int iters,
@@ -52,7 +53,9 @@ __global__ void __launch_bounds__(384, 1) k_x(int mode, int cs, unsigned bytes, 
     cluster_sync_all();
     const unsigned per_peer = bytes / npeers;
     long long t0 = clock64();
+    long long t_data = 0;
     for (int it = 0; it < iters; ++it) {
+        const long long t_it = clock64();
         if (mode == 1 && tid < 256) {
             for (int p = 0; p < npeers; ++p) {
                 const unsigned r = mapa(sm(dst), (me + 1 + p) % cs);
@@ -69,6 +72,19 @@ __global__ void __launch_bounds__(384, 1) k_x(int mode, int cs, unsigned bytes, 
                     asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(r + o + 32), "d"(2.0) : "memory");
                 }
             }
+        } else if (mode == 4) {
+            // st.async (STAS) with byte-counted completion on the receiver's mbarrier: no release / acquire round trip
+            if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sm(bar)), "r"(bytes) : "memory");
+            if (tid < 256) {
+                for (int p = 0; p < npeers; ++p) {
+                    const unsigned r = mapa(sm(dst), (me + 1 + p) % cs), rb = mapa(sm(bar), (me + 1 + p) % cs);
+                    for (unsigned e = tid; e < per_peer / 16; e += 256)
+                        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];"
+                                     ::"r"(r + e * 16), "d"(1.0 + it), "d"(2.0), "r"(rb) : "memory");
+                }
+            }
+            mbar_wait(sm(bar), it & 1);
+            t_data += clock64() - t_it;
         } else if (mode == 3) {
             // the receiver expects `bytes` in total on its own barrier; `issuers` warps issue the copies, round robin
             if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sm(bar)), "r"(bytes) : "memory");
@@ -92,7 +108,7 @@ __global__ void __launch_bounds__(384, 1) k_x(int mode, int cs, unsigned bytes, 
         cluster_sync_all();
     }
     long long t1 = clock64();
-    if (tid == 0) out[blockIdx.x] = (t1 - t0) / iters;
+    if (tid == 0) out[blockIdx.x] = mode == 4 ? t_data / iters : (t1 - t0) / iters;
     if (dst[5] == -1.0) out[0] = 0;   // keep the stores alive
 }
 
@@ -134,6 +150,9 @@ int main() {
                 {1, 49152, 3, 1, "st v2.f64 48 KB -> 3 peers"},
                 {2, 24576, 1, 1, "st f64 pairs 24 KB -> 1 peer"},
                 {2, 49152, 3, 1, "st f64 pairs 48 KB -> 3 peers"},
+                {4, 24576, 1, 1, "st.async v2 24 KB -> 1 peer (to data)"},
+                {4, 49152, 1, 1, "st.async v2 48 KB -> 1 peer (to data)"},
+                {4, 49152, 3, 1, "st.async v2 48 KB -> 3 peers (to data)"},
                 {3, 24576, 1, 1, "bulk 24 KB -> 1 peer, 1 issuer"},
                 {3, 49152, 1, 1, "bulk 48 KB -> 1 peer, 1 issuer"},
                 {3, 49152, 1, 4, "bulk 48 KB -> 1 peer, 4 issuers"},

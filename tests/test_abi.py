@@ -41,6 +41,8 @@ def test_library_contains_sm100a_dmma_code(built_lib):
     assert "DMMA.8x8x4" in out, "the resident kernel must issue FP64 tensor-core instructions"
     # the persistent streamed kernel is fed by TMA bulk copies with mbarrier completion
     assert "UBLKCP" in out and "SYNCS.ARRIVE.TRANS64" in out, "k_stream_tma must issue cp.async.bulk (TMA) copies"
+    # the cluster-resident kernel separates its stages with the hardware cluster barrier
+    assert "k_cluster_eo" in out and "UCGABAR_ARV" in out and "UCGABAR_WAIT" in out
 
 
 def test_batch_beyond_the_grid_limit_is_refused(built_lib):

@@ -240,7 +240,9 @@ def test_streamed_even_odd_kernel_large_grids(ldc, N):
     names = {"tiled": "tiled", "stream_eo": "k_stream_stage", "stream_tma": "k_stream_tma"}
     for path in names:
         with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
-            assert s.kernel_name == names[path]
+            # 50 <= N <= 65 with a cluster per cavity: the cluster-resident shape of the persistent streamed path
+            want = "k_cluster_eo" if (path == "stream_tma" and 50 <= N <= 65) else names[path]
+            assert s.kernel_name == want
             s.set_cases(Re, corner_smoothing=[0.15, 0.05]).set_state(u, v, p)
             s.step(2, freeze_pressure=(N % 2 == 0))
             r = s.step(3, freeze_pressure=(N % 2 == 0))   # second call: state comes back from the rotated buffers

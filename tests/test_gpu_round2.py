@@ -275,3 +275,64 @@ def test_config5_on_the_wide_tiles(ldc, golden, monkeypatch):
     """The config-5 pin (N = 128, Re = 5000, 200 steps from the prolongated state) on the 16 x 32 tile shape."""
     monkeypatch.setenv("LDC_STREAM_CW", "2")
     test_config5_n128_re5000_from_the_prolongated_state(ldc, golden, "stream_tma")
+
+
+@pytest.mark.parametrize("N,B", [(64, 2), (50, 3), (57, 21), (65, 1)])
+def test_cluster_resident_kernel(ldc, monkeypatch, N, B):
+    """k_cluster_eo (50 <= N <= 65: a cavity over a cluster of 8 CTAs, state in distributed shared memory, LDC_STREAM_CW=3;
+    AUTO takes it on the streamed path when every cavity can have a cluster): against the tiled FMA path and the 16 x 16
+    TMA shape from a BC-violating random state with both pressure semantics, a continued run, bitwise reproducible, and
+    -- B = 21: more cavities than clusters -- independent of the batch-mates while cavities migrate between clusters."""
+    rng = np.random.default_rng(N)
+    u, v = 0.1 * rng.standard_normal((2, B, N + 1, N + 1))
+    p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
+    Re = np.linspace(300.0, 2000.0, B)
+    out = {}
+    for path, cw in (("tiled", None), ("stream_tma", "3"), ("stream_tma", "3"), ("stream_tma", "1")):
+        if cw:
+            monkeypatch.setenv("LDC_STREAM_CW", cw)
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            if cw:
+                assert s.kernel_name == ("k_cluster_eo" if cw == "3" else "k_stream_tma")
+            s.set_cases(Re, corner_smoothing=0.1).set_state(u, v, p)
+            s.step(2, freeze_pressure=(N % 2 == 0))
+            r = s.step(4 if B < 10 else 9, freeze_pressure=(N % 2 == 0))
+            res = (*s.get_state(), r)
+        key = path + (cw or "")
+        if key in out:
+            assert all(np.array_equal(a, c) for a, c in zip(out[key], res)), "not bitwise reproducible"
+        out[key] = res
+    for key in ("stream_tma3", "stream_tma1"):
+        for a, c in zip(out[key][:3], out["tiled"][:3]):
+            assert rel(a, c) < 1e-10, key
+        assert np.allclose(out[key][3], out["tiled"][3], rtol=1e-8), key
+    if B > 1:   # a cavity's trajectory does not depend on its batch-mates
+        monkeypatch.setenv("LDC_STREAM_CW", "3")
+        with ldc.BatchedSpectralLDC(N, batch=1, path="stream_tma") as s:
+            s.set_cases(Re[-1:], corner_smoothing=0.1).set_state(u[-1:], v[-1:], p[-1:])
+            s.step(2, freeze_pressure=(N % 2 == 0))
+            s.step(4 if B < 10 else 9, freeze_pressure=(N % 2 == 0))
+            solo = s.get_state()
+        assert all(np.array_equal(a[0], c[-1]) for a, c in zip(solo, out["stream_tma3"][:3]))
+
+
+def test_cluster_resident_kernel_to_tolerance(ldc, monkeypatch):
+    """A to-tolerance solve on k_cluster_eo: per-cavity convergence, iteration counts equal to the launch-per-stage streamed
+    kernels, and AUTO's choice for few cavities on these grids."""
+    N, B = 52, 5
+    Re = np.linspace(60.0, 200.0, B)
+    res = {}
+    for path in ("stream_eo", "stream_tma"):
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            if path == "stream_tma":
+                assert s.kernel_name == "k_cluster_eo"
+            s.set_cases(Re).init_state()
+            r = s.solve(1e-4, 100000, warmup=0)
+            res[path] = (r.iterations.copy(), r.converged.copy(), s.get_state())
+    assert res["stream_tma"][1].all()
+    assert len(set(res["stream_tma"][0].tolist())) > 1   # the cavities stop at different iterations
+    assert np.array_equal(res["stream_tma"][0], res["stream_eo"][0])
+    for a, c in zip(res["stream_tma"][2], res["stream_eo"][2]):
+        assert rel(a, c) < 1e-9
+    with ldc.BatchedSpectralLDC(64, batch=8) as s:   # AUTO: few cavities on the largest resident grid
+        assert s.kernel_name == "k_cluster_eo"
