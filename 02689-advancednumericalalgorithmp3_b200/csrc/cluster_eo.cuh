@@ -331,8 +331,12 @@ struct CEGeo {
 
 // one block value pair of the thread into every panel that holds it: columns j0, j0 + 1 of row i
 //   offR: double offset inside a row panel (a double2), offC: inside a column panel (second column 4 doubles further on)
-__device__ __forceinline__ void ce_publish(const CESmem& S, const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
-    // remote panels first (the SM-to-SM network is the slow part), the CTA's own by plain shared-memory stores
+__device__ __forceinline__ void ce_publish_local(const CESmem& S, unsigned offR, unsigned offC, double x0, double x1) {
+    *reinterpret_cast<double2*>(S.rp + offR) = make_double2(x0, x1);
+    S.cp[offC] = x0;
+    S.cp[offC + 4] = x1;
+}
+__device__ __forceinline__ void ce_publish_remote(const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
     const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
 #pragma unroll
     for (int r = 1; r < CE_CR; ++r) {
@@ -341,9 +345,6 @@ __device__ __forceinline__ void ce_publish(const CESmem& S, const CEGeo& G, unsi
     }
 #pragma unroll
     for (int c = 1; c < CE_CC; ++c) ce_sta2(G.rrow[c] + offR * 8u, x0, x1, G.rrow[c] + G.bar_off);
-    *reinterpret_cast<double2*>(S.rp + offR) = make_double2(x0, x1);
-    S.cp[offC] = x0;
-    S.cp[offC + 4] = x1;
 }
 
 // After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): swap accumulator halves
@@ -355,7 +356,7 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
                                           bool bc_lines, double dt, int fld, int lane, const double (&uo)[4][2],
                                           const double (&vo)[4][2], const double (&fN)[4][2], const double (&pN)[4][2],
                                           double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2],
-                                          long long* __restrict__ tdbg) {
+                                          double (&fn)[4][2], double (&pn)[4][2], long long* __restrict__ tdbg) {
     const int g = lane >> 2, t = lane & 3, tid64 = fld * 32 + lane, warp = 2 * X + fld;
     const int m = P.m, h = G.h, centre = (m & 1) ? h - 1 : -1;
     const int i = G.r0 + g, j0 = G.c0 + 8 * X + 2 * t;
@@ -392,7 +393,6 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
     const double adt = rk_alpha(stage) * dt;
     const bool last = (stage == 3);
     double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
-    double fn[4][2];
     {
         const double wi = (i == centre) ? 0.5 : 1.0;
         const double w0 = 4.0 * wi * (j0 == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j0 + 1 == centre ? 0.5 : 1.0);
@@ -436,28 +436,20 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
     __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red; S.edgep has been read
     // frozen pressure (SGSolver): every stage takes grad(p^n), so stages 0..2 leave the pressure blocks alone
     const bool keep_pn = P.freeze && stage != 3;
-    double pn[4][2];
+    const unsigned offR = (unsigned)(((j0 >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j0 & 3));
+    const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j0 & 15) * 4 + (i & 3));
+    // the CTA's own panels (its own warps have all read them: the barrier above); the other CTAs' by the caller
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ce_publish_local(S, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
     if (fld == 0 && !keep_pn) {
+        const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const double dv0 = b1[q][0] + S.x[(X * 8 + q * 2 + 0) * 32 + lane];
             const double dv1 = b1[q][1] + S.x[(X * 8 + q * 2 + 1) * 32 + lane];
             pn[q][0] = pN[q][0] + adt * (-V.beta2 * dv0);
             pn[q][1] = pN[q][1] + adt * (-V.beta2 * dv1);
-        }
-    }
-    if (tdbg) tdbg[5] = clock64();
-    ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
-    if (tdbg) tdbg[6] = clock64();
-    {
-        const unsigned offR = (unsigned)(((j0 >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j0 & 3));
-        const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j0 & 15) * 4 + (i & 3));
-#pragma unroll
-        for (int q = 0; q < 4; ++q) ce_publish(S, G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
-        if (fld == 0 && !keep_pn) {
-            const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) ce_publish(S, G, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
+            ce_publish_local(S, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
         }
     }
     if (!bc_lines) {
@@ -488,8 +480,8 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             for (int q = 0; q < 6; ++q) ce_sta(dst + 8 * q, o[q], bar);
         }
     }
-    if (tdbg) tdbg[7] = clock64();
-    __syncthreads();   // the CTA's own panels are complete: the caller runs the local part of the next K loop, then the barrier
+    __syncthreads();   // the CTA's own panels are complete: the caller runs the local part of the next K loop
+    if (tdbg) tdbg[5] = clock64();
 }
 
 // The persistent kernel.  grid = clusters x 8 (cluster dimension 8 set at launch); a cluster pops a cavity from the queue,
@@ -502,9 +494,10 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
     const int X = warp >> 1, fld = warp & 1, g = lane >> 2, t = lane & 3;
     const int fo = g * 4 + t;   // the thread's fragment offset inside a block (A: row g; B: column g; k = t)
     const int m = G.m, h = G.h, n1 = G.n1;
-    // LDC_S2_DEBUG: clock samples of warp 0 of CTA 0 per stage -- [0] stage start, [1] K loop done, [2] own elements read,
-    // [3] accumulator swap done, [4] assembly done, [5] pressure update done, [6] every CTA has read its panels, [7] stage
-    // output stored, [8] stage output visible everywhere
+    // LDC_S2_DEBUG: clock samples of warp 0 of CTA 0 per stage -- [0] stage start, [1] remote part of the K loop done, [2] own
+    // elements read, [3] accumulator swap done, [4] assembly done, [5] own panels written, [6] every CTA has read its panels,
+    // [10] local part of the next K loop + the stores to the other CTAs done, [8] the others' output has arrived; [9] cycles
+    // of the end-of-step reduction in front of the stage
     const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && tid == 0;
     int dbg_stage = 0;
     for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
@@ -592,18 +585,41 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
             active = st.active != 0;
             dt = V.cfl / (lam_x + lam_y);
         };
-        double a1[4][2][2], a2[4][2][2], aL[4][2][2];
-        auto start_stage = [&]() {   // accumulators to zero, then the part of the K loop that needs no one else's output
+        // Start of a stage: accumulators to zero, then the part of the K loop that needs no one else's output (three
+        // half-steps, ce_local_part) -- with the st.async stores of the previous stage's output to the other CTAs' panels
+        // (fn, pn: what ce_finish has just put into this CTA's own) issued in between, one parity block at a time: the
+        // SM-to-SM network takes ~20 B/clk out of an SM, and the DMMAs run while the stores queue up for it.
+        double a1[4][2][2], a2[4][2][2], aL[4][2][2], fn[4][2], pn[4][2];
+        const int i_own = G.r0 + g, j_own = G.c0 + 8 * X + 2 * t;
+        const unsigned offR = (unsigned)(((j_own >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j_own & 3));
+        const unsigned offC = (unsigned)(((i_own >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j_own & 15) * 4 + (i_own & 3));
+        auto send = [&](int q, bool with_p) {
+            ce_publish_remote(G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
+            if (with_p)
+                ce_publish_remote(G, offR + (S2_BP - S2_BU + q) * CE_ABLK, offC + (S2_BP - S2_BU + q) * CE_BBLK, pn[q][0], pn[q][1]);
+        };
+        auto start_stage = [&](bool publish, bool with_p) {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
-            if (fld == 0) ce_local_part<true>(S.rp, S.cp, fo, X, G.trow, G.tcol, 0, a1, a2, aL);
-            else ce_local_part<false>(S.rp, S.cp, fo, X, G.trow, G.tcol, 1, a1, a2, aL);
+            const double* rp = S.rp + fo;
+            const double* cp = S.cp + fo;
+            const int ka = 2 * G.trow + X, kb0 = 4 * G.tcol + X, kb1 = kb0 + 2;
+            if (publish) send(0, with_p);
+            if (fld == 0) ce_kstep_opsA<true>(rp + (size_t)ka * (S2_NB * CE_ABLK), cp + (size_t)ka * (S2_NB * CE_BBLK), 0, a1, aL);
+            else ce_kstep_opsA<false>(rp + (size_t)ka * (S2_NB * CE_ABLK), cp + (size_t)ka * (S2_NB * CE_BBLK), 1, a1, aL);
+            if (publish) send(1, with_p);
+            if (fld == 0) ce_kstep_opsB<true>(rp + (size_t)kb0 * (S2_NB * CE_ABLK), cp + (size_t)kb0 * (S2_NB * CE_BBLK), 0, a2, aL);
+            else ce_kstep_opsB<false>(rp + (size_t)kb0 * (S2_NB * CE_ABLK), cp + (size_t)kb0 * (S2_NB * CE_BBLK), 1, a2, aL);
+            if (publish) send(2, with_p);
+            if (fld == 0) ce_kstep_opsB<true>(rp + (size_t)kb1 * (S2_NB * CE_ABLK), cp + (size_t)kb1 * (S2_NB * CE_BBLK), 0, a2, aL);
+            else ce_kstep_opsB<false>(rp + (size_t)kb1 * (S2_NB * CE_ABLK), cp + (size_t)kb1 * (S2_NB * CE_BBLK), 1, a2, aL);
+            if (publish) send(3, with_p);
         };
-        start_stage();
+        start_stage(false, false);
         for (long long step = 0; step < nsteps; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
                 // The previous step's reduction: convergence, dt.  Should the cavity have gone inactive, the K loop parts
@@ -651,12 +667,12 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 }
                 ce_arrive_relaxed();   // this CTA has read its panels (the wait is in ce_finish, behind the assembly)
                 if (tdbg) tdbg[2] = clock64();
-                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
-                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
+                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, fn, pn, tdbg);
+                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, fn, pn, nullptr);
                 bc_lines = true;
-                // The local part of the next stage's K loop runs while the stores cross the SM-to-SM network.  They are
-                // st.async stores that count their bytes on the receiver's mbarrier: no release fence, no barrier round trip.
-                start_stage();
+                ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
+                if (tdbg) tdbg[6] = clock64();
+                start_stage(true, fld == 0 && !(P.freeze && stage != 3));
                 if (tdbg) tdbg[10] = clock64();
                 mbar_wait(S.databar, nphase & 1);   // everyone else's part of the stage output is in this CTA's panels
                 ++nphase;
