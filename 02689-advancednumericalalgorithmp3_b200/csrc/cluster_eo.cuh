@@ -12,9 +12,9 @@
 //   * the end-of-step sums (convergence norms, maxima for the next dt) are exchanged the same way and reduced redundantly,
 //     in fixed order, by every CTA; status and state go back to the record in L2 only at the end of a visit.
 // What bounds it: the SM-to-SM network takes ~20 B/clk out of an SM (scripts/dsmem_bw.cu, profiles/r02_dsmem_bw.txt), and
-// a stage sends 48 KB per CTA; the K loop of a stage is 160 DMMAs per warp, one warp per SM sub-partition.
-// Four warps per CTA: (k-group X: even | odd k4-steps) x (u | v equation), each over the whole 8 x 16 tile; the groups swap
-// accumulator halves and each runs the epilogue of one 8-column half (as k_stream_tma does).
+// a stage sends 48 KB per CTA; the K loop of a stage is 80 DMMAs per warp, two warps per SM sub-partition.
+// Eight warps per CTA: (k-group X: even | odd k4-steps) x (u | v equation) x (8-column half of the tile); the two k-groups
+// swap accumulator halves -- each thread keeps ONE of its two columns -- and both run the epilogue, one element per thread.
 // Records, pack / unpack kernels, queue and host-side driver are those of stream_tma.cuh (ldc_abi.cu picks this kernel as a
 // third "shape" of the persistent streamed path when every cavity still iterating can have a cluster).
 #pragma once
@@ -26,14 +26,14 @@ constexpr int CE_NK4 = 8;                        // k4-steps of a 32-wide parity
 constexpr int CE_TR = 8, CE_TC = 16;             // tile of a CTA: rows x columns
 constexpr int CE_CR = 32 / CE_TR, CE_CC = 32 / CE_TC;
 constexpr int CE_CLUSTER = CE_CR * CE_CC;        // 8 CTAs per cavity; rank = row tile * CE_CC + column tile
-constexpr int CE_THREADS = 128;
+constexpr int CE_THREADS = 256;
 constexpr int CE_ABLK = CE_TR * 4, CE_BBLK = CE_TC * 4;      // doubles per block of the row / column panel
 constexpr int CE_RP = CE_NK4 * S2_NB * CE_ABLK;              // row panel    [kk][blk][8 r][4]
 constexpr int CE_CP = CE_NK4 * S2_NB * CE_BBLK;              // column panel [kk][blk][16 c][4]
-constexpr int CE_EXCH = 2 * 24 * 64;                         // accumulator swap: [group][24 values][64 threads]
+constexpr int CE_EXCH = 2 * 12 * 128;                        // accumulator swap: [group][12 values][128 threads]
 constexpr size_t CE_SMEM_DOUBLES = (size_t)CE_RP + CE_CP + CE_EXCH
                                    + 8 * S2_HP + 16 * S2_HP  // boundary-column vectors, boundary lines in parity form
-                                   + 2 * 8 * 32              // dv/dy hand-over v warps -> u warps
+                                   + 4 * 4 * 32              // dv/dy hand-over v warps -> u warps
                                    + CE_CLUSTER * 8 + 64 + 16 + 2;   // partials of the 8 tiles, reduction scratch, step info, cavity + mbarrier
 
 struct CESmem {
@@ -47,7 +47,7 @@ struct CESmem {
         vec = exch + CE_EXCH;
         edgep = vec + 8 * S2_HP;
         x = edgep + 16 * S2_HP;
-        part = x + 2 * 8 * 32;
+        part = x + 4 * 4 * 32;
         red = part + CE_CLUSTER * 8;
         step = red + 64;   // [2..5] boundary-line sums of a first step, [6..7] max |lid|, [8..11] sums of later steps
         cavity = reinterpret_cast<int*>(step + 16);
@@ -91,23 +91,24 @@ __device__ __forceinline__ void ce_arrive_relaxed() { asm volatile("barrier.clus
 __device__ __forceinline__ void ce_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 // ---- one k4-step of the warp's contractions (cf. s2_chunk), in two halves ---------------------------------------------
+// A warp computes an 8 x 8 sub-tile of every parity block of its field (accumulators [block][2]: the thread's two columns).
 //   A = row panel at this k4-step + the thread's A-fragment offset (g * 4 + t), block b at A + b * CE_ABLK
-//   Bp = column panel likewise,                                                  block b at Bp + b * CE_BBLK (+ 32: second half)
+//   Bp = column panel likewise, + 32 for the second 8-column half,               block b at Bp + b * CE_BBLK
 // ce_kstep_opsA: operator rows (row panel) x state columns (column panel) -- needs the state rows 4 kk .. 4 kk + 3, which
 //   the CTAs of row tile kk / 2 produce;
 // ce_kstep_opsB: state rows (row panel) x operator rows at the tile's columns (column panel) -- needs the state columns
 //   4 kk .. 4 kk + 3, which the CTAs of column tile kk / 4 produce.
-// So three of a warp's eight half-steps work on state this CTA has produced itself (ce_local_part).
+// So three of a warp's eight half-steps work on state this CTA has produced itself: opsA at k4-step 2 trow + X, opsB at
+// 4 tcol + X and 4 tcol + 2 + X (k-group X takes the k4-steps X, X + 2, X + 4, X + 6).  They run right after the CTA's own
+// stores of the previous stage, while the other CTAs' stores are still crossing the SM-to-SM network; the other five follow
+// once everything has arrived.  (The order of the accumulation differs from tile to tile but is fixed for a tile.)
 template <bool P_LEFT>
 __device__ __forceinline__ void ce_kstep_opsA(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
-                                              double (&a1)[4][2][2], double (&aL)[4][2][2]) {
-    constexpr int NT = 2;
+                                              double (&a1)[4][2], double (&aL)[4][2]) {
     const int bf = S2_BU + 4 * fld;
-    double FB[4][NT], dA[2], ddA[2];
+    double FB[4], dA[2], ddA[2];
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) FB[q][nt] = Bp[(bf + q) * CE_BBLK + nt * 32];
+    for (int q = 0; q < 4; ++q) FB[q] = Bp[(bf + q) * CE_BBLK];
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
         dA[a] = A[a * CE_ABLK];
@@ -116,106 +117,70 @@ __device__ __forceinline__ void ce_kstep_opsA(const double* __restrict__ A, cons
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int b = 0; b < 2; ++b)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-                dmma884(a1[2 * a + b][nt][0], a1[2 * a + b][nt][1], dA[a], FB[2 * (1 - a) + b][nt]);
-                dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
-            }
+        for (int b = 0; b < 2; ++b) {
+            dmma884(a1[2 * a + b][0], a1[2 * a + b][1], dA[a], FB[2 * (1 - a) + b]);
+            dmma884(aL[2 * a + b][0], aL[2 * a + b][1], ddA[a], FB[2 * a + b]);
+        }
     if (P_LEFT) {
-        double gA[2], PB[4][NT];
+        double gA[2], PB[4];
 #pragma unroll
         for (int a = 0; a < 2; ++a) gA[a] = A[(4 + a) * CE_ABLK];
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) PB[q][nt] = Bp[(S2_BP + q) * CE_BBLK + nt * 32];
+        for (int q = 0; q < 4; ++q) PB[q] = Bp[(S2_BP + q) * CE_BBLK];
 #pragma unroll
         for (int a = 0; a < 2; ++a)
 #pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt)
-                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
+            for (int b = 0; b < 2; ++b) dmma884(aL[2 * a + b][0], aL[2 * a + b][1], gA[a], PB[2 * (1 - a) + b]);
     }
 }
 template <bool P_LEFT>
 __device__ __forceinline__ void ce_kstep_opsB(const double* __restrict__ A, const double* __restrict__ Bp, int fld,
-                                              double (&a2)[4][2][2], double (&aL)[4][2][2]) {
-    constexpr int NT = 2;
+                                              double (&a2)[4][2], double (&aL)[4][2]) {
     const int bf = S2_BU + 4 * fld;
-    double FA[4], dB[2][NT], ddB[2][NT];
+    double FA[4], dB[2], ddB[2];
 #pragma unroll
     for (int q = 0; q < 4; ++q) FA[q] = A[(bf + q) * CE_ABLK];
 #pragma unroll
-    for (int b = 0; b < 2; ++b)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            dB[b][nt] = Bp[b * CE_BBLK + nt * 32];
-            ddB[b][nt] = Bp[(2 + b) * CE_BBLK + nt * 32];
-        }
+    for (int b = 0; b < 2; ++b) {
+        dB[b] = Bp[b * CE_BBLK];
+        ddB[b] = Bp[(2 + b) * CE_BBLK];
+    }
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int b = 0; b < 2; ++b)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-                dmma884(a2[2 * a + b][nt][0], a2[2 * a + b][nt][1], FA[2 * a + (1 - b)], dB[b][nt]);
-                dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
-            }
+        for (int b = 0; b < 2; ++b) {
+            dmma884(a2[2 * a + b][0], a2[2 * a + b][1], FA[2 * a + (1 - b)], dB[b]);
+            dmma884(aL[2 * a + b][0], aL[2 * a + b][1], FA[2 * a + b], ddB[b]);
+        }
     if (!P_LEFT) {
-        double PA[4], gB[2][NT];
+        double PA[4], gB[2];
 #pragma unroll
         for (int q = 0; q < 4; ++q) PA[q] = A[(S2_BP + q) * CE_ABLK];
 #pragma unroll
-        for (int b = 0; b < 2; ++b)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) gB[b][nt] = Bp[(4 + b) * CE_BBLK + nt * 32];
+        for (int b = 0; b < 2; ++b) gB[b] = Bp[(4 + b) * CE_BBLK];
 #pragma unroll
         for (int a = 0; a < 2; ++a)
 #pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt)
-                    dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], PA[2 * a + (1 - b)], gB[b][nt]);
+            for (int b = 0; b < 2; ++b) dmma884(aL[2 * a + b][0], aL[2 * a + b][1], PA[2 * a + (1 - b)], gB[b]);
     }
 }
-// The K loop of a stage for k-group X (k4-steps X, X + 2, X + 4, X + 6) in two parts.  Local part: the half-steps whose state
-// operand this CTA produces itself -- opsA at k4-step 2 trow + X, opsB at 4 tcol + X and 4 tcol + 2 + X.  It runs right
-// after the CTA's own stores of the previous stage, while the other CTAs' stores are still crossing the SM-to-SM network.
-// Remote part: the other five half-steps, once the cluster barrier says that everything has arrived.  (The order of the
-// accumulation differs from tile to tile but is fixed for a tile.)
+// the five half-steps of k-group X that need other CTAs' output
 template <bool P_LEFT>
-__device__ __forceinline__ void ce_local_part(const double* __restrict__ rp, const double* __restrict__ cp, int fo, int X, int trow,
-                                              int tcol, int fld, double (&a1)[4][2][2], double (&a2)[4][2][2],
-                                              double (&aL)[4][2][2]) {
-    {
-        const int kk = 2 * trow + X;
-        ce_kstep_opsA<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a1, aL);
-    }
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-        const int kk = 4 * tcol + 2 * c + X;
-        ce_kstep_opsB<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a2, aL);
-    }
-}
-template <bool P_LEFT>
-__device__ __forceinline__ void ce_remote_part(const double* __restrict__ rp, const double* __restrict__ cp, int fo, int X, int trow,
-                                               int tcol, int fld, double (&a1)[4][2][2], double (&a2)[4][2][2],
-                                               double (&aL)[4][2][2]) {
+__device__ __forceinline__ void ce_remote_part(const double* __restrict__ rp, const double* __restrict__ cp, int X, int trow,
+                                               int tcol, int fld, double (&a1)[4][2], double (&a2)[4][2], double (&aL)[4][2]) {
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
         const int kk = 4 * (1 - tcol) + 2 * c + X;
-        ce_kstep_opsB<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a2, aL);
+        ce_kstep_opsB<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK), cp + (size_t)kk * (S2_NB * CE_BBLK), fld, a2, aL);
     }
 #pragma unroll
     for (int c = 1; c < CE_CR; ++c) {
         const int kk = 2 * ((trow + c) % CE_CR) + X;
-        ce_kstep_opsA<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK) + fo, cp + (size_t)kk * (S2_NB * CE_BBLK) + fo, fld, a1, aL);
+        ce_kstep_opsA<P_LEFT>(rp + (size_t)kk * (S2_NB * CE_ABLK), cp + (size_t)kk * (S2_NB * CE_BBLK), fld, a1, aL);
     }
 }
 
-// 4 sums + 2 NaN-propagating maxima across the four warps, fixed order, result in every thread.
+// 4 sums + 2 NaN-propagating maxima across the eight warps, fixed order, result in every thread.
 __device__ __forceinline__ void ce_block_reduce(double (&s)[4], double (&mx)[2], double* sRed, int warp, int lane) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -329,96 +294,154 @@ struct CEGeo {
     }
 };
 
-// one block value pair of the thread into every panel that holds it: columns j0, j0 + 1 of row i
-//   offR: double offset inside a row panel (a double2), offC: inside a column panel (second column 4 doubles further on)
-__device__ __forceinline__ void ce_publish_local(const CESmem& S, unsigned offR, unsigned offC, double x0, double x1) {
-    *reinterpret_cast<double2*>(S.rp + offR) = make_double2(x0, x1);
-    S.cp[offC] = x0;
-    S.cp[offC + 4] = x1;
-}
-__device__ __forceinline__ void ce_publish_remote(const CEGeo& G, unsigned offR, unsigned offC, double x0, double x1) {
-    const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
+// Boundary-line corrections + nonlinear assembly at ONE element (row i, column j) of every parity block: s2_assemble for a
+// single column.
+//   in: b1 = D f, b2 = f D^T, bL = linear part (the thread's values at this column);  out: bL = momentum residual blocks,
+//   b1 = d(field)/dx (u warps) or d(field)/dy (v warps)
+__device__ __forceinline__ void ce_assemble_col(const double* __restrict__ sVec, const double* __restrict__ sEdgeF, double nu,
+                                                bool bc_lines, bool is_u, int i, int j, const double (&uo)[4], const double (&vo)[4],
+                                                double (&b1)[4], const double (&b2)[4], double (&bL)[4]) {
+    constexpr int HP = S2_HP;
+    double dx[4], dy[4];
+    if (bc_lines) {   // W = E = S = 0: only the lid line contributes, and only to the y-derivatives
 #pragma unroll
-    for (int r = 1; r < CE_CR; ++r) {
-        ce_sta(G.rcol[r] + offC * 8u, x0, G.rcol[r] + cp_to_bar);
-        ce_sta(G.rcol[r] + offC * 8u + 32u, x1, G.rcol[r] + cp_to_bar);
+        for (int b = 0; b < 2; ++b) {
+            const double dNj = sVec[(2 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const int q = 2 * a + b;
+                const double Ni = sEdgeF[(6 + a) * HP + i];
+                dx[q] = b1[q];
+                dy[q] = fma(Ni, dNj, b2[q]);
+                bL[q] = fma(nu * Ni, ddNj, bL[q]);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const double Wj = sEdgeF[(0 + b) * HP + j], Ej = sEdgeF[(2 + b) * HP + j];
+            const double d0j = sVec[(0 + b) * HP + j], dNj = sVec[(2 + b) * HP + j];
+            const double dd0j = sVec[(4 + b) * HP + j], ddNj = sVec[(6 + b) * HP + j];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const int q = 2 * a + b;
+                const double d0i = sVec[(0 + a) * HP + i], dNi = sVec[(2 + a) * HP + i];
+                const double dd0i = sVec[(4 + a) * HP + i], ddNi = sVec[(6 + a) * HP + i];
+                const double Si = sEdgeF[(4 + a) * HP + i], Ni = sEdgeF[(6 + a) * HP + i];
+                dx[q] = b1[q] + d0i * Wj + dNi * Ej;
+                dy[q] = b2[q] + Si * d0j + Ni * dNj;
+                bL[q] += nu * (dd0i * Wj + ddNi * Ej + Si * dd0j + Ni * ddNj);
+            }
+        }
+    }
+    // convective term in parity form: Z2 x Z2 group convolution (see eo_assemble)
+    double cq[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        double c = uo[q] * dx[0];
+#pragma unroll
+        for (int bb = 1; bb < 4; ++bb) c = fma(uo[q ^ bb], dx[bb], c);
+#pragma unroll
+        for (int bb = 0; bb < 4; ++bb) c = fma(vo[q ^ bb], dy[bb], c);
+        cq[q] = c;
     }
 #pragma unroll
-    for (int c = 1; c < CE_CC; ++c) ce_sta2(G.rrow[c] + offR * 8u, x0, x1, G.rrow[c] + G.bar_off);
+    for (int q = 0; q < 4; ++q) {
+        bL[q] -= cq[q];
+        b1[q] = is_u ? dx[q] : dy[q];
+    }
 }
 
-// After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): swap accumulator halves
-// with the other k-group, epilogue of this group's 8-column half, then -- once every CTA of the cluster has read its panels --
-// the stage output into the panels of the CTAs that need it, and the barrier that makes it visible.  cf. s2_finish.
-//   uo, vo: stage input at the thread's elements; fN, pN: phi^n of the warp's field and p^n there (u warps)
+// the thread's value of one block (row i, column j) into the CTA's own panels / into the other CTAs' that hold it
+//   offR / offC: its double offsets inside a row / column panel
+__device__ __forceinline__ void ce_publish_local(const CESmem& S, unsigned offR, unsigned offC, double x) {
+    S.rp[offR] = x;
+    S.cp[offC] = x;
+}
+// The CTA's part of a stage output to the other CTAs' panels, out of its own (complete) panels: its tile's region of the row
+// panel (k4-steps 4 tcol .. + 3: 64 nb double2) to the other CTA of the tile row, of the column panel (k4-steps 2 trow, + 1:
+// 64 nb double2) to the three other CTAs of the tile column; nb = 8 state blocks (u, v) or 12 (u, v, p), which sit back to
+// back.  Thread tid sends the double2 number 256 it + tid of each region: 16-byte st.async stores, 512 contiguous bytes per
+// warp instruction, bytes counted on the receiver's mbarrier.
+__device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it, int nb) {
+    const int e = it * CE_THREADS + (int)threadIdx.x;
+    const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
+    {
+        const int kk = 4 * G.tcol + e / (16 * nb), blk = S2_BU + (e / 16) % nb, w = e % 16;
+        const unsigned off = (unsigned)((kk * S2_NB + blk) * CE_ABLK + 2 * w);
+        const double2 x = *reinterpret_cast<const double2*>(S.rp + off);
+#pragma unroll
+        for (int c = 1; c < CE_CC; ++c) ce_sta2(G.rrow[c] + off * 8u, x.x, x.y, G.rrow[c] + G.bar_off);
+    }
+    {
+        const int kk = 2 * G.trow + e / (32 * nb), blk = S2_BU + (e / 32) % nb, w = e % 32;
+        const unsigned off = (unsigned)((kk * S2_NB + blk) * CE_BBLK + 2 * w);
+        const double2 x = *reinterpret_cast<const double2*>(S.cp + off);
+#pragma unroll
+        for (int r = 1; r < CE_CR; ++r) ce_sta2(G.rcol[r] + off * 8u, x.x, x.y, G.rcol[r] + cp_to_bar);
+    }
+}
+
+// After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): the two k-groups swap
+// accumulator halves -- group X keeps column X of every thread's pair -- then the epilogue of the thread's ONE element
+// (row i, column j) of the four parity blocks: boundary corrections + nonlinear assembly, RK stage update, pressure update on
+// the u warps, the CTA's own panels, at the last stage the tile's partial sums.  cf. s2_finish.  The stores to the other
+// CTAs' panels are the caller's (ce_send, out of the CTA's own panels), between the half-steps of the next K loop's local part.
+//   uo, vo: stage input at the thread's element; fN, pN: phi^n of the warp's field and p^n there (u warps)
 template <int X>
 __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, const CESmem& S, const CEGeo& G, int b, int stage,
-                                          bool bc_lines, double dt, int fld, int lane, const double (&uo)[4][2],
-                                          const double (&vo)[4][2], const double (&fN)[4][2], const double (&pN)[4][2],
-                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2],
-                                          double (&fn)[4][2], double (&pn)[4][2], long long* __restrict__ tdbg) {
-    const int g = lane >> 2, t = lane & 3, tid64 = fld * 32 + lane, warp = 2 * X + fld;
+                                          bool bc_lines, double dt, int fld, int nt, int lane, const double (&uo)[4],
+                                          const double (&vo)[4], const double (&fN)[4], const double (&pN)[4],
+                                          const double (&a1)[4][2], const double (&a2)[4][2], const double (&aL)[4][2],
+                                          long long* __restrict__ tdbg) {
+    const int g = lane >> 2, t = lane & 3, tid128 = (fld * 2 + nt) * 32 + lane, warp = (X * 2 + fld) * 2 + nt;
     const int m = P.m, h = G.h, centre = (m & 1) ? h - 1 : -1;
-    const int i = G.r0 + g, j0 = G.c0 + 8 * X + 2 * t;
-    // ---- split-K hand-over: give away the other half, take the partner's contribution to this half ----
-    double* exch_own = S.exch + X * 24 * 64;
-    const double* exch_other = S.exch + (1 - X) * 24 * 64;
+    const int i = G.r0 + g, j = G.c0 + 8 * nt + 2 * t + X;
+    // ---- split-K hand-over: give away the other column, take the partner's contribution to this one ----
+    double* exch_own = S.exch + X * 12 * 128;
+    const double* exch_other = S.exch + (1 - X) * 12 * 128;
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-            const int idx = q * 2 + hh;
-            exch_own[(0 + idx) * 64 + tid64] = a1[q][1 - X][hh];
-            exch_own[(8 + idx) * 64 + tid64] = a2[q][1 - X][hh];
-            exch_own[(16 + idx) * 64 + tid64] = aL[q][1 - X][hh];
-        }
+    for (int q = 0; q < 4; ++q) {
+        exch_own[(0 + q) * 128 + tid128] = a1[q][1 - X];
+        exch_own[(4 + q) * 128 + tid128] = a2[q][1 - X];
+        exch_own[(8 + q) * 128 + tid128] = aL[q][1 - X];
+    }
     __syncthreads();
     if (tdbg) tdbg[3] = clock64();
-    double b1[4][2], b2[4][2], bL[4][2];
+    double b1[4], b2[4], bL[4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-            const int idx = q * 2 + hh;
-            // group 0's sum first, whichever group does the addition (bitwise the same in both)
-            const double o1 = exch_other[(0 + idx) * 64 + tid64], o2 = exch_other[(8 + idx) * 64 + tid64],
-                         oL = exch_other[(16 + idx) * 64 + tid64];
-            b1[q][hh] = X == 0 ? a1[q][X][hh] + o1 : o1 + a1[q][X][hh];
-            b2[q][hh] = X == 0 ? a2[q][X][hh] + o2 : o2 + a2[q][X][hh];
-            bL[q][hh] = X == 0 ? aL[q][X][hh] + oL : oL + aL[q][X][hh];
-        }
-    if (fld == 0) s2_assemble<true>(S.vec, S.edgep, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
-    else s2_assemble<false>(S.vec, S.edgep + 8 * S2_HP, V.nu, bc_lines, i, j0, uo, vo, b1, b2, bL);
+    for (int q = 0; q < 4; ++q) {
+        // group 0's sum first, whichever group does the addition (bitwise the same in both)
+        const double o1 = exch_other[(0 + q) * 128 + tid128], o2 = exch_other[(4 + q) * 128 + tid128],
+                     oL = exch_other[(8 + q) * 128 + tid128];
+        b1[q] = X == 0 ? a1[q][X] + o1 : o1 + a1[q][X];
+        b2[q] = X == 0 ? a2[q][X] + o2 : o2 + a2[q][X];
+        bL[q] = X == 0 ? aL[q][X] + oL : oL + aL[q][X];
+    }
+    ce_assemble_col(S.vec, S.edgep + (fld ? 8 * S2_HP : 0), V.nu, bc_lines, fld == 0, i, j, uo, vo, b1, b2, bL);
 
     const double adt = rk_alpha(stage) * dt;
     const bool last = (stage == 3);
     double s0 = 0.0, s1 = 0.0, mx = 0.0;   // sum d^2, sum phi_n^2, max |phi_new| of this warp's field
+    double fn[4];
     {
-        const double wi = (i == centre) ? 0.5 : 1.0;
-        const double w0 = 4.0 * wi * (j0 == centre ? 0.5 : 1.0), w1 = 4.0 * wi * (j0 + 1 == centre ? 0.5 : 1.0);
+        const double w = 4.0 * ((i == centre) ? 0.5 : 1.0) * (j == centre ? 0.5 : 1.0);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double fx = fN[q][0], fy = fN[q][1];
-            fn[q][0] = fx + adt * bL[q][0];
-            fn[q][1] = fy + adt * bL[q][1];
+            const double f0 = fN[q];
+            fn[q] = f0 + adt * bL[q];
             if (last) {
-                double d;
-                d = fn[q][0] - fx; s0 = fma(w0 * d, d, s0); s1 = fma(w0 * fx, fx, s1);
-                d = fn[q][1] - fy; s0 = fma(w1 * d, d, s0); s1 = fma(w1 * fy, fy, s1);
+                const double d = fn[q] - f0;
+                s0 = fma(w * d, d, s0);
+                s1 = fma(w * f0, f0, s1);
             }
-            if (fld == 1) {   // dv/dy to the u warp of the same k-group
-                S.x[(X * 8 + q * 2 + 0) * 32 + lane] = b1[q][0];
-                S.x[(X * 8 + q * 2 + 1) * 32 + lane] = b1[q][1];
-            }
+            if (fld == 1) S.x[((X * 2 + nt) * 4 + q) * 32 + lane] = b1[q];   // dv/dy to the u warp of the same elements
         }
         if (last) {
+            double fr[4];
+            eo_to_points(fn[0], fn[1], fn[2], fn[3], fr);
 #pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-                double fr[4];
-                eo_to_points(fn[0][hh], fn[1][hh], fn[2][hh], fn[3][hh], fr);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) mx = nanmax(mx, fabs(fr[q]));
-            }
+            for (int q = 0; q < 4; ++q) mx = nanmax(mx, fabs(fr[q]));
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 s0 += __shfl_xor_sync(0xffffffffu, s0, o);
@@ -436,20 +459,17 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
     __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red; S.edgep has been read
     // frozen pressure (SGSolver): every stage takes grad(p^n), so stages 0..2 leave the pressure blocks alone
     const bool keep_pn = P.freeze && stage != 3;
-    const unsigned offR = (unsigned)(((j0 >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j0 & 3));
-    const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j0 & 15) * 4 + (i & 3));
+    const unsigned offR = (unsigned)(((j >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j & 3));
+    const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j & 15) * 4 + (i & 3));
     // the CTA's own panels (its own warps have all read them: the barrier above); the other CTAs' by the caller
 #pragma unroll
-    for (int q = 0; q < 4; ++q) ce_publish_local(S, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
+    for (int q = 0; q < 4; ++q) ce_publish_local(S, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q]);
     if (fld == 0 && !keep_pn) {
         const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double dv0 = b1[q][0] + S.x[(X * 8 + q * 2 + 0) * 32 + lane];
-            const double dv1 = b1[q][1] + S.x[(X * 8 + q * 2 + 1) * 32 + lane];
-            pn[q][0] = pN[q][0] + adt * (-V.beta2 * dv0);
-            pn[q][1] = pN[q][1] + adt * (-V.beta2 * dv1);
-            ce_publish_local(S, pR + q * CE_ABLK, pC + q * CE_BBLK, pn[q][0], pn[q][1]);
+            const double dv = b1[q] + S.x[((X * 2 + nt) * 4 + q) * 32 + lane];
+            ce_publish_local(S, pR + q * CE_ABLK, pC + q * CE_BBLK, pN[q] + adt * (-V.beta2 * dv));
         }
     }
     if (!bc_lines) {
@@ -467,10 +487,14 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
         }
     }
     if (last && threadIdx.x < CE_CLUSTER) {
-        // this tile's partial sums to every CTA of the cluster.  warps: w = 2 X + fld; u: warps 0, 2; v: warps 1, 3
-        const double o[6] = {S.red[0 * 4 + 0] + S.red[2 * 4 + 0], S.red[0 * 4 + 1] + S.red[2 * 4 + 1],
-                             S.red[1 * 4 + 0] + S.red[3 * 4 + 0], S.red[1 * 4 + 1] + S.red[3 * 4 + 1],
-                             nanmax(S.red[0 * 4 + 2], S.red[2 * 4 + 2]), nanmax(S.red[1 * 4 + 2], S.red[3 * 4 + 2])};
+        // this tile's partial sums to every CTA of the cluster.  warps: w = (2 X + fld) 2 + nt; u: warps 0, 1, 4, 5; v: 2, 3, 6, 7
+        const double* r = S.red;
+        const double o[6] = {((r[0 * 4 + 0] + r[1 * 4 + 0]) + r[4 * 4 + 0]) + r[5 * 4 + 0],
+                             ((r[0 * 4 + 1] + r[1 * 4 + 1]) + r[4 * 4 + 1]) + r[5 * 4 + 1],
+                             ((r[2 * 4 + 0] + r[3 * 4 + 0]) + r[6 * 4 + 0]) + r[7 * 4 + 0],
+                             ((r[2 * 4 + 1] + r[3 * 4 + 1]) + r[6 * 4 + 1]) + r[7 * 4 + 1],
+                             nanmax(nanmax(r[0 * 4 + 2], r[1 * 4 + 2]), nanmax(r[4 * 4 + 2], r[5 * 4 + 2])),
+                             nanmax(nanmax(r[2 * 4 + 2], r[3 * 4 + 2]), nanmax(r[6 * 4 + 2], r[7 * 4 + 2]))};
         if ((int)threadIdx.x == G.rank) {
 #pragma unroll
             for (int q = 0; q < 6; ++q) S.part[G.rank * 8 + q] = o[q];
@@ -485,14 +509,14 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
 }
 
 // The persistent kernel.  grid = clusters x 8 (cluster dimension 8 set at launch); a cluster pops a cavity from the queue,
-// advances it `chunk` steps and hands it back.  128 threads: warp w = 2 X + fld.
+// advances it `chunk` steps and hands it back.  256 threads: warp w = (2 X + fld) 2 + nt.
 __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) {
     extern __shared__ __align__(16) double smem[];
     const CESmem S(smem);
     const CEGeo G(P, S);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int X = warp >> 1, fld = warp & 1, g = lane >> 2, t = lane & 3;
-    const int fo = g * 4 + t;   // the thread's fragment offset inside a block (A: row g; B: column g; k = t)
+    const int X = warp >> 2, fld = (warp >> 1) & 1, nt = warp & 1, g = lane >> 2, t = lane & 3;
+    const int fo = g * 4 + t;   // the thread's fragment offset inside a block (A: row g; B: column 8 nt + g; k = t)
     const int m = G.m, h = G.h, n1 = G.n1;
     // LDC_S2_DEBUG: clock samples of warp 0 of CTA 0 per stage -- [0] stage start, [1] remote part of the K loop done, [2] own
     // elements read, [3] accumulator swap done, [4] assembly done, [5] own panels written, [6] every CTA has read its panels,
@@ -547,9 +571,9 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
         ce_visit_prepare(S, V.first != 0, rec + S2_EDGE_OFF, ul, vl, m, h, n1);   // ends with a CTA barrier
         double dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
         bool bc_lines = !V.first, active = true;
-        double fN[4][2], pN[4][2];
+        double fN[4], pN[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) fN[q][0] = fN[q][1] = pN[q][0] = pN[q][1] = 0.0;
+        for (int q = 0; q < 4; ++q) fN[q] = pN[q] = 0.0;
 
         // end of a step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread (the same numbers
         // everywhere): convergence bookkeeping, dt of the next step
@@ -586,38 +610,29 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
             dt = V.cfl / (lam_x + lam_y);
         };
         // Start of a stage: accumulators to zero, then the part of the K loop that needs no one else's output (three
-        // half-steps, ce_local_part) -- with the st.async stores of the previous stage's output to the other CTAs' panels
-        // (fn, pn: what ce_finish has just put into this CTA's own) issued in between, one parity block at a time: the
-        // SM-to-SM network takes ~20 B/clk out of an SM, and the DMMAs run while the stores queue up for it.
-        double a1[4][2][2], a2[4][2][2], aL[4][2][2], fn[4][2], pn[4][2];
-        const int i_own = G.r0 + g, j_own = G.c0 + 8 * X + 2 * t;
-        const unsigned offR = (unsigned)(((j_own >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j_own & 3));
-        const unsigned offC = (unsigned)(((i_own >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j_own & 15) * 4 + (i_own & 3));
-        auto send = [&](int q, bool with_p) {
-            ce_publish_remote(G, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q][0], fn[q][1]);
-            if (with_p)
-                ce_publish_remote(G, offR + (S2_BP - S2_BU + q) * CE_ABLK, offC + (S2_BP - S2_BU + q) * CE_BBLK, pn[q][0], pn[q][1]);
-        };
+        // half-steps) -- with the st.async stores of the previous stage's output to the other CTAs' panels (ce_send, out of
+        // this CTA's own panels, which ce_finish has just completed) issued in between: the SM-to-SM network takes ~20 B/clk
+        // out of an SM, and the DMMAs run while the stores queue up for it.
+        double a1[4][2], a2[4][2], aL[4][2];
+        const int j_own = G.c0 + 8 * nt + 2 * t + X;   // the thread's element in the epilogue: row r0 + g, column j_own
+        const double* rpf = S.rp + fo;                  // fragment bases: row panel, column panel at the warp's 8-column half
+        const double* cpf = S.cp + fo + nt * 32;
         auto start_stage = [&](bool publish, bool with_p) {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
 #pragma unroll
-                for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) a1[q][nt][hh] = a2[q][nt][hh] = aL[q][nt][hh] = 0.0;
-            const double* rp = S.rp + fo;
-            const double* cp = S.cp + fo;
+                for (int hh = 0; hh < 2; ++hh) a1[q][hh] = a2[q][hh] = aL[q][hh] = 0.0;
             const int ka = 2 * G.trow + X, kb0 = 4 * G.tcol + X, kb1 = kb0 + 2;
-            if (publish) send(0, with_p);
-            if (fld == 0) ce_kstep_opsA<true>(rp + (size_t)ka * (S2_NB * CE_ABLK), cp + (size_t)ka * (S2_NB * CE_BBLK), 0, a1, aL);
-            else ce_kstep_opsA<false>(rp + (size_t)ka * (S2_NB * CE_ABLK), cp + (size_t)ka * (S2_NB * CE_BBLK), 1, a1, aL);
-            if (publish) send(1, with_p);
-            if (fld == 0) ce_kstep_opsB<true>(rp + (size_t)kb0 * (S2_NB * CE_ABLK), cp + (size_t)kb0 * (S2_NB * CE_BBLK), 0, a2, aL);
-            else ce_kstep_opsB<false>(rp + (size_t)kb0 * (S2_NB * CE_ABLK), cp + (size_t)kb0 * (S2_NB * CE_BBLK), 1, a2, aL);
-            if (publish) send(2, with_p);
-            if (fld == 0) ce_kstep_opsB<true>(rp + (size_t)kb1 * (S2_NB * CE_ABLK), cp + (size_t)kb1 * (S2_NB * CE_BBLK), 0, a2, aL);
-            else ce_kstep_opsB<false>(rp + (size_t)kb1 * (S2_NB * CE_ABLK), cp + (size_t)kb1 * (S2_NB * CE_BBLK), 1, a2, aL);
-            if (publish) send(3, with_p);
+            const int nb = with_p ? 12 : 8;
+            if (publish) ce_send(S, G, 0, nb);
+            if (fld == 0) ce_kstep_opsA<true>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 0, a1, aL);
+            else ce_kstep_opsA<false>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 1, a1, aL);
+            if (publish) ce_send(S, G, 1, nb);
+            if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 0, a2, aL);
+            else ce_kstep_opsB<false>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 1, a2, aL);
+            if (publish && with_p) ce_send(S, G, 2, nb);
+            if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 0, a2, aL);
+            else ce_kstep_opsB<false>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 1, a2, aL);
         };
         start_stage(false, false);
         for (long long step = 0; step < nsteps; ++step) {
@@ -641,38 +656,31 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                     mbar_expect_tx(S.databar, 4u * blocks * (CE_TR * CE_TC * 8u) + (stage == 3 ? 7u * 48u : 0u));
                 }
                 // the rest of the K loop: everything has arrived
-                if (fld == 0) ce_remote_part<true>(S.rp, S.cp, fo, X, G.trow, G.tcol, 0, a1, a2, aL);
-                else ce_remote_part<false>(S.rp, S.cp, fo, X, G.trow, G.tcol, 1, a1, a2, aL);
+                if (fld == 0) ce_remote_part<true>(rpf, cpf, X, G.trow, G.tcol, 0, a1, a2, aL);
+                else ce_remote_part<false>(rpf, cpf, X, G.trow, G.tcol, 1, a1, a2, aL);
                 if (tdbg) tdbg[1] = clock64();
-                // the stage input at the thread's own elements (columns 8 X + 2 t, + 1 of the tile), before anyone overwrites it
-                double uo[4][2], vo[4][2];
+                // the stage input at the thread's own element (row i_own, column j_own), before anyone overwrites it
+                double uo[4], vo[4];
                 {
-                    const int j0 = G.c0 + 8 * X + 2 * t;
-                    const double* own = S.rp + (size_t)(j0 >> 2) * (S2_NB * CE_ABLK) + g * 4 + (j0 & 3);
+                    const double* own = S.rp + (size_t)(j_own >> 2) * (S2_NB * CE_ABLK) + g * 4 + (j_own & 3);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const double2 a = *reinterpret_cast<const double2*>(own + (S2_BU + q) * CE_ABLK);
-                        const double2 c = *reinterpret_cast<const double2*>(own + (S2_BV + q) * CE_ABLK);
-                        uo[q][0] = a.x; uo[q][1] = a.y;
-                        vo[q][0] = c.x; vo[q][1] = c.y;
+                        uo[q] = own[(S2_BU + q) * CE_ABLK];
+                        vo[q] = own[(S2_BV + q) * CE_ABLK];
                         if (stage == 0) {   // phi^n of the warp's field (u warps: also p^n), kept for the four stages
-                            fN[q][0] = fld == 0 ? a.x : c.x;
-                            fN[q][1] = fld == 0 ? a.y : c.y;
-                            if (fld == 0) {
-                                const double2 pp = *reinterpret_cast<const double2*>(own + (S2_BP + q) * CE_ABLK);
-                                pN[q][0] = pp.x; pN[q][1] = pp.y;
-                            }
+                            fN[q] = fld == 0 ? uo[q] : vo[q];
+                            if (fld == 0) pN[q] = own[(S2_BP + q) * CE_ABLK];
                         }
                     }
                 }
                 ce_arrive_relaxed();   // this CTA has read its panels (the wait is in ce_finish, behind the assembly)
                 if (tdbg) tdbg[2] = clock64();
-                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, fn, pn, tdbg);
-                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, lane, uo, vo, fN, pN, a1, a2, aL, fn, pn, nullptr);
+                if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
+                else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
                 bc_lines = true;
                 ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
                 if (tdbg) tdbg[6] = clock64();
-                start_stage(true, fld == 0 && !(P.freeze && stage != 3));
+                start_stage(true, !(P.freeze && stage != 3));
                 if (tdbg) tdbg[10] = clock64();
                 mbar_wait(S.databar, nphase & 1);   // everyone else's part of the stage output is in this CTA's panels
                 ++nphase;

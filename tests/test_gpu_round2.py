@@ -339,3 +339,21 @@ def test_cluster_resident_kernel_to_tolerance(ldc, monkeypatch):
         assert rel(a, c) < 1e-9
     with ldc.BatchedSpectralLDC(64, batch=8) as s:   # AUTO: few cavities on the largest resident grid
         assert s.kernel_name == "k_cluster_eo"
+
+
+@pytest.mark.parametrize("path", ["stream_tma", "resident_eo"])
+def test_config5_coarse_level_n64_re5000_from_the_cold_start(ldc, golden, path):
+    """The N = 64 level of BASELINE config 5 pinned to the reference: 600 `MultigridSmoother.step` equivalents at Re = 5000
+    (1 +- 2 %) from the cold start (tests/golden/make_golden_n128.py records the reference's state there as the input of the
+    prolongation) -- on the cluster-resident kernel, which AUTO runs this level on, and on the resident even-odd kernel."""
+    g = golden.n128
+    ncav, k64, _ = (int(x) for x in g["meta"])
+    with ldc.BatchedSpectralLDC(64, batch=ncav, path=path) as s:
+        assert s.kernel_name == ("k_cluster_eo" if path == "stream_tma" else "k_resident_eo")
+        s.set_cases(g["Re"], corner_smoothing=0.15).init_state()
+        s.step(k64, freeze_pressure=False)
+        u, v, p = s.get_state()
+    for b in range(ncav):
+        assert rel(u[b], g[f"c{b}_u64"]) < 1e-10, b
+        assert rel(v[b], g[f"c{b}_v64"]) < 1e-10, b
+        assert rel(p[b], g[f"c{b}_p64"]) < 1e-10, b
