@@ -34,12 +34,13 @@ constexpr int CE_EXCH = 2 * 12 * 128;                        // accumulator swap
 constexpr size_t CE_SMEM_DOUBLES = (size_t)CE_RP + CE_CP + CE_EXCH
                                    + 8 * S2_HP + 16 * S2_HP  // boundary-column vectors, boundary lines in parity form
                                    + 4 * 4 * 32              // dv/dy hand-over v warps -> u warps
-                                   + CE_CLUSTER * 8 + 64 + 16 + 2;   // partials of the 8 tiles, reduction scratch, step info, cavity + mbarrier
+                                   + CE_CLUSTER * 8 + 64 + 16 + 3;   // partials of the 8 tiles, reduction scratch, step info, cavity + mbarriers
 
 struct CESmem {
     double *rp, *cp, *exch, *vec, *edgep, *x, *part, *red, *step;
     int* cavity;
     unsigned long long* databar;   // mbarrier: the other CTAs' part of a stage output has arrived (byte count)
+    unsigned long long* partbar;   // mbarrier: the other CTAs' end-of-step sums have arrived
     __device__ explicit CESmem(double* smem) {
         rp = smem;
         cp = rp + CE_RP;
@@ -52,6 +53,7 @@ struct CESmem {
         step = red + 64;   // [2..5] boundary-line sums of a first step, [6..7] max |lid|, [8..11] sums of later steps
         cavity = reinterpret_cast<int*>(step + 16);
         databar = reinterpret_cast<unsigned long long*>(step + 17);
+        partbar = databar + 1;
     }
 };
 
@@ -361,10 +363,9 @@ __device__ __forceinline__ void ce_publish_local(const CESmem& S, unsigned offR,
 // The CTA's part of a stage output to the other CTAs' panels, out of its own (complete) panels: its tile's region of the row
 // panel (k4-steps 4 tcol .. + 3: 64 nb double2) to the other CTA of the tile row, of the column panel (k4-steps 2 trow, + 1:
 // 64 nb double2) to the three other CTAs of the tile column; nb = 8 state blocks (u, v) or 12 (u, v, p), which sit back to
-// back.  Thread tid sends the double2 number 256 it + tid of each region: 16-byte st.async stores, 512 contiguous bytes per
-// warp instruction, bytes counted on the receiver's mbarrier.
-__device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it, int nb) {
-    const int e = it * CE_THREADS + (int)threadIdx.x;
+// back.  ce_send_slot sends the double2 number e of each region (ce_send: thread tid takes e = 256 it + tid): 16-byte st.async
+// stores, 512 contiguous bytes per warp instruction, bytes counted on the receiver's mbarrier.
+__device__ __forceinline__ void ce_send_slot(const CESmem& S, const CEGeo& G, int e, int nb) {
     const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
     {
         const int kk = 4 * G.tcol + e / (16 * nb), blk = S2_BU + (e / 16) % nb, w = e % 16;
@@ -380,6 +381,10 @@ __device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it,
 #pragma unroll
         for (int r = 1; r < CE_CR; ++r) ce_sta2(G.rcol[r] + off * 8u, x.x, x.y, G.rcol[r] + cp_to_bar);
     }
+}
+
+__device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it, int nb) {
+    ce_send_slot(S, G, it * CE_THREADS + (int)threadIdx.x, nb);
 }
 
 // After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): the two k-groups swap
@@ -499,7 +504,7 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
 #pragma unroll
             for (int q = 0; q < 6; ++q) S.part[G.rank * 8 + q] = o[q];
         } else {
-            const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x), bar = ce_mapa(S.databar, threadIdx.x);
+            const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x), bar = ce_mapa(S.partbar, threadIdx.x);
 #pragma unroll
             for (int q = 0; q < 6; ++q) ce_sta(dst + 8 * q, o[q], bar);
         }
@@ -527,9 +532,11 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
     for (int e = tid; e < 8 * S2_HP; e += CE_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);
     if (tid == 0) {
         mbar_init(S.databar, 1);   // one arrival per stage (with the byte count the other CTAs will deliver)
+        mbar_init(S.partbar, 1);   // one per step
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     unsigned nphase = 0;   // stages whose output has been waited for (the data barrier's phase)
+    unsigned npart = 0;    // steps whose sums have been waited for
     ce_arrive();
     ce_wait();   // every CTA of the cluster is running: its shared memory may be written
 
@@ -617,43 +624,52 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
         const int j_own = G.c0 + 8 * nt + 2 * t + X;   // the thread's element in the epilogue: row r0 + g, column j_own
         const double* rpf = S.rp + fo;                  // fragment bases: row panel, column panel at the warp's 8-column half
         const double* cpf = S.cp + fo + nt * 32;
-        auto start_stage = [&](bool publish, bool with_p) {
+        auto start_stage = [&](bool publish, bool with_p, bool reduce_now, bool first_step) {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) a1[q][hh] = a2[q][hh] = aL[q][hh] = 0.0;
             const int ka = 2 * G.trow + X, kb0 = 4 * G.tcol + X, kb1 = kb0 + 2;
             const int nb = with_p ? 12 : 8;
-            if (publish) ce_send(S, G, 0, nb);
+            if (reduce_now) {
+                // Last stage of a step: warp 0 runs the step's reduction (convergence, dt: ~2.2 k cycles of dependent FP64
+                // operations; the others' sums left before their stage output) while the other seven warps push the stage
+                // output into the network -- which takes them as long, the network being what limits the stores.
+                if (warp == 0) {
+                    mbar_wait(S.partbar, npart & 1);
+                    reduce_step(first_step);
+                    if (lane == 0) {
+                        S.step[0] = dt;
+                        S.step[1] = active ? 1.0 : 0.0;
+                    }
+                } else {
+                    for (int e = tid - 32; e < 64 * nb; e += CE_THREADS - 32) ce_send_slot(S, G, e, nb);
+                }
+                ++npart;
+            }
+            if (publish && !reduce_now) ce_send(S, G, 0, nb);
             if (fld == 0) ce_kstep_opsA<true>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 0, a1, aL);
             else ce_kstep_opsA<false>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 1, a1, aL);
-            if (publish) ce_send(S, G, 1, nb);
+            if (publish && !reduce_now) ce_send(S, G, 1, nb);
             if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 0, a2, aL);
             else ce_kstep_opsB<false>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 1, a2, aL);
-            if (publish && with_p) ce_send(S, G, 2, nb);
+            if (publish && !reduce_now && with_p) ce_send(S, G, 2, nb);
             if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 0, a2, aL);
             else ce_kstep_opsB<false>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 1, a2, aL);
         };
-        start_stage(false, false);
+        start_stage(false, false, false, false);
         for (long long step = 0; step < nsteps; ++step) {
             for (int stage = 0; stage < 4; ++stage) {
-                // The previous step's reduction: convergence, dt.  Should the cavity have gone inactive, the K loop parts
-                // run so far were speculative (they only read) and the visit ends before anything is published.
-                const long long t_red0 = dbg_on ? clock64() : 0;
-                if (stage == 0 && step > 0) reduce_step(V.first && step == 1);
-                const long long t_red1 = dbg_on ? clock64() : 0;
-                if (stage == 0 && !active) break;
                 long long* tdbg = (dbg_on && dbg_stage < S2_DBG_STAGES) ? P.dbg + dbg_stage * 16 : nullptr;
                 ++dbg_stage;
-                if (tdbg) {
-                    tdbg[9] = t_red1 - t_red0;   // the previous step's reduction (stage 0)
-                    tdbg[0] = clock64();
-                }
+                if (tdbg) tdbg[0] = clock64();
                 if (tid == 0) {
                     // what the other CTAs will deliver for this stage: u, v (8 blocks) and, unless the pressure is frozen, p
-                    // (4 blocks) of one tile into the row panel and of three into the column panel; 6 sums from 7 CTAs
+                    // (4 blocks) of one tile into the row panel and of three into the column panel; at the last stage 6 sums
+                    // from each of the 7 others
                     const unsigned blocks = (P.freeze && stage != 3) ? 8u : 12u;
-                    mbar_expect_tx(S.databar, 4u * blocks * (CE_TR * CE_TC * 8u) + (stage == 3 ? 7u * 48u : 0u));
+                    mbar_expect_tx(S.databar, 4u * blocks * (CE_TR * CE_TC * 8u));
+                    if (stage == 3) mbar_expect_tx(S.partbar, 7u * 48u);
                 }
                 // the rest of the K loop: everything has arrived
                 if (fld == 0) ce_remote_part<true>(rpf, cpf, X, G.trow, G.tcol, 0, a1, a2, aL);
@@ -680,15 +696,19 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 bc_lines = true;
                 ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
                 if (tdbg) tdbg[6] = clock64();
-                start_stage(true, !(P.freeze && stage != 3));
+                start_stage(true, !(P.freeze && stage != 3), stage == 3, V.first && step == 0);
+                if (stage == 3) {
+                    __syncthreads();   // warp 0's verdict on the step
+                    dt = S.step[0];
+                    active = S.step[1] != 0.0;
+                }
                 if (tdbg) tdbg[10] = clock64();
                 mbar_wait(S.databar, nphase & 1);   // everyone else's part of the stage output is in this CTA's panels
                 ++nphase;
                 if (tdbg) tdbg[8] = clock64();
             }
-            if (!active) break;
+            if (!active) break;   // (the local part run for a next step was speculative: it only reads)
         }
-        if (active && nsteps > 0) reduce_step(V.first && nsteps == 1);   // the last step of the visit
 
         // ---- visit end: the state back into the record (rows by the CTAs of column tile 0, columns by those of row tile
         // 0), boundary-condition lines and status by CTA 0, then the cavity goes back to the queue ----

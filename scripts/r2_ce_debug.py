@@ -26,5 +26,4 @@ names = ["K loop, remote part", "own elements + arrive", "accumulator swap", "as
 for k, nm in enumerate(names):
     c = d[:, order[k + 1]] - d[:, order[k]]
     print(f"{nm:38s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}")
-print("end-of-step reduction (stage 0): mean", d[0::4, 9].mean(), d[4::4, 9].mean())
 print("stage period: mean", np.diff(d[:, 0]).mean(), "clk;  last stage of a step to the next:", np.diff(d[:, 0])[3::4].mean())
