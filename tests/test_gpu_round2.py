@@ -357,3 +357,24 @@ def test_config5_coarse_level_n64_re5000_from_the_cold_start(ldc, golden, path):
         assert rel(u[b], g[f"c{b}_u64"]) < 1e-10, b
         assert rel(v[b], g[f"c{b}_v64"]) < 1e-10, b
         assert rel(p[b], g[f"c{b}_p64"]) < 1e-10, b
+
+
+def test_cluster_resident_kernel_divergence_and_iteration_cap(ldc):
+    """k_cluster_eo's bookkeeping off the happy path: a cavity that blows up (CFL far beyond stability) leaves with the
+    non-finite exit at the same iteration as on the launch-per-stage kernels while its batch-mates carry on to the cap, and
+    a cap that is no multiple of anything is hit exactly."""
+    N, B, cap = 60, 3, 137
+    res = {}
+    for path in ("stream_eo", "stream_tma"):
+        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
+            if path == "stream_tma":
+                assert s.kernel_name == "k_cluster_eo"
+            s.set_cases([100.0, 400.0, 100.0], CFL=[1.5, 60.0, 1.5]).init_state()
+            r = s.solve(1e-12, cap, warmup=0)
+            res[path] = (r.iterations.copy(), r.converged.copy(), r.diverged.copy(), s.get_state())
+    it, conv, divg, _ = res["stream_tma"]
+    assert divg[1] and not divg[0] and not divg[2] and not conv.any()
+    assert it[0] == cap and it[2] == cap and it[1] < cap
+    assert np.array_equal(it, res["stream_eo"][0]) and np.array_equal(divg, res["stream_eo"][2])
+    for a, c in zip(res["stream_tma"][3], res["stream_eo"][3]):
+        assert rel(a[0], c[0]) < 1e-10 and rel(a[2], c[2]) < 1e-10
