@@ -5,12 +5,16 @@
 //   * every CTA keeps the operand panels of its tile in its own shared memory for the whole visit -- the row panel
 //     (operator rows and state rows of its 8 lines, all k) and the column panel (its 16 columns, all k), in the
 //     k4-interleaved block layout of stream_tma.cuh, so that the DMMA fragment loads are the same conflict-free 256-byte reads;
-//   * the output of an RK stage is written straight into the panels of the CTAs that need it -- the row panels of the two
-//     CTAs of the tile's row, the column panels of the four CTAs of its column -- with st.shared::cluster (distributed
-//     shared memory), and the stages are separated by the hardware cluster barrier (barrier.cluster arrive / wait,
-//     ~620 cycles: scripts/dsmem_bw.cu) instead of a counter in global memory plus a round of bulk copies out of L2;
-//   * the end-of-step sums (convergence norms, maxima for the next dt) are exchanged the same way and reduced redundantly,
-//     in fixed order, by every CTA; status and state go back to the record in L2 only at the end of a visit.
+//   * the output of an RK stage goes straight into the panels of the CTAs that need it -- the row panels of the two CTAs
+//     of the tile's row, the column panels of the four CTAs of its column: the CTA's own by plain stores, the others'
+//     through distributed shared memory by st.async stores (SASS STAS) that count their bytes on an mbarrier of the
+//     RECEIVING CTA, which waits for its byte count instead of for a barrier round trip.  The one hardware cluster barrier
+//     of a stage (barrier.cluster arrive.relaxed / wait) says that every CTA has finished reading its panels;
+//   * the K loop of a stage runs in two parts: the half-steps on state the CTA produced itself right after its own stores,
+//     with the remote stores issued between them, the others once the mbarrier says that everything has arrived;
+//   * the end-of-step sums (convergence norms, maxima for the next dt) travel the same way ahead of the last stage's output
+//     and are reduced, in fixed order, by warp 0 of every CTA while the other warps send; status and state go back to the
+//     record in L2 only at the end of a visit.
 // What bounds it: the SM-to-SM network takes ~20 B/clk out of an SM (scripts/dsmem_bw.cu, profiles/r02_dsmem_bw.txt), and
 // a stage sends 48 KB per CTA; the K loop of a stage is 80 DMMAs per warp, two warps per SM sub-partition.
 // Eight warps per CTA: (k-group X: even | odd k4-steps) x (u | v equation) x (8-column half of the tile); the two k-groups
