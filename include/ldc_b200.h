@@ -57,8 +57,8 @@ enum {
                                  LDC_PATH_STREAM_EO; AUTO picks it wherever it picked that path (LDC_STREAM_TMA=0 in the
                                  environment keeps the launch-per-stage kernels for A / B runs).  Its kernel comes in three
                                  shapes chosen per launch from the number of cavities still iterating: 16 x 16 tiles
-                                 (k_stream_tma), 16 x 32 tiles (k_stream_tma_wide) and, for 50 <= nx <= 65 with at most one
-                                 cavity per thread-block cluster the device holds (15 on B200), k_cluster_eo: a cavity over a
+                                 (k_stream_tma), 16 x 32 tiles (k_stream_tma_wide) and, for 50 <= nx <= 65 with at most two
+                                 cavities per thread-block cluster the device holds (15 on B200), k_cluster_eo: a cavity over a
                                  cluster of 8 CTAs with operators and state resident in distributed shared memory */
 };
 
