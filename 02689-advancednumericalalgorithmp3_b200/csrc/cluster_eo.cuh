@@ -369,17 +369,17 @@ __device__ __forceinline__ void ce_publish_local(const CESmem& S, unsigned offR,
 // 64 nb double2) to the three other CTAs of the tile column; nb = 8 state blocks (u, v) or 12 (u, v, p), which sit back to
 // back.  ce_send_slot sends the double2 number e of each region (ce_send: thread tid takes e = 256 it + tid): 16-byte st.async
 // stores, 512 contiguous bytes per warp instruction, bytes counted on the receiver's mbarrier.
-__device__ __forceinline__ void ce_send_slot(const CESmem& S, const CEGeo& G, int e, int nb) {
+__device__ __forceinline__ void ce_send_slot(const CESmem& S, const CEGeo& G, int e, int nb, int blk0 = S2_BU) {
     const unsigned cp_to_bar = G.bar_off - (unsigned)(CE_RP * sizeof(double));   // (the column panel follows the row panel)
     {
-        const int kk = 4 * G.tcol + e / (16 * nb), blk = S2_BU + (e / 16) % nb, w = e % 16;
+        const int kk = 4 * G.tcol + e / (16 * nb), blk = blk0 + (e / 16) % nb, w = e % 16;
         const unsigned off = (unsigned)((kk * S2_NB + blk) * CE_ABLK + 2 * w);
         const double2 x = *reinterpret_cast<const double2*>(S.rp + off);
 #pragma unroll
         for (int c = 1; c < CE_CC; ++c) ce_sta2(G.rrow[c] + off * 8u, x.x, x.y, G.rrow[c] + G.bar_off);
     }
     {
-        const int kk = 2 * G.trow + e / (32 * nb), blk = S2_BU + (e / 32) % nb, w = e % 32;
+        const int kk = 2 * G.trow + e / (32 * nb), blk = blk0 + (e / 32) % nb, w = e % 32;
         const unsigned off = (unsigned)((kk * S2_NB + blk) * CE_BBLK + 2 * w);
         const double2 x = *reinterpret_cast<const double2*>(S.cp + off);
 #pragma unroll
@@ -387,8 +387,8 @@ __device__ __forceinline__ void ce_send_slot(const CESmem& S, const CEGeo& G, in
     }
 }
 
-__device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it, int nb) {
-    ce_send_slot(S, G, it * CE_THREADS + (int)threadIdx.x, nb);
+__device__ __forceinline__ void ce_send(const CESmem& S, const CEGeo& G, int it, int nb, int blk0 = S2_BU) {
+    ce_send_slot(S, G, it * CE_THREADS + (int)threadIdx.x, nb, blk0);
 }
 
 // After the K loop (and after the first arrival at the cluster barrier: this CTA has read its panels): the two k-groups swap
@@ -464,15 +464,23 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             }
         }
     }
-    if (tdbg) tdbg[4] = clock64();
-    __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red; S.edgep has been read
     // frozen pressure (SGSolver): every stage takes grad(p^n), so stages 0..2 leave the pressure blocks alone
     const bool keep_pn = P.freeze && stage != 3;
     const unsigned offR = (unsigned)(((j >> 2) * S2_NB + S2_BU + 4 * fld) * CE_ABLK + g * 4 + (j & 3));
     const unsigned offC = (unsigned)(((i >> 2) * S2_NB + S2_BU + 4 * fld) * CE_BBLK + (j & 15) * 4 + (i & 3));
-    // the CTA's own panels (its own warps have all read them: the barrier above); the other CTAs' by the caller
+    // the CTA's own panels (its own warps have all read them: the barrier after the swap); the other CTAs' below / by the caller
 #pragma unroll
     for (int q = 0; q < 4; ++q) ce_publish_local(S, offR + q * CE_ABLK, offC + q * CE_BBLK, fn[q]);
+    if (tdbg) tdbg[4] = clock64();
+    __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red, u and v in the CTA's own panels
+    ce_wait();         // every CTA of the cluster has finished reading its panels: they may be overwritten
+    if (tdbg) tdbg[6] = clock64();
+    // u and v leave for the other CTAs' panels ahead of the pressure update (not at the last stage of a step, where all the
+    // sends run beside warp 0's reduction: the caller's)
+    if (!last) {
+        ce_send(S, G, 0, 8);
+        ce_send(S, G, 1, 8);
+    }
     if (fld == 0 && !keep_pn) {
         const unsigned pR = offR + (S2_BP - S2_BU) * CE_ABLK, pC = offC + (S2_BP - S2_BU) * CE_BBLK;
 #pragma unroll
@@ -651,13 +659,12 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 }
                 ++npart;
             }
-            if (publish && !reduce_now) ce_send(S, G, 0, nb);
+            // (stages 0..2: u and v have left in ce_finish; the pressure blocks, one double2 of each region per thread, now)
+            if (publish && !reduce_now && with_p) ce_send(S, G, 0, 4, S2_BP);
             if (fld == 0) ce_kstep_opsA<true>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 0, a1, aL);
             else ce_kstep_opsA<false>(rpf + (size_t)ka * (S2_NB * CE_ABLK), cpf + (size_t)ka * (S2_NB * CE_BBLK), 1, a1, aL);
-            if (publish && !reduce_now) ce_send(S, G, 1, nb);
             if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 0, a2, aL);
             else ce_kstep_opsB<false>(rpf + (size_t)kb0 * (S2_NB * CE_ABLK), cpf + (size_t)kb0 * (S2_NB * CE_BBLK), 1, a2, aL);
-            if (publish && !reduce_now && with_p) ce_send(S, G, 2, nb);
             if (fld == 0) ce_kstep_opsB<true>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 0, a2, aL);
             else ce_kstep_opsB<false>(rpf + (size_t)kb1 * (S2_NB * CE_ABLK), cpf + (size_t)kb1 * (S2_NB * CE_BBLK), 1, a2, aL);
         };
@@ -698,8 +705,6 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
                 else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
                 bc_lines = true;
-                ce_wait();   // every CTA of the cluster has finished reading its panels: they may be overwritten
-                if (tdbg) tdbg[6] = clock64();
                 start_stage(true, !(P.freeze && stage != 3), stage == 3, V.first && step == 0);
                 if (stage == 3) {
                     __syncthreads();   // warp 0's verdict on the step

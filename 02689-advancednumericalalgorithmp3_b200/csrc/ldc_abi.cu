@@ -861,10 +861,6 @@ static int run_steps(ldc_handle* h, const double* tol_dev, long long start, long
             LDC_CUDA(cudaMemsetAsync(dbg, 0, S2_DBG_STAGES * 16 * sizeof(long long), h->stream));
         }
         P.dbg = dbg;
-        {
-            const char* e = getenv("LDC_STREAM_SPLIT");   // 0: no split K loop on the 4 x 4 tiles (A / B runs)
-            P.split = (e && atoi(e) == 0) ? 0 : 1;
-        }
         h->canon_valid = false;
         const long long per_launch = 512;   // steps per launch (the host looks at the active count between launches)
         for (long long done = start; done < stop; done += per_launch) {

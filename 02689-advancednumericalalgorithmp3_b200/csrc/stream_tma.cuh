@@ -53,7 +53,7 @@ constexpr size_t S2_SMEM_DOUBLES = (size_t)S2_SLOTS * S2_SLOT   // chunk ring
                                    + 8 * S2_HP + 16 * S2_HP     // boundary-column vectors, boundary lines in parity form
                                    + 4 * 8 * 32                 // dv/dy hand-over v warps -> u warps
                                    + 16 * 8 + 80 + 16           // tile partials, reduction scratch, step info
-                                   + 2 * S2_SLOTS + 3;          // mbarriers
+                                   + 2 * S2_SLOTS + 2;          // mbarriers
 
 __host__ __device__ inline size_t s2_off(int tile, int kk, int blk, int r, int kq) {
     return (((size_t)tile * S2_NK4 + kk) * S2_NB + blk) * 64 + r * 4 + kq;
@@ -75,7 +75,6 @@ struct S2Params {
     unsigned* team_bar;           // [teams] arrivals at the team's stage barriers (zero at launch)
     unsigned long long* team_mail;// [teams] (visit number << 32) | (cavity + 1), written by the team's leader
     long long* dbg;               // optional [S2_DBG_STAGES][16] clock samples of CTA 0 (LDC_S2_DEBUG), else null
-    int split;                    // 1: split K loop on 4 x 4 tiles (LDC_STREAM_SPLIT=0 turns it off for A / B runs)
 };
 constexpr int S2_DBG_STAGES = 256;
 
@@ -309,10 +308,7 @@ __global__ void __launch_bounds__(256) k_s2_begin(const double* __restrict__ buf
 // ---- the K loop of one chunk -------------------------------------------------------------------------------------------
 // Contractions of the warp's field for the k4-steps [kbeg, kend) of one chunk slot (cf. st_chunk / eo_field_pass).
 //   ro = (8 tw + g) * 4 + t : the thread's A-fragment offset inside a 16 x 4 block;  co = g * 4 + t : B-fragment offset
-//   PART: 0 = all contractions; 1 = only those of operator rows (row side) with state columns (column side); 2 = only those
-//   of state rows (row side) with operator rows at the tile's columns (column side) -- the two halves of k_stream_tma's
-//   split K loop (s2_consumer_main)
-template <bool P_LEFT, int PART = 0>
+template <bool P_LEFT>
 __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff, int kbeg, int kend, int ro, int co, int fld,
                                          double (&a1)[4][2][2], double (&a2)[4][2][2], double (&aL)[4][2][2]) {
     constexpr int NT = 2;
@@ -328,12 +324,11 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff
         double FA[4], FB[4][NT];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            if (PART != 1) FA[q] = sFa[(kk * S2_NB + q) * 64];
+            FA[q] = sFa[(kk * S2_NB + q) * 64];
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-                if (PART != 2) FB[q][nt] = sFb[(kk * S2_NB + q) * 64 + nt * 32];
+            for (int nt = 0; nt < NT; ++nt) FB[q][nt] = sFb[(kk * S2_NB + q) * 64 + nt * 32];
         }
-        if (PART != 2) {
+        {
             double dA[2], ddA[2];
 #pragma unroll
             for (int a = 0; a < 2; ++a) {
@@ -350,7 +345,7 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff
                         dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], ddA[a], FB[2 * a + b][nt]);
                     }
         }
-        if (PART != 1) {
+        {
             double dB[2][NT], ddB[2][NT];
 #pragma unroll
             for (int b = 0; b < 2; ++b)
@@ -369,7 +364,7 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff
                         dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], FA[2 * a + b], ddB[b][nt]);
                     }
         }
-        if (P_LEFT && PART != 2) {
+        if (P_LEFT) {
             double gA[2], PB[4][NT];
 #pragma unroll
             for (int a = 0; a < 2; ++a) gA[a] = sOa[(kk * S2_NB + 4 + a) * 64];
@@ -384,8 +379,7 @@ __device__ __forceinline__ void s2_chunk(const double* __restrict__ sl, int boff
 #pragma unroll
                     for (int nt = 0; nt < NT; ++nt)
                         dmma884(aL[2 * a + b][nt][0], aL[2 * a + b][nt][1], gA[a], PB[2 * (1 - a) + b][nt]);
-        }
-        if (!P_LEFT && PART != 1) {
+        } else {
             double PA[4], gB[2][NT];
 #pragma unroll
             for (int q = 0; q < 4; ++q) PA[q] = sPa[(kk * S2_NB + q) * 64];
@@ -690,7 +684,7 @@ __device__ __forceinline__ void s2_consumer_reduce(double (&s)[4], double (&mx)[
 // shared-memory carve-up of k_stream_tma
 struct S2Smem {
     double *slot, *uv, *phin, *vec, *edgep, *x, *part, *red, *step;
-    unsigned long long *full, *empty, *stepbar, *teambar, *ownbar;
+    unsigned long long *full, *empty, *stepbar, *teambar;
     int* cavity;
     __device__ explicit S2Smem(double* smem) {
         slot = smem;
@@ -706,7 +700,6 @@ struct S2Smem {
         empty = full + S2_SLOTS;
         stepbar = empty + S2_SLOTS;
         teambar = stepbar + 1;
-        ownbar = teambar + 1;   // this CTA's stage output is in global memory (split K loop)
         cavity = reinterpret_cast<int*>(step + 15);
     }
 };
@@ -714,7 +707,6 @@ struct S2Smem {
 // CTA geometry inside its team
 struct S2Geo {
     int ntile, ntc, team_size, team, tin, trow, tcol, tile, r0, c0, m, h, n1, nk4, nch;
-    bool split;   // k_stream_tma on 4 x 4 tiles: the K loop runs in a local and a remote part (s2_consumer_main)
     // cw = 16-column tiles per CTA: 1 (k_stream_tma) or 2 (k_stream_tma_wide); tcol = the CTA's first column tile
     __device__ S2Geo(const S2Params& P, int cw) {
         ntile = P.ntile; ntc = (ntile + cw - 1) / cw; team_size = ntile * ntc;
@@ -723,7 +715,6 @@ struct S2Geo {
         r0 = trow * 16; c0 = tcol * 16;
         m = P.m; h = eo_half(m); n1 = P.n1;
         nk4 = P.K4 / 4; nch = (nk4 + S2_KC4 - 1) / S2_KC4;
-        split = cw == 1 && ntile == 4 && P.split != 0;
     }
 };
 
@@ -862,22 +853,18 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                 }
                 long long t_start = 0, t_wait = 0;
                 if (dbg_on) t_start = clock64();
-                // One chunk of the ring: `part` says which contractions it feeds (s2_chunk), `release` whether the slot goes
-                // back to the producers right away (the last two stay for the accumulator swap).
-                unsigned idx = 0;   // chunks consumed in this stage
-                auto consume = [&](int c, int part, bool release) {
-                    const unsigned gc = gcb + idx, slot = gc % S2_SLOTS;
+                for (int c = 0; c < nch; ++c) {
+                    const unsigned gc = gcb + c, slot = gc % S2_SLOTS;
                     long long tw0 = 0;
                     if (dbg_on) tw0 = clock64();
                     mbar_wait(S.full + slot, (gc / S2_SLOTS) & 1);
                     if (dbg_on) {
                         const long long tw1 = clock64();
                         t_wait += tw1 - tw0;
-                        if (idx == 0 && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + X * 4 + 1] = tw1 - t_start;
+                        if (c == 0 && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + X * 4 + 1] = tw1 - t_start;
                     }
-                    ++idx;
                     const double* sl = S.slot + (size_t)slot * S2_SLOT;
-                    if (c == cgrab && part != 1) {
+                    if (c == cgrab) {
                         // the thread's own elements of its field's stage input: columns 8 X + 2 t, + 1 of the tile
                         const int pos = (X * 2 + tw) * 32 + lane;
                         const double* src = sl + S2_SL_A + ((t >> 1) * S2_NB + S2_BU + 4 * fld) * 64 + (8 * tw + g) * 4 + 2 * (t & 1);
@@ -892,44 +879,15 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                     }
                     const int ksteps = min(S2_KC4, G.nk4 - c * S2_KC4);
                     const int kend = ksteps < X + 1 ? ksteps : X + 1;
-                    if (part == 0) {
-                        if (fld == 0) s2_chunk<true>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                        else s2_chunk<false>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                    } else if (part == 1) {
-                        if (fld == 0) s2_chunk<true, 1>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                        else s2_chunk<false, 1>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                    } else {
-                        if (fld == 0) s2_chunk<true, 2>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                        else s2_chunk<false, 2>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
-                    }
-                    if (release) {
+                    if (fld == 0) s2_chunk<true>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
+                    else s2_chunk<false>(sl, S2_SL_B, X, kend, ro, co, fld, a1, a2, aL);
+                    if (c < nch - 2) {
                         __syncwarp();
                         if (lane == 0) mbar_arrive(S.empty + slot);
                     }
-                };
-                if (G.split) {
-                    // Split K loop (4 x 4 tiles): first the contractions whose state operand this CTA wrote itself in the
-                    // previous stage -- operator rows x state columns at the k range of its own tile ROW (chunks 2 trow, + 1),
-                    // state rows x operator columns at the k range of its own tile COLUMN (chunks 2 tcol, + 1; the second pass
-                    // also brings the thread's own elements) -- which the producers fetch as soon as this CTA's stores are out,
-                    // without waiting for the team; then everything else, once the team barrier has let the other chunks in.
-                    for (int q = 0; q < 2; ++q)
-                        if (2 * G.trow + q < nch) consume(2 * G.trow + q, 1, true);
-                    for (int q = 0; q < 2; ++q)
-                        if (2 * G.tcol + q < nch) consume(2 * G.tcol + q, 2, true);
-                    const int nrem = nch - ((G.trow == G.tcol) ? min(2, nch - 2 * G.trow) : 0);
-                    int r = 0;
-                    for (int c = 0; c < nch; ++c) {
-                        const bool doA = (c >> 1) != G.trow, doB = (c >> 1) != G.tcol;
-                        if (!doA && !doB) continue;
-                        consume(c, doA && doB ? 0 : (doA ? 1 : 2), r < nrem - 2);
-                        ++r;
-                    }
-                } else {
-                    for (int c = 0; c < nch; ++c) consume(c, 0, c < nch - 2);
                 }
-                const unsigned slot_own = (gcb + idx - 2 + X) % S2_SLOTS, slot_other = (gcb + idx - 1 - X) % S2_SLOTS;
-                gcb += idx;
+                const unsigned slot_own = (gcb + nch - 2 + X) % S2_SLOTS, slot_other = (gcb + nch - 1 - X) % S2_SLOTS;
+                gcb += nch;
                 long long t_loop = 0;
                 if (dbg_on) t_loop = clock64();
                 if (stage == 0 && step > 0) {
@@ -965,17 +923,7 @@ __device__ __forceinline__ void s2_consumer_main(const S2Params& P, const S2Smem
                 // update (cumulative over the CTA barrier) publishes every consumer's stores; the readers are TMA copies,
                 // whose issuing thread crosses to the async proxy after its acquire (s2_producer_main) ----
                 consumer_sync();
-                if (tid == 0) {
-                    if (G.split) {
-                        // a fence, then the news for this CTA's own producers (its stage output can be fetched) and a
-                        // relaxed increment of the team's counter: together the release that red.release would be
-                        fence_acq_rel_gpu();
-                        mbar_arrive(S.ownbar);
-                        asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(P.team_bar + G.team), "r"(1u) : "memory");
-                    } else {
-                        red_release_add(P.team_bar + G.team, 1u);
-                    }
-                }
+                if (tid == 0) red_release_add(P.team_bar + G.team, 1u);
                 if (dbg_on && dbg_stage < S2_DBG_STAGES) {
                     // per group X: [0] stage start (absolute), [1] wait for the first chunk, [2] K loop incl. waits,
                     // [3] all waits inside the K loop; group 0 also: [8] exchange + epilogue, [9] arrive,
@@ -1018,7 +966,6 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S,
     unsigned nbar = 0;       // team barriers completed before the current stage
     unsigned nstepinfo = 0;  // step-info hand-overs seen so far (helpers)
     unsigned nteam = 0;      // team-barrier hand-overs seen so far (helpers)
-    unsigned nfin = 0;       // stages this CTA's consumers have finished (arrivals at S.ownbar; split K loop)
     unsigned visit = 0;
     const bool dbg_on = P.dbg != nullptr && blockIdx.x == 0 && lane == 0 && leader;
     int dbg_stage = 0;
@@ -1108,46 +1055,8 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S,
                 const bool reduce_now = stage == 0 && step > 0;
                 const int s_lo = (!WIDE && reduce_now && pw == 1) ? 0 : side, s_hi = (!WIDE && reduce_now && pw == 1) ? 2 : side + 1;
                 const bool idle = WIDE ? (pw == 3 ? !reduce_now : (reduce_now && leader)) : (reduce_now && leader);
-                // chunks of this stage in ring order: with the split K loop first the four local ones (s2_consumer_main), which
-                // need only this CTA's own stage output, then the others behind the team barrier
-                int nstage = nch;
-                bool split = false;
-                if constexpr (!WIDE) {
-                    split = G.split;
-                    if (split) {
-                        const int la = min(2, nch - 2 * G.trow), lb = min(2, nch - 2 * G.tcol);
-                        nstage = nch + la + lb - (G.trow == G.tcol ? la : 0);
-                    }
-                }
                 if (lane == 0) {
                     long long tp0 = 0, tp1 = 0;
-                    unsigned idx = 0;
-                    auto issue = [&](int c) {
-                        if (!idle && (int)(idx % (unsigned)cstep) == cpar) {
-                            const unsigned gc = gcb + idx, slot = gc % SLOTS, fb = full0 + 8 * slot;
-                            mbar_wait_a(empty0 + 8 * slot, ((gc / SLOTS) & 1) ^ 1);
-                            for (int sd = s_lo; sd < s_hi; ++sd) {
-                                mbar_expect_tx_a(fb, S2_SIDE_BYTES);
-                                bulk_g2s_a(slot0 + slot * SLOT_BYTES + sd * S2_SIDE_BYTES,
-                                           rec_in + (sd == 0 ? offA : (sd == 1 ? offB : offB1)) + (size_t)c * (S2_KC4 * S2_NB * 64),
-                                           S2_SIDE_BYTES, fb);
-                            }
-                        }
-                        ++idx;
-                    };
-                    if constexpr (!WIDE) {
-                        if (split) {
-                            if (need_bar) {
-                                // this CTA's own stage output is out (fence + arrival by its consumers, s2_consumer_main)
-                                mbar_wait_a(s2_smem(S.ownbar), (nfin - 1) & 1);
-                                fence_proxy_async();
-                            }
-                            for (int q = 0; q < 2; ++q)
-                                if (2 * G.trow + q < nch) issue(2 * G.trow + q);
-                            for (int q = 0; q < 2; ++q)
-                                if (2 * G.tcol + q < nch) issue(2 * G.tcol + q);
-                        }
-                    }
                     if (dbg_on) tp0 = clock64();
                     if (need_bar) {
                         // the leader polls the team's counter in global memory and passes the news on in shared memory
@@ -1161,21 +1070,28 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S,
                         fence_proxy_async();
                     }
                     if (dbg_on) tp1 = clock64();
-                    for (int c = 0; c < nch; ++c) {
-                        if (split && (c >> 1) == G.trow && (c >> 1) == G.tcol) continue;   // both halves were local
-                        if (dbg_on && idx == (unsigned)(nstage - nch + (split && G.trow == G.tcol ? min(2, nch - 2 * G.trow) : 0)) &&
-                            dbg_stage < S2_DBG_STAGES) {
-                            // [10] start of the wait (absolute), [11] wait at the team barrier
-                            P.dbg[dbg_stage * 16 + 10] = tp0;
-                            P.dbg[dbg_stage * 16 + 11] = tp1 - tp0;
+                    if (!idle) {
+                        for (int c = cpar; c < nch; c += cstep) {
+                            const unsigned gc = gcb + c, slot = gc % SLOTS, fb = full0 + 8 * slot;
+                            mbar_wait_a(empty0 + 8 * slot, ((gc / SLOTS) & 1) ^ 1);
+                            for (int sd = s_lo; sd < s_hi; ++sd) {
+                                mbar_expect_tx_a(fb, S2_SIDE_BYTES);
+                                bulk_g2s_a(slot0 + slot * SLOT_BYTES + sd * S2_SIDE_BYTES,
+                                           rec_in + (sd == 0 ? offA : (sd == 1 ? offB : offB1)) + (size_t)c * (S2_KC4 * S2_NB * 64),
+                                           S2_SIDE_BYTES, fb);
+                            }
+                            if (dbg_on && c == cpar && dbg_stage < S2_DBG_STAGES) {
+                                // [10] start of the wait (absolute), [11] wait at the team barrier, [12] first chunk issued
+                                P.dbg[dbg_stage * 16 + 10] = tp0;
+                                P.dbg[dbg_stage * 16 + 11] = tp1 - tp0;
+                                P.dbg[dbg_stage * 16 + 12] = clock64() - tp1;
+                            }
                         }
-                        issue(c);
                     }
-                    if (dbg_on && dbg_stage < S2_DBG_STAGES) P.dbg[dbg_stage * 16 + 12] = clock64() - tp1;   // [12] chunks issued
                     ++dbg_stage;
                 }
                 __syncwarp();
-                gcb += nstage;
+                gcb += nch;
                 if (reduce_now && leader) {
                     // the previous step's sums (needed by the consumers only at this stage's epilogue)
                     reduce_step(first && step == 1);
@@ -1196,7 +1112,6 @@ __device__ __forceinline__ void s2_producer_main(const S2Params& P, const SM& S,
                 }
                 if (!active) break;   // the consumers drop this (speculative) stage as well: no barrier follows it
                 ++nbar;
-                ++nfin;
                 if (stage == 3) cur = (cur + 2) % 3;
             }
         }
@@ -1255,7 +1170,6 @@ __global__ void __launch_bounds__(S2_THREADS, 1) k_stream_tma(const S2Params P) 
         }
         mbar_init(S.stepbar, 1);
         mbar_init(S.teambar, 1);
-        mbar_init(S.ownbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int e = tid; e < 8 * S2_HP; e += S2_THREADS) S.vec[e] = __ldg(P.ops + 6 * ST_BLK + e);

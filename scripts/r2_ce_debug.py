@@ -20,10 +20,11 @@ with ldc_b200.BatchedSpectralLDC(N, batch=B, path="stream_tma") as s:
     print("N", N, "B", B, s.kernel_name, "kernel ms", s.last_kernel_ms, "us/step", 1e3 * s.last_kernel_ms / K)
 d = np.loadtxt(out)
 d = d[8:8 + 4 * 40]   # skip the first two steps
-order = [0, 1, 2, 3, 4, 5, 6, 10, 8]
-names = ["K loop, remote part", "own elements + arrive", "accumulator swap", "assembly", "sync, pressure, own panels, sync",
-         "wait: panels read everywhere", "K loop, local part + stores", "wait: the others' output has arrived"]
+order = [0, 1, 2, 3, 4, 6, 5, 10, 8]
+names = ["K loop, remote part", "own elements + arrive", "accumulator swap", "assembly + own u, v panels",
+         "sync + wait: panels read everywhere", "u, v sends, pressure, own p panels, sync", "K loop, local part + p sends",
+         "wait: the others' output has arrived"]
 for k, nm in enumerate(names):
     c = d[:, order[k + 1]] - d[:, order[k]]
-    print(f"{nm:38s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}")
+    print(f"{nm:42s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}")
 print("stage period: mean", np.diff(d[:, 0]).mean(), "clk;  last stage of a step to the next:", np.diff(d[:, 0])[3::4].mean())

@@ -378,33 +378,3 @@ def test_cluster_resident_kernel_divergence_and_iteration_cap(ldc):
     assert np.array_equal(it, res["stream_eo"][0]) and np.array_equal(divg, res["stream_eo"][2])
     for a, c in zip(res["stream_tma"][3], res["stream_eo"][3]):
         assert rel(a[0], c[0]) < 1e-10 and rel(a[2], c[2]) < 1e-10
-
-
-@pytest.mark.parametrize("N,B", [(128, 2), (100, 3)])
-def test_split_k_loop_of_the_streamed_kernel(ldc, monkeypatch, N, B):
-    """k_stream_tma on 4 x 4 tiles runs the contractions on state a CTA wrote itself ahead of the team barrier (split K
-    loop, the default; LDC_STREAM_SPLIT=0 turns it off): both orders of accumulation against the tiled FMA path from a
-    BC-violating random state with both pressure semantics and a continued run, each bitwise reproducible."""
-    rng = np.random.default_rng(N + 1)
-    u, v = 0.1 * rng.standard_normal((2, B, N + 1, N + 1))
-    p = 0.1 * rng.standard_normal((B, N - 1, N - 1))
-    Re = np.linspace(300.0, 2000.0, B)
-    monkeypatch.setenv("LDC_STREAM_CW", "1")
-    out = {}
-    for path, split in (("tiled", None), ("stream_tma", "1"), ("stream_tma", "1"), ("stream_tma", "0")):
-        if split:
-            monkeypatch.setenv("LDC_STREAM_SPLIT", split)
-        with ldc.BatchedSpectralLDC(N, batch=B, path=path) as s:
-            s.set_cases(Re, corner_smoothing=0.1).set_state(u, v, p)
-            s.step(2, freeze_pressure=(N % 8 == 0))
-            r = s.step(5, freeze_pressure=(N % 8 == 0))
-            res = (*s.get_state(), r)
-        key = path + (split or "")
-        if key in out:
-            assert all(np.array_equal(a, c) for a, c in zip(out[key], res)), "not bitwise reproducible"
-        out[key] = res
-    for key in ("stream_tma1", "stream_tma0"):
-        for a, c in zip(out[key][:3], out["tiled"][:3]):
-            assert rel(a, c) < 1e-10, key
-        assert np.allclose(out[key][3], out["tiled"][3], rtol=1e-8), key
-    assert not all(np.array_equal(a, c) for a, c in zip(out["stream_tma1"][:3], out["stream_tma0"][:3]))   # two orders
