@@ -73,12 +73,6 @@ __device__ __forceinline__ unsigned ce_mapa(const void* p, unsigned rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(s2_smem(p)), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void ce_st(unsigned addr, double v) {
-    asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
-}
-__device__ __forceinline__ void ce_st2(unsigned addr, double v0, double v1) {
-    asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v0), "d"(v1) : "memory");
-}
 // stores into another CTA's shared memory that count their bytes on an mbarrier there once they have landed (STAS)
 __device__ __forceinline__ void ce_sta(unsigned addr, double v, unsigned bar) {
     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(addr), "d"(v), "r"(bar)
@@ -282,7 +276,7 @@ __device__ __forceinline__ void ce_visit_prepare(const CESmem& S, bool first, co
 
 // geometry of a CTA inside its cluster and the shared::cluster addresses it stores to
 struct CEGeo {
-    int rank, trow, tcol, r0, c0, m, h, n1, nk4;
+    int rank, trow, tcol, r0, c0, m, h, n1;
     unsigned rrow[CE_CC];        // row panels of the CTAs of this tile row
     unsigned rcol[CE_CR];        // column panels of the CTAs of this tile column
     unsigned bar_off;            // data barrier of a CTA = its panel address + bar_off (one window per CTA, same layout)
@@ -290,7 +284,7 @@ struct CEGeo {
         rank = (int)ce_rank();
         trow = rank / CE_CC; tcol = rank % CE_CC;
         r0 = trow * CE_TR; c0 = tcol * CE_TC;
-        m = P.m; h = eo_half(m); n1 = P.n1; nk4 = P.K4 / 4;
+        m = P.m; h = eo_half(m); n1 = P.n1;
         // entry 0 is this CTA itself (stored to directly), entries 1.. the other CTAs of the row / column, starting with the next
 #pragma unroll
         for (int c = 0; c < CE_CC; ++c) rrow[c] = ce_mapa(S.rp, trow * CE_CC + (tcol + c) % CE_CC);
