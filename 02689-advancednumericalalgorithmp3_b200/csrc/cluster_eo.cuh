@@ -180,6 +180,16 @@ __device__ __forceinline__ void ce_remote_part(const double* __restrict__ rp, co
     }
 }
 
+// s2_dt with the two quotients that do not change during a visit, nu / dx_min^2 and nu / dy_min^2, taken out (the same
+// operations on the same operands: the same bits).  Two square roots and three divisions are left: ~1 k cycles in a row.
+__device__ __forceinline__ double ce_dt(double umax, double vmax, double lidv, double b2, double cfl, double dx_min, double dy_min,
+                                        double nu_dx2, double nu_dy2) {
+    const double ua = (lidv > umax) ? lidv : umax, va = (1e-10 > vmax) ? 1e-10 : vmax;
+    const double lam_x = (ua + sqrt(ua * ua + b2)) / dx_min + nu_dx2;
+    const double lam_y = (va + sqrt(va * va + b2)) / dy_min + nu_dy2;
+    return cfl / (lam_x + lam_y);
+}
+
 // 4 sums + 2 NaN-propagating maxima across the eight warps, fixed order, result in every thread.
 __device__ __forceinline__ void ce_block_reduce(double (&s)[4], double (&mx)[2], double* sRed, int warp, int lane) {
 #pragma unroll
@@ -469,6 +479,24 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
     __syncthreads();   // dv/dy of the v warps is in S.x, the warps' partial sums in S.red, u and v in the CTA's own panels
     ce_wait();         // every CTA of the cluster has finished reading its panels: they may be overwritten
     if (tdbg) tdbg[6] = clock64();
+    if (last && threadIdx.x < CE_CLUSTER) {
+        // this tile's partial sums to every CTA of the cluster.  warps: w = (2 X + fld) 2 + nt; u: warps 0, 1, 4, 5; v: 2, 3, 6, 7
+        const double* r = S.red;
+        const double o[6] = {((r[0 * 4 + 0] + r[1 * 4 + 0]) + r[4 * 4 + 0]) + r[5 * 4 + 0],
+                             ((r[0 * 4 + 1] + r[1 * 4 + 1]) + r[4 * 4 + 1]) + r[5 * 4 + 1],
+                             ((r[2 * 4 + 0] + r[3 * 4 + 0]) + r[6 * 4 + 0]) + r[7 * 4 + 0],
+                             ((r[2 * 4 + 1] + r[3 * 4 + 1]) + r[6 * 4 + 1]) + r[7 * 4 + 1],
+                             nanmax(nanmax(r[0 * 4 + 2], r[1 * 4 + 2]), nanmax(r[4 * 4 + 2], r[5 * 4 + 2])),
+                             nanmax(nanmax(r[2 * 4 + 2], r[3 * 4 + 2]), nanmax(r[6 * 4 + 2], r[7 * 4 + 2]))};
+        if ((int)threadIdx.x == G.rank) {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) S.part[G.rank * 8 + q] = o[q];
+        } else {
+            const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x), bar = ce_mapa(S.partbar, threadIdx.x);
+#pragma unroll
+            for (int q = 0; q < 6; ++q) ce_sta(dst + 8 * q, o[q], bar);
+        }
+    }
     // u and v leave for the other CTAs' panels ahead of the pressure update (not at the last stage of a step, where all the
     // sends run beside warp 0's reduction: the caller's)
     if (!last) {
@@ -495,24 +523,6 @@ __device__ __forceinline__ void ce_finish(const S2Params& P, const S2Visit& V, c
             }
             S.edgep[2 * line * S2_HP + k] = 0.5 * (x + y);
             S.edgep[(2 * line + 1) * S2_HP + k] = 0.5 * (x - y);
-        }
-    }
-    if (last && threadIdx.x < CE_CLUSTER) {
-        // this tile's partial sums to every CTA of the cluster.  warps: w = (2 X + fld) 2 + nt; u: warps 0, 1, 4, 5; v: 2, 3, 6, 7
-        const double* r = S.red;
-        const double o[6] = {((r[0 * 4 + 0] + r[1 * 4 + 0]) + r[4 * 4 + 0]) + r[5 * 4 + 0],
-                             ((r[0 * 4 + 1] + r[1 * 4 + 1]) + r[4 * 4 + 1]) + r[5 * 4 + 1],
-                             ((r[2 * 4 + 0] + r[3 * 4 + 0]) + r[6 * 4 + 0]) + r[7 * 4 + 0],
-                             ((r[2 * 4 + 1] + r[3 * 4 + 1]) + r[6 * 4 + 1]) + r[7 * 4 + 1],
-                             nanmax(nanmax(r[0 * 4 + 2], r[1 * 4 + 2]), nanmax(r[4 * 4 + 2], r[5 * 4 + 2])),
-                             nanmax(nanmax(r[2 * 4 + 2], r[3 * 4 + 2]), nanmax(r[6 * 4 + 2], r[7 * 4 + 2]))};
-        if ((int)threadIdx.x == G.rank) {
-#pragma unroll
-            for (int q = 0; q < 6; ++q) S.part[G.rank * 8 + q] = o[q];
-        } else {
-            const unsigned dst = ce_mapa(S.part + G.rank * 8, threadIdx.x), bar = ce_mapa(S.partbar, threadIdx.x);
-#pragma unroll
-            for (int q = 0; q < 6; ++q) ce_sta(dst + 8 * q, o[q], bar);
         }
     }
     __syncthreads();   // the CTA's own panels are complete: the caller runs the local part of the next K loop
@@ -582,7 +592,8 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 reinterpret_cast<double2*>(S.cp)[e] = __ldcg(reinterpret_cast<const double2*>(srcB) + e);
         }
         ce_visit_prepare(S, V.first != 0, rec + S2_EDGE_OFF, ul, vl, m, h, n1);   // ends with a CTA barrier
-        double dt = s2_dt(st.umax, st.vmax, V.lidv, V.nu, V.beta2, V.cfl, P.dx_min, P.dy_min);
+        const double nu_dx2 = V.nu / (P.dx_min * P.dx_min), nu_dy2 = V.nu / (P.dy_min * P.dy_min);
+        double dt = ce_dt(st.umax, st.vmax, V.lidv, V.beta2, V.cfl, P.dx_min, P.dy_min, nu_dx2, nu_dy2);
         bool bc_lines = !V.first, active = true;
         double fN[4], pN[4];
 #pragma unroll
@@ -590,9 +601,12 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
 
         // end of a step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread (the same numbers
         // everywhere): convergence bookkeeping, dt of the next step
+        long long* red_dbg = nullptr;   // LDC_S2_DEBUG: [11..15] clock samples inside the reduction
         auto reduce_step = [&](bool first_step) {
+            if (red_dbg) red_dbg[11] = clock64();
             const double* es = S.step + (first_step ? 2 : 8);
             double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0.0, 0.0};
+#pragma unroll
             for (int tl = 0; tl < CE_CLUSTER; ++tl) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
@@ -601,26 +615,13 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
             }
             st.umax = nanmax(mx[0], S.step[6]);
             st.vmax = nanmax(mx[1], S.step[7]);
-            // The six square roots and then the six divisions of the residuals and of s2_dt are independent of each other:
-            // lane l of every warp takes the l-th, so that their latencies (a couple of hundred cycles each) overlap.  Same
-            // operations on the same operands as the serial forms (s2_dt; sqrt(s0) / (sqrt(s1) + 1e-12)).
-            const double ua = (V.lidv > st.umax) ? V.lidv : st.umax, va = (1e-10 > st.vmax) ? 1e-10 : st.vmax;
-            const double sq_arg = lane == 0 ? s[0] : (lane == 1 ? s[1] : (lane == 2 ? s[2] : (lane == 3 ? s[3] :
-                                  (lane == 4 ? ua * ua + V.beta2 : va * va + V.beta2))));
-            const double sq = sqrt(sq_arg);
-            const double r0 = __shfl_sync(0xffffffffu, sq, 0), r1 = __shfl_sync(0xffffffffu, sq, 1),
-                         r2 = __shfl_sync(0xffffffffu, sq, 2), r3 = __shfl_sync(0xffffffffu, sq, 3),
-                         r4 = __shfl_sync(0xffffffffu, sq, 4), r5 = __shfl_sync(0xffffffffu, sq, 5);
-            const double num = lane == 0 ? r0 : (lane == 1 ? r2 : (lane == 2 ? ua + r4 : (lane == 3 ? va + r5 : V.nu)));
-            const double den = lane == 0 ? r1 + 1e-12 : (lane == 1 ? r3 + 1e-12 : (lane == 2 ? P.dx_min : (lane == 3 ? P.dy_min :
-                               (lane == 4 ? P.dx_min * P.dx_min : P.dy_min * P.dy_min))));
-            const double qt = num / den;
-            const double ures = __shfl_sync(0xffffffffu, qt, 0), vres = __shfl_sync(0xffffffffu, qt, 1);
-            const double lam_x = __shfl_sync(0xffffffffu, qt, 2) + __shfl_sync(0xffffffffu, qt, 4);
-            const double lam_y = __shfl_sync(0xffffffffu, qt, 3) + __shfl_sync(0xffffffffu, qt, 5);
+            if (red_dbg) red_dbg[12] = clock64();
+            const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
+            if (red_dbg) red_dbg[14] = clock64();
             update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
             active = st.active != 0;
-            dt = V.cfl / (lam_x + lam_y);
+            dt = ce_dt(st.umax, st.vmax, V.lidv, V.beta2, V.cfl, P.dx_min, P.dy_min, nu_dx2, nu_dy2);
+            if (red_dbg) red_dbg[15] = clock64();
         };
         // Start of a stage: accumulators to zero, then the part of the K loop that needs no one else's output (three
         // half-steps) -- with the st.async stores of the previous stage's output to the other CTAs' panels (ce_send, out of
@@ -699,6 +700,7 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
                 if (X == 0) ce_finish<0>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, tdbg);
                 else ce_finish<1>(P, V, S, G, b, stage, bc_lines, dt, fld, nt, lane, uo, vo, fN, pN, a1, a2, aL, nullptr);
                 bc_lines = true;
+                red_dbg = tdbg;
                 start_stage(true, !(P.freeze && stage != 3), stage == 3, V.first && step == 0);
                 if (stage == 3) {
                     __syncthreads();   // warp 0's verdict on the step
