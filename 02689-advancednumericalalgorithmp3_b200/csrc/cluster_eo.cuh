@@ -13,7 +13,7 @@
 //   * the K loop of a stage runs in two parts: the half-steps on state the CTA produced itself right after its own stores,
 //     with the remote stores issued between them, the others once the mbarrier says that everything has arrived;
 //   * the end-of-step sums (convergence norms, maxima for the next dt) travel the same way ahead of the last stage's output
-//     and are reduced, in fixed order, by warp 0 of every CTA while the other warps send; status and state go back to the
+//     and are reduced, in fixed order, by warps 0 and 1 of every CTA while the other warps send; status and state go back to the
 //     record in L2 only at the end of a visit.
 // What bounds it: the SM-to-SM network takes ~20 B/clk out of an SM (scripts/dsmem_bw.cu, profiles/r02_dsmem_bw.txt), and
 // a stage sends 48 KB per CTA; the K loop of a stage is 80 DMMAs per warp, two warps per SM sub-partition.
@@ -602,26 +602,36 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
         // end of a step: the eight tiles' partial sums + boundary lines, in fixed order, by every thread (the same numbers
         // everywhere): convergence bookkeeping, dt of the next step
         long long* red_dbg = nullptr;   // LDC_S2_DEBUG: [11..15] clock samples inside the reduction
-        auto reduce_step = [&](bool first_step) {
-            if (red_dbg) red_dbg[11] = clock64();
-            const double* es = S.step + (first_step ? 2 : 8);
-            double s[4] = {es[0], es[1], es[2], es[3]}, mx[2] = {0.0, 0.0};
+        // Two warps share it at the end of a step (start_stage): warp 0 the residuals and the bookkeeping, warp 1 the next dt.
+        auto reduce_maxima = [&]() {
+            double mx[2] = {0.0, 0.0};
 #pragma unroll
             for (int tl = 0; tl < CE_CLUSTER; ++tl) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
                 mx[0] = nanmax(mx[0], S.part[tl * 8 + 4]);
                 mx[1] = nanmax(mx[1], S.part[tl * 8 + 5]);
             }
             st.umax = nanmax(mx[0], S.step[6]);
             st.vmax = nanmax(mx[1], S.step[7]);
+        };
+        auto reduce_status = [&](bool first_step) {
+            if (red_dbg) red_dbg[11] = clock64();
+            const double* es = S.step + (first_step ? 2 : 8);
+            double s[4] = {es[0], es[1], es[2], es[3]};
+#pragma unroll
+            for (int tl = 0; tl < CE_CLUSTER; ++tl)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) s[q] += S.part[tl * 8 + q];
+            reduce_maxima();
             if (red_dbg) red_dbg[12] = clock64();
             const double ures = sqrt(s[0]) / (sqrt(s[1]) + 1e-12), vres = sqrt(s[2]) / (sqrt(s[3]) + 1e-12);
             if (red_dbg) red_dbg[14] = clock64();
             update_status(st, ures, vres, V.tol, P.warmup, P.max_iter, P.nan_exit);
             active = st.active != 0;
-            dt = ce_dt(st.umax, st.vmax, V.lidv, V.beta2, V.cfl, P.dx_min, P.dy_min, nu_dx2, nu_dy2);
             if (red_dbg) red_dbg[15] = clock64();
+        };
+        auto reduce_dt = [&]() {
+            reduce_maxima();
+            dt = ce_dt(st.umax, st.vmax, V.lidv, V.beta2, V.cfl, P.dx_min, P.dy_min, nu_dx2, nu_dy2);
         };
         // Start of a stage: accumulators to zero, then the part of the K loop that needs no one else's output (three
         // half-steps) -- with the st.async stores of the previous stage's output to the other CTAs' panels (ce_send, out of
@@ -639,18 +649,20 @@ __global__ void __launch_bounds__(CE_THREADS, 1) k_cluster_eo(const S2Params P) 
             const int ka = 2 * G.trow + X, kb0 = 4 * G.tcol + X, kb1 = kb0 + 2;
             const int nb = with_p ? 12 : 8;
             if (reduce_now) {
-                // Last stage of a step: warp 0 runs the step's reduction (convergence, dt: ~2.2 k cycles of dependent FP64
-                // operations; the others' sums left before their stage output) while the other seven warps push the stage
-                // output into the network -- which takes them as long, the network being what limits the stores.
-                if (warp == 0) {
+                // Last stage of a step: warps 0 and 1 run the step's reduction (residuals + bookkeeping, and the next dt:
+                // ~1.2 k cycles of dependent FP64 operations each; the others' sums left ahead of their stage output) while the
+                // other six warps push the stage output into the network.
+                if (warp < 2) {
                     mbar_wait(S.partbar, npart & 1);
-                    reduce_step(first_step);
-                    if (lane == 0) {
-                        S.step[0] = dt;
-                        S.step[1] = active ? 1.0 : 0.0;
+                    if (warp == 0) {
+                        reduce_status(first_step);
+                        if (lane == 0) S.step[1] = active ? 1.0 : 0.0;
+                    } else {
+                        reduce_dt();
+                        if (lane == 0) S.step[0] = dt;
                     }
                 } else {
-                    for (int e = tid - 32; e < 64 * nb; e += CE_THREADS - 32) ce_send_slot(S, G, e, nb);
+                    for (int e = tid - 64; e < 64 * nb; e += CE_THREADS - 64) ce_send_slot(S, G, e, nb);
                 }
                 ++npart;
             }

@@ -28,5 +28,5 @@ for k, nm in enumerate(names):
     c = d[:, order[k + 1]] - d[:, order[k]]
     print(f"{nm:42s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}")
 r3 = d[3::4]
-print("reduction on warp 0 (last stage): wait for the sums + their addition", (r3[:, 12] - r3[:, 11]).mean(), "| residuals", (r3[:, 14] - r3[:, 12]).mean(), "| status, dt", (r3[:, 15] - r3[:, 14]).mean(), "| start after the stage's [5]:", (r3[:, 11] - r3[:, 5]).mean())
+print("reduction on warp 0 (last stage): wait for the sums + their addition", (r3[:, 12] - r3[:, 11]).mean(), "| residuals", (r3[:, 14] - r3[:, 12]).mean(), "| status", (r3[:, 15] - r3[:, 14]).mean(), "| start after the stage's [5]:", (r3[:, 11] - r3[:, 5]).mean())
 print("stage period: mean", np.diff(d[:, 0]).mean(), "clk;  last stage of a step to the next:", np.diff(d[:, 0])[3::4].mean())
