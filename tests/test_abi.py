@@ -43,6 +43,8 @@ def test_library_contains_sm100a_dmma_code(built_lib):
     assert "UBLKCP" in out and "SYNCS.ARRIVE.TRANS64" in out, "k_stream_tma must issue cp.async.bulk (TMA) copies"
     # the cluster-resident kernel separates its stages with the hardware cluster barrier
     assert "k_cluster_eo" in out and "UCGABAR_ARV" in out and "UCGABAR_WAIT" in out
+    # ... and exchanges their output through distributed shared memory by st.async stores counted on the receiver's mbarrier
+    assert "STAS" in out, "k_cluster_eo must issue st.async (STAS) stores"
 
 
 def test_batch_beyond_the_grid_limit_is_refused(built_lib):
